@@ -1,0 +1,31 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    config.addinivalue_line("markers", "reference: needs the read-only reference tree at /root/reference")
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    from oracle import binding
+
+    binding.build()
+    return binding
+
+
+@pytest.fixture(scope="session")
+def ref():
+    import refimport
+
+    if not refimport.available():
+        pytest.skip("reference tree not present (expected on the GPU box)")
+    return refimport.load_reference()

@@ -1,0 +1,188 @@
+"""Generate the committed golden vectors by running the UNMODIFIED reference on CPU.
+
+Run in the build container only (needs /root/reference):
+    python tests/golden/make_golden.py
+Writes tests/golden/*.npz.  The reference has no tests or fixtures of its own for this path
+(SURVEY.md section 4), so these outputs of the reference itself are what pins the oracle
+(oracle/cfd3d_oracle.c) and, through it and directly, the CUDA kernels.
+
+Every array stored under a key starting with "in_" is an input, "out_" an output of reference code.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import refimport  # noqa: E402
+from centerfusiondetect3d_b200 import synthetic as syn  # noqa: E402
+from helpers import ensure_margins, ref_assoc_indices, ref_pc_dep_from_points, tie_free  # noqa: E402
+
+torch.set_num_threads(1)
+ns = refimport.load_reference()
+
+
+def t(a):
+    return torch.from_numpy(np.ascontiguousarray(a))
+
+
+def save(name, **arrs):
+    path = os.path.join(HERE, name + ".npz")
+    np.savez_compressed(path, **arrs)
+    print("wrote", path, os.path.getsize(path) // 1024, "KiB")
+
+
+def gen_topk_nms():
+    wl = syn.Workload("g_topk", 2, 24, 40, 20, 0, C=4, blobs=12)
+    for seed in range(100, 200):
+        rng = np.random.default_rng(seed)
+        heat = syn.make_heatmap(rng, wl.B, wl.C, wl.H, wl.W, wl.blobs)
+        if tie_free(heat, wl.K + 8):
+            break
+    nmsd = ns.nms(t(heat))
+    raw = ns.topk(t(heat), K=wl.K)
+    sup = ns.topk(nmsd, K=wl.K)
+    feat = rng.normal(size=(2, 5, 24, 40)).astype(np.float32)
+    g = ns.transposeAndGetFeature(t(feat), raw[1])
+    save("topk_nms", in_heat=heat, in_K=np.int64(wl.K), out_nms=nmsd.numpy(),
+         out_raw_scores=raw[0].numpy(), out_raw_inds=raw[1].numpy(), out_raw_classes=raw[2].numpy(),
+         out_raw_ys=raw[3].numpy(), out_raw_xs=raw[4].numpy(),
+         out_nms_scores=sup[0].numpy(), out_nms_inds=sup[1].numpy(), out_nms_classes=sup[2].numpy(),
+         out_nms_ys=sup[3].numpy(), out_nms_xs=sup[4].numpy(),
+         in_feat=feat, out_gather=g.numpy())
+
+
+def gen_alpha_thr():
+    rng = np.random.default_rng(7)
+    B, K = 3, 64
+    rot = rng.normal(size=(B, K, 8)).astype(np.float32)
+    rot[0, 0, 1] = rot[0, 0, 5]  # tie in the bin classifier -> second branch
+    dim = np.stack([rng.uniform(0.5, 4, (B, K)), rng.uniform(0.5, 3, (B, K)), rng.uniform(0.5, 12, (B, K))], -1).astype(np.float32)
+    center = np.stack([rng.uniform(0, 200, (B, K)), rng.uniform(0, 112, (B, K))], -1).astype(np.float32)
+    calib = syn.make_calib(rng, B).astype(np.float32)
+    alpha = ns.get_alpha(t(rot))
+    thr = ns.getDistanceThresh(t(calib), t(center), t(dim), alpha)
+    save("alpha_thr", in_rot=rot, in_dim=dim, in_center=center, in_calib=calib, out_alpha=alpha.numpy(), out_thr=thr.numpy())
+
+
+def gen_pillars():
+    cfg_a = refimport.make_config(K=100, out_hw=(112, 200))
+    cfg_b = refimport.make_config(K=100, out_hw=(225, 400))
+    arrs = {}
+    for tag, cfg, n, seed in (("a", cfg_a, 100, 11), ("b", cfg_b, 300, 12), ("c", cfg_a, 2000, 13)):
+        H, W = cfg.MODEL.OUTPUT_SIZE
+        rng = np.random.default_rng(seed)
+        pts, counts = syn.make_radar(rng, 1, n)
+        calib = syn.make_calib(rng, 1)
+        A = syn.output_affine(H, W)
+        pc_dep = ref_pc_dep_from_points(ns, pts[0], calib[0], A, (1600, 900), cfg)
+        arrs.update({f"in_points_{tag}": pts, f"in_counts_{tag}": counts, f"in_calib_{tag}": calib,
+                     f"in_A_{tag}": A[None], f"in_hw_{tag}": np.array([H, W]), f"out_pc_dep_{tag}": pc_dep[None]})
+    save("pillars", **arrs)
+
+
+def _small_pc_dep(H, W, n, seed, cfg):
+    rng = np.random.default_rng(seed)
+    pts, _ = syn.make_radar(rng, 1, n)
+    calib = syn.make_calib(rng, 1)
+    A = syn.output_affine(H, W)
+    return ref_pc_dep_from_points(ns, pts[0], calib[0], A, (1600, 900), cfg)
+
+
+def gen_pc2hm_quirks():
+    H, W = 24, 40
+    cfg = refimport.make_config(K=10, out_hw=(H, W))
+    pc_dep = _small_pc_dep(H, W, 60, 21, cfg)
+    # two pillars of EQUAL depth but different velocity in one ROI (argmin tie -> first in row-major order)
+    pc_dep[:, 3:6, 30:32] = np.array([33.0, 1.0, 2.0], np.float32)[:, None, None]
+    pc_dep[:, 4:7, 34:36] = np.array([33.0, -3.0, 4.0], np.float32)[:, None, None]
+    cases = [
+        # bbox x1,y1,x2,y2, depth, thr
+        ([10.2, 5.1, 20.7, 15.9], 30.0, 40.0),    # ordinary
+        ([-3.5, 4.0, 8.5, 12.0], 30.0, 40.0),     # x1 < 0: negative slice start wraps -> ROI empty or shifted
+        ([-45.0, 4.0, 8.5, 12.0], 30.0, 40.0),    # x1 <= -W: start clamps to 0
+        ([2.0, -2.5, 12.0, 6.0], 30.0, 40.0),     # y1 < 0
+        ([30.0, 15.0, 47.0, 30.0], 30.0, 40.0),   # beyond right/bottom edge
+        ([12.5, 8.5, 12.5, 8.5], 30.0, 40.0),     # w = h = 0 box
+        ([28.5, 2.0, 37.5, 8.0], 33.0, 5.0),      # equal-depth tie between the two painted pillars
+        ([10.2, 5.1, 20.7, 15.9], 3.0, 40.0),     # depth - thr < 0 -> lower bound 0
+        ([10.2, 5.1, 20.7, 15.9], 200.0, 1.0),    # nothing within threshold
+        ([0.2, 0.3, 39.9, 23.8], 30.0, 100.0),    # whole map
+        ([1.0, 1.0, 3.0, 3.0], 30.0, 40.0),       # small box near the origin (paint w_min may be 1)
+        ([0.5, 0.5, 1.9, 1.7], 30.0, 40.0),       # paint window starts at 0 after trunc
+        ([36.0, 20.0, 39.5, 23.5], 30.0, 40.0),   # bottom-right corner
+    ]
+    # pillar depth exactly at depth +- thr (strict compares): take a depth present in the map
+    dvals = np.unique(pc_dep[0][pc_dep[0] != 0])
+    d0 = float(dvals[len(dvals) // 2])
+    cases.append(([0.2, 0.3, 39.9, 23.8], d0 - 2.0, 2.0))   # d0 == depth + thr -> excluded
+    cases.append(([0.2, 0.3, 39.9, 23.8], d0 + 2.0, 2.0))   # d0 == depth - thr -> excluded
+    outs, assoc = [], []
+    idxmap = pc_dep.copy()
+    idxmap[1] = np.arange(H * W, dtype=np.float32).reshape(H, W)
+    for bbox, depth, thr in cases:
+        hm = torch.zeros(3, H, W)
+        ns.cvtPcDepthToHeatmap(hm, t(pc_dep), torch.tensor([depth]), torch.tensor(bbox), torch.tensor(thr), 60.0)
+        outs.append(hm.numpy())
+        hm2 = torch.zeros(3, H, W)
+        ns.cvtPcDepthToHeatmap(hm2, t(idxmap), torch.tensor([depth]), torch.tensor(bbox), torch.tensor(thr), 60.0)
+        w = hm2[0] != 0
+        assoc.append(int(hm2[1][w][0].item()) if w.any() else -1)
+    save("pc2hm_quirks", in_pc_dep=pc_dep, in_bbox=np.array([c[0] for c in cases], np.float32),
+         in_depth=np.array([c[1] for c in cases], np.float32), in_thr=np.array([c[2] for c in cases], np.float32),
+         in_max_pc_dist=np.float32(60.0), out_pc_hm=np.stack(outs), out_assoc=np.array(assoc, np.int32))
+
+
+def gen_frustum_and_decode():
+    wl = syn.Workload("g_frustum", 2, 48, 80, 40, 300, C=4, blobs=25)
+    # PILLAR_DIMS is a config knob (configs/*.yaml DATASET.PILLAR_DIMS); larger pillars give the small map real coverage
+    cfg = refimport.make_config(K=wl.K, out_hw=(wl.H, wl.W), pillar_dims=(3.0, 0.8, 0.8))
+    for seed in range(300, 400):
+        inp = syn.make_inputs(wl, seed=seed)
+        if tie_free(inp["heatmap"], wl.K + 8):
+            break
+    inp["widthHeight"] *= 0.5  # boxes sized for the small map
+    pc_dep = np.stack([ref_pc_dep_from_points(ns, inp["radar_points"][b], inp["calib64"][b], inp["A_out"][b],
+                                              (1600, 900), cfg) for b in range(wl.B)])
+    nudged = ensure_margins(inp, pc_dep, wl.K, wl.max_pc_dist)
+    print("frustum golden: nudged", nudged, "depth values for margin")
+    output = {k: t(inp[k]) for k in ("heatmap", "widthHeight", "depth", "dimension", "rotation")}
+    pc_hm = ns.getPcFrustumHeatmap(output, t(pc_dep), t(inp["calib"]), cfg)
+    assoc, thr = ref_assoc_indices(ns, inp, pc_dep, wl.K, wl.max_pc_dist)
+    print("frustum golden: matched", int((assoc >= 0).sum()), "of", assoc.size)
+    arrs = {"in_" + k: inp[k] for k in ("heatmap", "widthHeight", "depth", "dimension", "rotation", "calib", "reg",
+                                         "amodal_offset", "velocity", "nuscenes_att", "depth2", "rotation2")}
+    arrs.update(in_pc_dep=pc_dep, in_K=np.int64(wl.K), in_max_pc_dist=np.float32(wl.max_pc_dist),
+                out_pc_hm=pc_hm.numpy(), out_assoc=assoc, out_thr=thr)
+    # decode variants on the same maps
+    unc = np.random.default_rng(5).normal(-1.0, 0.5, size=(wl.B, 1, wl.H, wl.W)).astype(np.float32)
+    arrs["in_uncertainty"] = unc
+    variants = {
+        "full": dict(keys=("heatmap", "reg", "widthHeight", "depth", "depth2", "rotation", "rotation2", "dimension",
+                           "amodal_offset", "nuscenes_att", "velocity"), norm2d=False),
+        "noreg_norm2d": dict(keys=("heatmap", "widthHeight", "depth", "rotation", "dimension", "amodal_offset"), norm2d=True),
+        "unc": dict(keys=("heatmap", "reg", "widthHeight", "depth2", "rotation2", "dimension", "velocity", "uncertainty"), norm2d=False),
+    }
+    for vname, v in variants.items():
+        out = {k: t(unc if k == "uncertainty" else inp[k]).clone() for k in v["keys"]}
+        ret = ns.fusionDecode([out], outputSize=(wl.H, wl.W), K=wl.K, norm2d=v["norm2d"])
+        for k, val in ret.items():
+            arrs[f"out_dec_{vname}_{k}"] = val.numpy()
+        arrs[f"in_dec_{vname}_keys"] = np.array(",".join(v["keys"]))
+        arrs[f"in_dec_{vname}_norm2d"] = np.bool_(v["norm2d"])
+    save("frustum_decode", **arrs)
+
+
+if __name__ == "__main__":
+    gen_topk_nms()
+    gen_alpha_thr()
+    gen_pillars()
+    gen_pc2hm_quirks()
+    gen_frustum_and_decode()

@@ -1,0 +1,110 @@
+"""Pin the CPU oracle (oracle/cfd3d_oracle.c) against golden vectors produced by the reference itself
+(tests/golden/make_golden.py).  CPU-only; runs everywhere."""
+import numpy as np
+
+from helpers import load_golden
+
+RTOL_LIBM = 2e-6  # reference trig is 1-ulp SLEEF fp32, oracle is fp64-rounded: a few ulp on derived values
+
+
+def test_nms_bit_exact(oracle):
+    g = load_golden("topk_nms")
+    out = oracle.nms(g["in_heat"])
+    assert np.array_equal(out.view(np.uint32), g["out_nms"].view(np.uint32))
+
+
+def test_topk_raw_and_nms_bit_exact(oracle):
+    g = load_golden("topk_nms")
+    K = int(g["in_K"])
+    for tag, apply_nms in (("raw", False), ("nms", True)):
+        s, i, c, y, x = oracle.topk(g["in_heat"], K, apply_nms=apply_nms)
+        assert np.array_equal(s.view(np.uint32), g[f"out_{tag}_scores"].view(np.uint32))
+        assert np.array_equal(i, g[f"out_{tag}_inds"])
+        assert c.dtype == g[f"out_{tag}_classes"].dtype == np.int32
+        assert np.array_equal(c, g[f"out_{tag}_classes"])
+        assert np.array_equal(y, g[f"out_{tag}_ys"])
+        assert np.array_equal(x, g[f"out_{tag}_xs"])
+
+
+def test_gather_bit_exact(oracle):
+    g = load_golden("topk_nms")
+    out = oracle.gather_nchw(g["in_feat"], g["out_raw_inds"])
+    assert np.array_equal(out, g["out_gather"])
+
+
+def test_alpha_and_dist_thresh(oracle):
+    g = load_golden("alpha_thr")
+    alpha = oracle.get_alpha(g["in_rot"])
+    np.testing.assert_allclose(alpha, g["out_alpha"], rtol=RTOL_LIBM, atol=1e-6)
+    # feed the reference's alpha so only yaw/corners/threshold arithmetic is compared
+    thr = oracle.dist_thresh(g["in_calib"], g["in_center"], g["in_dim"], g["out_alpha"])
+    np.testing.assert_allclose(thr, g["out_thr"], rtol=RTOL_LIBM, atol=1e-6)
+
+
+def test_pc_dep_to_hm_quirks_bit_exact(oracle):
+    g = load_golden("pc2hm_quirks")
+    pc_dep = g["in_pc_dep"]
+    n = len(g["in_depth"])
+    matched = 0
+    for j in range(n):
+        hm = np.zeros_like(pc_dep)
+        a = oracle.pc_dep_to_hm(hm, pc_dep, g["in_depth"][j], g["in_bbox"][j], g["in_thr"][j], float(g["in_max_pc_dist"]))
+        assert np.array_equal(hm.view(np.uint32), g["out_pc_hm"][j].view(np.uint32)), f"case {j}"
+        if g["out_assoc"][j] >= 0:
+            assert a == g["out_assoc"][j], f"case {j}"
+            matched += 1
+        elif a >= 0:  # reference wrote nothing: only legal when the paint window is empty
+            assert not hm.any()
+    assert matched >= 5
+
+
+def test_pillars_bit_exact(oracle):
+    g = load_golden("pillars")
+    for tag in "abc":
+        H, W = (int(v) for v in g[f"in_hw_{tag}"])
+        calib = g[f"in_calib_{tag}"]
+        pc_dep, owner = oracle.radar_pillars(g[f"in_points_{tag}"], g[f"in_counts_{tag}"], calib[:, :, :3], calib,
+                                             g[f"in_A_{tag}"], (1600, 900), (H, W))
+        ref = g[f"out_pc_dep_{tag}"]
+        assert np.array_equal(pc_dep.view(np.uint32), ref.view(np.uint32)), tag
+        assert ((owner >= 0) == (ref[:, 0] != 0)).all()
+        assert (ref[:, 0] != 0).mean() > 0.05
+
+
+def test_frustum_pc_hm(oracle):
+    g = load_golden("frustum_decode")
+    K = int(g["in_K"])
+    pc_hm, assoc, thr, _ = oracle.frustum_pc_hm(g["in_heatmap"], g["in_widthHeight"], g["in_depth"], g["in_dimension"],
+                                                g["in_rotation"], g["in_pc_dep"], g["in_calib"], K,
+                                                float(g["in_max_pc_dist"]))
+    # end to end thr passes through alpha -> yaw -> sin/cos times up to l/2 = 6 m: 1-ulp libm differences in the
+    # reference (SLEEF fp32) amplify to a few 1e-6 absolute
+    np.testing.assert_allclose(thr, g["out_thr"], rtol=2e-5, atol=5e-6)
+    known = g["out_assoc"] != -2
+    assert np.array_equal(assoc[known], g["out_assoc"][known])  # association indices bit-exact
+    assert (g["out_assoc"] >= 0).sum() >= 10
+    # every painted value is a copy of a pc_dep value (or d/60): bit-exact
+    assert np.array_equal(pc_hm.view(np.uint32), g["out_pc_hm"].view(np.uint32))
+
+
+def _decode_inputs(g, vname):
+    keys = str(g[f"in_dec_{vname}_keys"]).split(",")
+    return {k: g["in_" + k] for k in keys}, bool(g[f"in_dec_{vname}_norm2d"])
+
+
+def test_fusion_decode_variants(oracle):
+    g = load_golden("frustum_decode")
+    K = int(g["in_K"])
+    H, W = g["in_heatmap"].shape[2:]
+    for vname in ("full", "noreg_norm2d", "unc"):
+        out, norm2d = _decode_inputs(g, vname)
+        ret = oracle.fusion_decode(out, (H, W), K, norm2d)
+        ref_keys = sorted(k[len(f"out_dec_{vname}_"):] for k in g if k.startswith(f"out_dec_{vname}_"))
+        assert sorted(k for k in ret if not k.startswith("_")) == ref_keys, vname
+        for k in ref_keys:
+            refv = g[f"out_dec_{vname}_{k}"]
+            assert ret[k].shape == refv.shape and ret[k].dtype == refv.dtype, (vname, k)
+            if k == "scores" and vname == "unc":
+                np.testing.assert_allclose(ret[k], refv, rtol=1e-6)  # expf differs by an ulp
+            else:
+                assert np.array_equal(ret[k].view(np.uint32), refv.view(np.uint32)), (vname, k)
