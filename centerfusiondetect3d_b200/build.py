@@ -1,0 +1,53 @@
+"""Builds libcfd3d_b200.so (the C-ABI CUDA library) in-tree with nvcc for sm_100a.
+
+    python -m centerfusiondetect3d_b200.build [--force]
+
+nvcc cross-compiles without a GPU; the resulting .so travels to the GPU box with the repo snapshot.
+Flags: -fmad=false keeps one rounding per written fp32/fp64 operation (parity contract),
+-lineinfo maps ncu's source page back to the .cu files.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libcfd3d_b200.so")
+SOURCES = ["api.cu", "peak_select.cu", "frustum.cu"]
+HEADERS = ["common.cuh", "select.cuh", "geometry.cuh", "kernels.cuh", os.path.join("..", "..", "include", "cfd3d_b200.h")]
+
+NVCC_FLAGS = [
+    "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",
+    "-Xcompiler", "-fPIC,-fvisibility=hidden,-O2", "-shared", "-Xptxas", "-v",
+]
+
+
+def _stale() -> bool:
+    if not os.path.isfile(LIB):
+        return True
+    t = os.path.getmtime(LIB)
+    deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__)]
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    if not force and not _stale():
+        return LIB
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    cmd = [nvcc] + NVCC_FLAGS + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    log = os.path.join(HERE, "build.log")
+    with open(log, "w") as f:
+        f.write(" ".join(cmd) + "\n" + res.stdout + res.stderr)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+        raise RuntimeError("nvcc failed building libcfd3d_b200.so (see %s)" % log)
+    if verbose:
+        sys.stderr.write(res.stderr)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose=True))

@@ -1,0 +1,276 @@
+// api.cu -- the C ABI of libcfd3d_b200.so (include/cfd3d_b200.h): argument checks, workspace carving and
+// kernel sequencing.  No allocation, no host synchronisation, no CPU compute path: every entry point
+// either launches the sm_100a kernels on the caller's stream or returns an error.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "kernels.cuh"
+
+using namespace cf;
+
+static thread_local char g_err[512] = "";
+static thread_local int g_launches = 0;
+
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+static int cuda_fail(cudaError_t e, const char* what) {
+    snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+    return (int)e;
+}
+#define CF_CUDA(call, what)                         \
+    do {                                            \
+        cudaError_t e__ = (call);                   \
+        if (e__ != cudaSuccess) return cuda_fail(e__, what); \
+    } while (0)
+
+static int check_dims(int B, int C, int H, int W) {
+    if (B < 0 || C < 1 || H < 1 || W < 1) return fail(CF_E_SHAPE, "bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+    if ((long long)C * H * W >= (1ll << 31)) return fail(CF_E_RANGE, "C*H*W does not fit 31 bits");
+    return 0;
+}
+static int check_k(int K, int H, int W) {
+    if (K < 1 || (long long)K > (long long)H * W)
+        return fail(CF_E_K, "K=%d out of range for a %dx%d map (selected index k out of range)", K, H, W);
+    if (K > CF_MAX_K) return fail(CF_E_K, "K=%d exceeds CF_MAX_K=%d", K, CF_MAX_K);
+    return 0;
+}
+static int check_ws(void* ws, size_t ws_bytes, size_t need) {
+    if (!ws) return fail(CF_E_WORKSPACE, "workspace is NULL (need %zu bytes)", need);
+    if (reinterpret_cast<uintptr_t>(ws) & 255u) return fail(CF_E_WORKSPACE, "workspace must be 256-byte aligned");
+    if (ws_bytes < need) return fail(CF_E_WORKSPACE, "workspace too small: %zu < %zu", ws_bytes, need);
+    return 0;
+}
+static bool misaligned4(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 3u) != 0; }
+
+extern "C" {
+
+int cf_version(void) { return 100; }
+const char* cf_last_error(void) { return g_err; }
+int cf_last_launch_count(void) { return g_launches; }
+
+size_t cf_workspace_bytes(int B, int C, int H, int W, int K) {
+    Plan plan;
+    if (B < 0 || C < 1 || H < 1 || W < 1 || K < 1 || K > CF_MAX_K || !make_plan(C, H, W, K, &plan)) return 0;
+    return workspace_layout(B, C, H, W, K, plan, nullptr, nullptr) + 256;
+}
+
+size_t cf_pillars_workspace_bytes(int B, int Nmax) {
+    if (B < 0 || Nmax < 0) return 0;
+    return (size_t)B * (size_t)Nmax * sizeof(PaintRec) + 256;
+}
+
+int cf_nms(const float* heat, int B, int C, int H, int W, float* out, void* stream) {
+    g_launches = 0;
+    if (!heat || !out) return fail(CF_E_NULL, "cf_nms: NULL pointer");
+    if (int rc = check_dims(B, C, H, W)) return rc;
+    if (B == 0) return 0;
+    int n = 0;
+    CF_CUDA(launch_nms(heat, B, C, H, W, out, (cudaStream_t)stream, &n), "cf_nms");
+    g_launches = n;
+    return 0;
+}
+
+int cf_gather_nchw(const float* feat, int B, int ch, int64_t HW, const int64_t* inds, int M, float* out,
+                   void* stream) {
+    g_launches = 0;
+    if (!feat || !inds || !out) return fail(CF_E_NULL, "cf_gather_nchw: NULL pointer");
+    if (B < 0 || ch < 1 || HW < 1 || M < 0) return fail(CF_E_SHAPE, "cf_gather_nchw: bad shape");
+    int n = 0;
+    CF_CUDA(launch_gather(feat, B, ch, HW, inds, M, out, (cudaStream_t)stream, &n), "cf_gather_nchw");
+    g_launches = n;
+    return 0;
+}
+
+int cf_get_alpha(const float* rot, int64_t n_, float* alpha, void* stream) {
+    g_launches = 0;
+    if (!rot || !alpha) return fail(CF_E_NULL, "cf_get_alpha: NULL pointer");
+    if (n_ < 0) return fail(CF_E_SHAPE, "cf_get_alpha: n < 0");
+    int n = 0;
+    CF_CUDA(launch_alpha(rot, n_, alpha, (cudaStream_t)stream, &n), "cf_get_alpha");
+    g_launches = n;
+    return 0;
+}
+
+int cf_dist_thresh(const float* calib, const float* center, const float* dim, const float* alpha, int B, int K,
+                   float* thr, void* stream) {
+    g_launches = 0;
+    if (!calib || !center || !dim || !alpha || !thr) return fail(CF_E_NULL, "cf_dist_thresh: NULL pointer");
+    if (B < 0 || K < 0) return fail(CF_E_SHAPE, "cf_dist_thresh: bad shape");
+    int n = 0;
+    CF_CUDA(launch_dist_thresh(calib, center, dim, alpha, B, K, thr, (cudaStream_t)stream, &n), "cf_dist_thresh");
+    g_launches = n;
+    return 0;
+}
+
+int cf_peak_topk(const float* heat, int B, int C, int H, int W, int K, int apply_nms, float* scores, int64_t* inds,
+                 int32_t* classes, int64_t* ys, int64_t* xs, void* ws, size_t ws_bytes, void* stream) {
+    g_launches = 0;
+    if (!heat) return fail(CF_E_NULL, "cf_peak_topk: heat is NULL");
+    if (int rc = check_dims(B, C, H, W)) return rc;
+    if (int rc = check_k(K, H, W)) return rc;
+    if (misaligned4(heat)) return fail(CF_E_ALIGN, "cf_peak_topk: heat not 4-byte aligned");
+    Plan plan;
+    if (!make_plan(C, H, W, K, &plan)) return fail(CF_E_SHAPE, "cf_peak_topk: unsupported map geometry %dx%d", H, W);
+    Workspace w;
+    const size_t need = workspace_layout(B, C, H, W, K, plan, ws, &w);
+    if (int rc = check_ws(ws, ws_bytes, need)) return rc;
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    int n = 0;
+    const int list = apply_nms ? LIST_NMS : LIST_RAW;
+    CF_CUDA(launch_peak_select(heat, B, C, H, W, K, list, plan, w, st, &n), "peak_select");
+    MergeJob job;
+    memset(&job, 0, sizeof(job));
+    job.epilogue = EPI_TOPK;
+    job.topk = TopkOut{scores, inds, classes, ys, xs};
+    CF_CUDA(launch_merge(heat, B, C, H, W, K, plan, w, apply_nms ? nullptr : &job, apply_nms ? &job : nullptr, st, &n),
+            "merge");
+    g_launches = n;
+    return 0;
+}
+
+static int check_frustum_args(const float* heat, const float* wh, const float* depth, const float* dim,
+                              const float* rot, const float* pc_dep, const float* calib, float* pc_hm) {
+    if (!heat || !wh || !depth || !dim || !rot || !pc_dep || !calib || !pc_hm)
+        return fail(CF_E_NULL, "frustum: NULL map pointer");
+    if (misaligned4(heat) || misaligned4(wh) || misaligned4(depth) || misaligned4(dim) || misaligned4(rot) ||
+        misaligned4(pc_dep) || misaligned4(calib) || misaligned4(pc_hm))
+        return fail(CF_E_ALIGN, "frustum: pointer not 4-byte aligned");
+    return 0;
+}
+
+static int check_decode_args(const cf_decode_heads_t* h, const cf_decode_out_t* o) {
+    if (!h || !o) return fail(CF_E_NULL, "decode: heads/out struct is NULL");
+    if (!h->heatmap) return fail(CF_E_NULL, "decode: heatmap is NULL");
+    if (!o->scores || !o->class_ids || !o->centers) return fail(CF_E_NULL, "decode: scores/class_ids/centers NULL");
+    if ((h->wh && !o->bboxes) || (h->depth && !o->depth) || (h->rot && !o->rot) || (h->dim && !o->dim) ||
+        (h->amodal && !o->amodal) || (h->nuscenes_att && !o->nuscenes_att) || (h->velocity && !o->velocity))
+        return fail(CF_E_NULL, "decode: a head is present but its output pointer is NULL");
+    return 0;
+}
+
+int cf_frustum_pc_hm(const float* heat, const float* wh, const float* depth, const float* dim, const float* rot,
+                     const float* pc_dep, const float* calib, int B, int C, int H, int W, int K, float max_pc_dist,
+                     float* pc_hm, int32_t* assoc, float* thr, int64_t* inds, void* ws, size_t ws_bytes,
+                     void* stream) {
+    return cf_fusion_stage(heat, wh, depth, dim, rot, pc_dep, calib, B, C, H, W, K, max_pc_dist, pc_hm, assoc, thr,
+                           inds, nullptr, 0, 0, 0, nullptr, ws, ws_bytes, stream);
+}
+
+int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W, int K, int out_h, int out_w,
+                     int norm2d, const cf_decode_out_t* out, void* ws, size_t ws_bytes, void* stream) {
+    g_launches = 0;
+    if (int rc = check_decode_args(heads, out)) return rc;
+    if (int rc = check_dims(B, C, H, W)) return rc;
+    if (int rc = check_k(K, H, W)) return rc;
+    Plan plan;
+    if (!make_plan(C, H, W, K, &plan)) return fail(CF_E_SHAPE, "decode: unsupported map geometry %dx%d", H, W);
+    Workspace w;
+    const size_t need = workspace_layout(B, C, H, W, K, plan, ws, &w);
+    if (int rc = check_ws(ws, ws_bytes, need)) return rc;
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    int n = 0;
+    CF_CUDA(launch_peak_select(heads->heatmap, B, C, H, W, K, LIST_NMS, plan, w, st, &n), "peak_select");
+    MergeJob job;
+    memset(&job, 0, sizeof(job));
+    job.epilogue = EPI_DECODE;
+    job.dec.heads = *heads;
+    job.dec.out = *out;
+    job.dec.out_h = out_h;
+    job.dec.out_w = out_w;
+    job.dec.norm2d = norm2d;
+    CF_CUDA(launch_merge(heads->heatmap, B, C, H, W, K, plan, w, nullptr, &job, st, &n), "merge");
+    g_launches = n;
+    return 0;
+}
+
+int cf_fusion_stage(const float* heat, const float* wh, const float* depth, const float* dim, const float* rot,
+                    const float* pc_dep, const float* calib, int B, int C, int H, int W, int K, float max_pc_dist,
+                    float* pc_hm, int32_t* assoc, float* thr, int64_t* inds, const cf_decode_heads_t* dec_heads,
+                    int out_h, int out_w, int norm2d, const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes,
+                    void* stream) {
+    g_launches = 0;
+    if (int rc = check_frustum_args(heat, wh, depth, dim, rot, pc_dep, calib, pc_hm)) return rc;
+    const bool with_decode = dec_heads != nullptr;
+    if (with_decode) {
+        if (int rc = check_decode_args(dec_heads, dec_out)) return rc;
+        if (dec_heads->heatmap != heat)
+            return fail(CF_E_NULL, "cf_fusion_stage: decode heatmap must be the frustum heatmap");
+    }
+    if (int rc = check_dims(B, C, H, W)) return rc;
+    if (int rc = check_k(K, H, W)) return rc;
+    Plan plan;
+    if (!make_plan(C, H, W, K, &plan)) return fail(CF_E_SHAPE, "frustum: unsupported map geometry %dx%d", H, W);
+    Workspace w;
+    const size_t need = workspace_layout(B, C, H, W, K, plan, ws, &w);
+    if (int rc = check_ws(ws, ws_bytes, need)) return rc;
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    int n = 0;
+    CF_CUDA(launch_peak_select(heat, B, C, H, W, K, with_decode ? (LIST_RAW | LIST_NMS) : LIST_RAW, plan, w, st, &n),
+            "peak_select");
+    MergeJob fj, dj;
+    memset(&fj, 0, sizeof(fj));
+    memset(&dj, 0, sizeof(dj));
+    fj.epilogue = EPI_FRUSTUM;
+    fj.fh = FrustumHeads{wh, depth, dim, rot, calib};
+    fj.fo = FrustumOut{thr, inds};
+    if (with_decode) {
+        dj.epilogue = EPI_DECODE;
+        dj.dec.heads = *dec_heads;
+        dj.dec.out = *dec_out;
+        dj.dec.out_h = out_h;
+        dj.dec.out_w = out_w;
+        dj.dec.norm2d = norm2d;
+    }
+    CF_CUDA(launch_merge(heat, B, C, H, W, K, plan, w, &fj, with_decode ? &dj : nullptr, st, &n), "merge");
+    CF_CUDA(launch_assoc(pc_dep, B, H, W, K, max_pc_dist, w, assoc, st, &n), "assoc");
+    CF_CUDA(launch_paint(w.recs, K, K, nullptr, B, H, W, pc_hm, nullptr, st, &n), "paint");
+    g_launches = n;
+    return 0;
+}
+
+int cf_pc_dep_to_hm_single(float* pc_hm, const float* pc_dep, int H, int W, const float* depth, const float* bbox,
+                           const float* thr, float max_pc_dist, int32_t* assoc, void* stream) {
+    g_launches = 0;
+    if (!pc_hm || !pc_dep || !depth || !bbox || !thr) return fail(CF_E_NULL, "cf_pc_dep_to_hm_single: NULL pointer");
+    if (H < 1 || W < 1 || (long long)H * W >= (1ll << 31)) return fail(CF_E_SHAPE, "cf_pc_dep_to_hm_single: bad shape");
+    int n = 0;
+    CF_CUDA(launch_pc2hm_single(pc_hm, pc_dep, H, W, depth, bbox, thr, max_pc_dist, assoc, (cudaStream_t)stream, &n),
+            "pc2hm_single");
+    g_launches = n;
+    return 0;
+}
+
+int cf_radar_pillars(const double* points, const int32_t* counts, int B, int Nmax, const double* cam,
+                     const double* calib, const double* A, int img_w, int img_h, int H, int W,
+                     const double* pillar_dims_host, double max_dist, double z_offset, float* pc_dep, int32_t* owner,
+                     void* ws, size_t ws_bytes, void* stream) {
+    g_launches = 0;
+    if (!counts || !cam || !calib || !A || !pillar_dims_host || !pc_dep || (Nmax > 0 && !points))
+        return fail(CF_E_NULL, "cf_radar_pillars: NULL pointer");
+    if (B < 0 || Nmax < 0 || H < 1 || W < 1 || H > 32767 || W > 32767)
+        return fail(CF_E_SHAPE, "cf_radar_pillars: bad shape");
+    const size_t need = (size_t)B * Nmax * sizeof(PaintRec);
+    if (need) {
+        if (int rc = check_ws(ws, ws_bytes, need)) return rc;
+    }
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    int n = 0;
+    CF_CUDA(launch_pillar_rects(points, counts, B, Nmax, cam, calib, A, img_w, img_h, H, W, pillar_dims_host[0],
+                                pillar_dims_host[1], pillar_dims_host[2], max_dist, z_offset, (PaintRec*)ws, st, &n),
+            "pillar_rects");
+    CF_CUDA(launch_paint((const PaintRec*)ws, Nmax, Nmax, nullptr, B, H, W, pc_dep, owner, st, &n), "paint");
+    g_launches = n;
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,450 @@
+// frustum.cu -- per-ROI nearest-depth radar association and the ordered, atomic-free-in-HBM paint of the
+// pc_hm / pc_dep maps; plus the small stand-alone geometry kernels.
+//
+// Replaces (reference, src/lib/): utils/pointcloud.py:383-392 (the B x K Python loop) and :397-481
+// cvtPcDepthToHeatmap; :195-211 get_alpha; :299-328 getDistanceThresh; the pillar loop of
+// dataset/generic_dataset.py:798-826 with dataset/datasets/nuscenes.py:234-263 drawPcHeat.
+//
+// The reference paints detection after detection, later ones overwriting earlier ones.  Equivalent
+// parallel form used here: association per (frame, detection) is independent (one warp each, warp-shuffle
+// lexicographic (depth, pixel) minimum over the ROI); the paint is "every pixel takes the covering record
+// with the LARGEST index", resolved in shared memory (atomicMax on a per-band owner map), after which
+// every output pixel is written to HBM exactly once, coalesced, zeros included.
+#include <math_constants.h>
+
+#include "geometry.cuh"
+#include "kernels.cuh"
+
+namespace cf {
+
+// -----------------------------------------------------------------------------------------------------
+// association: one warp per detection
+// -----------------------------------------------------------------------------------------------------
+constexpr int AW = 8;  // warps (detections) per CTA
+
+struct RoiMatch {
+    bool found;
+    uint32_t pix;  // flat y*W+x of the matched pc_dep pixel
+    float v;       // its depth
+};
+
+// ROI + threshold test + first-minimum search of cvtPcDepthToHeatmap (pointcloud.py:424-461), executed by
+// NT cooperating threads (lane `t` of NT); the caller reduces `best` across them.
+__device__ __forceinline__ unsigned long long roi_scan(const float* __restrict__ dep, int H, int W, float x1, float y1,
+                                                       float x2, float y2, float depth, float thr, int t, int NT) {
+    int ya, yb, xa, xb;
+    pyslice((long long)floorf(y1), (long long)ceilf(y2) + 1, H, ya, yb);
+    pyslice((long long)floorf(x1), (long long)ceilf(x2) + 1, W, xa, xb);
+    const float hi = __fadd_rn(depth, thr);
+    float lo = __fsub_rn(depth, thr);
+    if (!(lo > 0.0f)) lo = 0.0f;  // python max(0, t)
+    unsigned long long best = ~0ull;
+    if (ya < yb && xa < xb) {
+        const int w = xb - xa;
+        const int n = (yb - ya) * w;
+        for (int i = t; i < n; i += NT) {
+            const int ry = i / w;
+            const int yy = ya + ry, xx = xa + (i - ry * w);
+            const float v = __ldg(dep + (size_t)yy * W + xx);
+            if (v != 0.0f && v < hi && v > lo) {  // v > lo >= 0: positive, so the bit pattern orders like the value
+                const unsigned long long key =
+                    ((unsigned long long)__float_as_uint(v) << 32) | (unsigned long long)(uint32_t)(yy * W + xx);
+                best = key < best ? key : best;
+            }
+        }
+    }
+    return best;
+}
+
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        const unsigned long long o = __shfl_xor_sync(FULL, v, off);
+        v = o < v ? o : v;
+    }
+    return v;
+}
+
+// paint window of cvtPcDepthToHeatmap (pointcloud.py:468-481): rows h_min:h_max+1, cols w_min:w_max+1+1
+__device__ __forceinline__ void paint_window(float x1, float y1, float x2, float y2, int H, int W, int& ra, int& rb,
+                                             int& ca, int& cb) {
+    const float cx = __fdiv_rn(__fadd_rn(x1, x2), 2.0f), cy = __fdiv_rn(__fadd_rn(y1, y2), 2.0f);
+    const float hw_ = __fdiv_rn(__fmul_rn(0.3f, __fsub_rn(x2, x1)), 2.0f);
+    const float hh_ = __fdiv_rn(__fmul_rn(0.3f, __fsub_rn(y2, y1)), 2.0f);
+    const long long wmin = (long long)__fsub_rn(cx, hw_), wmax = (long long)__fadd_rn(cx, hw_);  // int(): toward 0
+    const long long hmin = (long long)__fsub_rn(cy, hh_), hmax = (long long)__fadd_rn(cy, hh_);
+    pyslice(hmin, hmax + 1, H, ra, rb);
+    pyslice(wmin, wmax + 2, W, ca, cb);
+}
+
+__global__ void __launch_bounds__(AW * 32) assoc_kernel(const float* __restrict__ pc_dep, int H, int W, int K,
+                                                        float max_pc_dist, const DetParam* __restrict__ det,
+                                                        PaintRec* __restrict__ recs, int32_t* __restrict__ assoc) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int k = blockIdx.x * AW + warp;
+    const int b = blockIdx.y;
+    if (k >= K) return;
+    const size_t HW = (size_t)H * W;
+    const size_t o = (size_t)b * K + k;
+    const DetParam d = det[o];
+    const float* dep = pc_dep + (size_t)b * 3 * HW;
+    const unsigned long long best =
+        warp_min_u64(roi_scan(dep, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32));
+    if (lane == 0) {
+        PaintRec r;
+        r.ra = r.rb = r.ca = r.cb = 0;
+        r.v0 = r.v1 = r.v2 = 0.0f;
+        r.pad_ = r.pad2_ = 0;
+        int32_t a = -1;
+        if (best != ~0ull) {
+            const uint32_t mp = (uint32_t)best;
+            a = (int32_t)mp;
+            r.v0 = __fdiv_rn(__uint_as_float((uint32_t)(best >> 32)), max_pc_dist);  // :462-466
+            r.v1 = __ldg(dep + HW + mp);
+            r.v2 = __ldg(dep + 2 * HW + mp);
+            int ra, rb, ca, cb;
+            paint_window(d.x1, d.y1, d.x2, d.y2, H, W, ra, rb, ca, cb);
+            if (ra < rb && ca < cb) {
+                r.ra = (int16_t)ra;
+                r.rb = (int16_t)rb;
+                r.ca = (int16_t)ca;
+                r.cb = (int16_t)cb;
+            }
+        }
+        recs[o] = r;
+        if (assoc) assoc[o] = a;
+    }
+}
+
+cudaError_t launch_assoc(const float* pc_dep, int B, int H, int W, int K, float max_pc_dist, const Workspace& ws,
+                         int32_t* assoc, cudaStream_t st, int* launches) {
+    assoc_kernel<<<dim3((K + AW - 1) / AW, B), AW * 32, 0, st>>>(pc_dep, H, W, K, max_pc_dist, ws.det, ws.recs,
+                                                                  assoc);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) ++*launches;
+    return e;
+}
+
+// -----------------------------------------------------------------------------------------------------
+// ordered rectangle paint: out (B,3,H,W) written completely; largest record index wins per pixel
+// -----------------------------------------------------------------------------------------------------
+constexpr int PT = 256;
+
+__global__ void __launch_bounds__(PT) paint_kernel(const PaintRec* __restrict__ recs, int n_max, int rec_stride,
+                                                   const int32_t* __restrict__ counts, int H, int W, int rows_per_cta,
+                                                   float* __restrict__ out, int32_t* __restrict__ owner_out) {
+    extern __shared__ int sown[];  // rows_per_cta x W owner indices
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = blockIdx.y;
+    const int y0 = blockIdx.x * rows_per_cta;
+    const int y1 = min(H, y0 + rows_per_cta);
+    const int npx = (y1 - y0) * W;
+    int n = n_max;
+    if (counts) n = min(n_max, counts[b]);
+    for (int i = tid; i < npx; i += PT) sown[i] = -1;
+    __syncthreads();
+
+    const PaintRec* fr = recs + (size_t)b * rec_stride;
+    for (int base = warp * 32; base < n; base += (PT / 32) * 32) {
+        const int k = base + lane;
+        int ra = 0, rb = 0, ca = 0, cb = 0;
+        if (k < n) {
+            const short4 q = __ldg(reinterpret_cast<const short4*>(fr + k));
+            ra = q.x;
+            rb = q.y;
+            ca = q.z;
+            cb = q.w;
+        }
+        const bool hit = rb > ra && cb > ca && ra < y1 && rb > y0;
+        uint32_t m = __ballot_sync(FULL, hit);
+        while (m) {
+            const int bit = __ffs(m) - 1;
+            m &= m - 1;
+            const int qa = max(__shfl_sync(FULL, ra, bit), y0), qb = min(__shfl_sync(FULL, rb, bit), y1);
+            const int xa = __shfl_sync(FULL, ca, bit), xb = __shfl_sync(FULL, cb, bit);
+            const int w = xb - xa;
+            const int cnt = (qb - qa) * w;
+            for (int t = lane; t < cnt; t += 32) {
+                const int ry = t / w;
+                atomicMax(&sown[(qa - y0 + ry) * W + xa + (t - ry * w)], base + bit);
+            }
+        }
+    }
+    __syncthreads();
+
+    const size_t HW = (size_t)H * W;
+    float* o0 = out + ((size_t)b * 3) * HW + (size_t)y0 * W;
+    int32_t* oo = owner_out ? owner_out + (size_t)b * HW + (size_t)y0 * W : nullptr;
+    const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0) &&
+                     (!owner_out || (reinterpret_cast<uintptr_t>(owner_out) & 15u) == 0);
+    if (vec) {
+        for (int i = tid * 4; i < npx; i += PT * 4) {
+            const int4 ow = *reinterpret_cast<const int4*>(sown + i);
+            const int os[4] = {ow.x, ow.y, ow.z, ow.w};
+            float v[3][4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                v[0][j] = v[1][j] = v[2][j] = 0.0f;
+                if (os[j] >= 0) {
+                    const PaintRec* r = fr + os[j];
+                    v[0][j] = __ldg(&r->v0);
+                    v[1][j] = __ldg(&r->v1);
+                    v[2][j] = __ldg(&r->v2);
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+                *reinterpret_cast<float4*>(o0 + c * HW + i) = make_float4(v[c][0], v[c][1], v[c][2], v[c][3]);
+            if (oo) *reinterpret_cast<int4*>(oo + i) = ow;
+        }
+    } else {
+        for (int i = tid; i < npx; i += PT) {
+            const int ow = sown[i];
+            float v0 = 0.0f, v1 = 0.0f, v2 = 0.0f;
+            if (ow >= 0) {
+                const PaintRec* r = fr + ow;
+                v0 = __ldg(&r->v0);
+                v1 = __ldg(&r->v1);
+                v2 = __ldg(&r->v2);
+            }
+            o0[i] = v0;
+            o0[HW + i] = v1;
+            o0[2 * HW + i] = v2;
+            if (oo) oo[i] = ow;
+        }
+    }
+}
+
+cudaError_t launch_paint(const PaintRec* recs, int n_per_frame, int rec_stride, const int32_t* counts, int B, int H,
+                         int W, float* out, int32_t* owner, cudaStream_t st, int* launches) {
+    // bands: enough CTAs to cover the chip a few times over, each band's owner map in shared memory
+    int rows = 16;
+    while (rows > 1 && (long long)B * ((H + rows - 1) / rows) < 2 * 148) rows >>= 1;
+    while ((size_t)rows * W * sizeof(int) > 96 * 1024 && rows > 1) rows >>= 1;
+    const size_t smem = (size_t)rows * W * sizeof(int);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(paint_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    paint_kernel<<<dim3((H + rows - 1) / rows, B), PT, smem, st>>>(recs, n_per_frame, rec_stride, counts, H, W, rows,
+                                                                    out, owner);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) ++*launches;
+    return e;
+}
+
+// -----------------------------------------------------------------------------------------------------
+// cvtPcDepthToHeatmap, one detection, in place                      reference pointcloud.py:397-481
+// -----------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) pc2hm_single_kernel(float* __restrict__ pc_hm, const float* __restrict__ pc_dep,
+                                                           int H, int W, const float* __restrict__ depth,
+                                                           const float* __restrict__ bbox,
+                                                           const float* __restrict__ thr, float max_pc_dist,
+                                                           int32_t* __restrict__ assoc) {
+    __shared__ unsigned long long wbest[8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const size_t HW = (size_t)H * W;
+    const float x1 = bbox[0], y1 = bbox[1], x2 = bbox[2], y2 = bbox[3];
+    unsigned long long best = warp_min_u64(roi_scan(pc_dep, H, W, x1, y1, x2, y2, depth[0], thr[0], tid, 256));
+    if (lane == 0) wbest[warp] = best;
+    __syncthreads();
+    best = wbest[0];
+#pragma unroll
+    for (int i = 1; i < 8; ++i) best = wbest[i] < best ? wbest[i] : best;
+    if (best == ~0ull) {
+        if (tid == 0 && assoc) assoc[0] = -1;
+        return;
+    }
+    const uint32_t mp = (uint32_t)best;
+    if (tid == 0 && assoc) assoc[0] = (int32_t)mp;
+    const float v0 = __fdiv_rn(__uint_as_float((uint32_t)(best >> 32)), max_pc_dist);
+    const float v1 = pc_dep[HW + mp], v2 = pc_dep[2 * HW + mp];
+    int ra, rb, ca, cb;
+    paint_window(x1, y1, x2, y2, H, W, ra, rb, ca, cb);
+    if (ra >= rb || ca >= cb) return;
+    const int w = cb - ca, n = (rb - ra) * w;
+    for (int i = tid; i < n; i += 256) {
+        const int ry = i / w;
+        const size_t p = (size_t)(ra + ry) * W + ca + (i - ry * w);
+        pc_hm[p] = v0;
+        pc_hm[HW + p] = v1;
+        pc_hm[2 * HW + p] = v2;
+    }
+}
+
+cudaError_t launch_pc2hm_single(float* pc_hm, const float* pc_dep, int H, int W, const float* depth,
+                                const float* bbox, const float* thr, float max_pc_dist, int32_t* assoc,
+                                cudaStream_t st, int* launches) {
+    pc2hm_single_kernel<<<1, 256, 0, st>>>(pc_hm, pc_dep, H, W, depth, bbox, thr, max_pc_dist, assoc);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) ++*launches;
+    return e;
+}
+
+// -----------------------------------------------------------------------------------------------------
+// get_alpha / getDistanceThresh as stand-alone ops
+// -----------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) alpha_kernel(const float* __restrict__ rot, long long n,
+                                                    float* __restrict__ alpha) {
+    const long long i = blockIdx.x * 128ll + threadIdx.x;
+    if (i >= n) return;
+    float r[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r[j] = rot[8 * i + j];
+    alpha[i] = get_alpha(r);
+}
+
+cudaError_t launch_alpha(const float* rot, int64_t n, float* alpha, cudaStream_t st, int* launches) {
+    if (n == 0) return cudaSuccess;
+    alpha_kernel<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(rot, (long long)n, alpha);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) ++*launches;
+    return e;
+}
+
+__global__ void __launch_bounds__(128) dist_thresh_kernel(const float* __restrict__ calib,
+                                                          const float* __restrict__ center,
+                                                          const float* __restrict__ dim,
+                                                          const float* __restrict__ alpha, int B, int K,
+                                                          float* __restrict__ thr) {
+    const int i = blockIdx.x * 128 + threadIdx.x;
+    if (i >= B * K) return;
+    const int b = i / K;
+    float cal[3] = {calib[12 * b + 0], calib[12 * b + 1], calib[12 * b + 2]};
+    float dm[3] = {dim[3 * i], dim[3 * i + 1], dim[3 * i + 2]};
+    thr[i] = dist_thresh_one(cal, center[2 * i], dm, alpha[i]);
+}
+
+cudaError_t launch_dist_thresh(const float* calib, const float* center, const float* dim, const float* alpha, int B,
+                               int K, float* thr, cudaStream_t st, int* launches) {
+    if (B * K == 0) return cudaSuccess;
+    dist_thresh_kernel<<<(B * K + 127) / 128, 128, 0, st>>>(calib, center, dim, alpha, B, K, thr);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) ++*launches;
+    return e;
+}
+
+// -----------------------------------------------------------------------------------------------------
+// radar pillar rectangles: one thread per point, fp64 exactly like the NumPy reference
+//   loadRadarPointCloud filters   dataset/datasets/nuscenes.py:172-205
+//   map_pointcloud_to_image       utils/pointcloud.py:17-49 (+ devkit view_points)
+//   transformPointCloud           dataset/generic_dataset.py:830-867
+//   getPcPillarsSize              dataset/generic_dataset.py:869-942 (get3dBox / project3DPoints, ddd.py:8-55)
+//   pillar box + np.round         dataset/generic_dataset.py:798-826
+// -----------------------------------------------------------------------------------------------------
+struct PillarParams {
+    const double *points, *cam, *calib, *A;
+    const int32_t* counts;
+    int B, Nmax, img_w, img_h, H, W;
+    double ox, oy, oz, max_dist, z_offset;
+    PaintRec* recs;
+};
+
+__device__ __forceinline__ double dot3(double a0, double x, double a1, double y, double a2, double z) {
+    return __dadd_rn(__dadd_rn(__dmul_rn(a0, x), __dmul_rn(a1, y)), __dmul_rn(a2, z));
+}
+
+__global__ void __launch_bounds__(128) pillar_rects_kernel(const PillarParams p) {
+    const int i = blockIdx.x * 128 + threadIdx.x;
+    const int b = blockIdx.y;
+    if (i >= p.Nmax) return;
+    PaintRec r;
+    r.ra = r.rb = r.ca = r.cb = 0;
+    r.v0 = r.v1 = r.v2 = 0.0f;
+    r.pad_ = r.pad2_ = 0;
+    PaintRec* dst = p.recs + (size_t)b * p.Nmax + i;
+    if (i >= p.counts[b]) {
+        *dst = r;
+        return;
+    }
+    const double* pt = p.points + ((size_t)b * p.Nmax + i) * 5;
+    const double* Kc = p.cam + 9 * (size_t)b;
+    const double* P = p.calib + 12 * (size_t)b;
+    const double* Ab = p.A + 6 * (size_t)b;
+    const double X = pt[0], Z = pt[2];
+    double Y = pt[1];
+    const int W = p.W, H = p.H;
+    bool ok = !(p.max_dist > 0 && !(Z <= p.max_dist));
+    Y = __dsub_rn(Y, p.z_offset);
+    const double uh = dot3(Kc[0], X, Kc[1], Y, Kc[2], Z);
+    const double vh = dot3(Kc[3], X, Kc[4], Y, Kc[5], Z);
+    const double zh = dot3(Kc[6], X, Kc[7], Y, Kc[8], Z);
+    const double u = uh / zh, v = vh / zh;
+    ok = ok && (Z > 0 && u > 1 && u < p.img_w - 1 && v > 1 && v < p.img_h - 1);
+    const double up = __dadd_rn(__dadd_rn(__dmul_rn(Ab[0], u), __dmul_rn(Ab[1], v)), Ab[2]);
+    const double vp = __dadd_rn(__dadd_rn(__dmul_rn(Ab[3], u), __dmul_rn(Ab[4], v)), Ab[5]);
+    ok = ok && (up < W && vp < H && 0 < up && 0 < vp);
+    if (ok) {
+        double umin = CUDART_INF, umax = -CUDART_INF, vmin = CUDART_INF, vmax = -CUDART_INF;
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const double cx = __dadd_rn(X, ((c >> 1) & 1) ? -p.ox : p.ox);
+            const double cy = __dadd_rn(Y, (c & 4) ? p.oy : 0.0);
+            const double cz = __dadd_rn(Z, (((c + 1) >> 1) & 1) ? -p.oz : p.oz);
+            const double q0 = __dadd_rn(dot3(P[0], cx, P[1], cy, P[2], cz), P[3]);
+            const double q1 = __dadd_rn(dot3(P[4], cx, P[5], cy, P[6], cz), P[7]);
+            const double q2 = __dadd_rn(dot3(P[8], cx, P[9], cy, P[10], cz), P[11]);
+            const double uu = q0 / q2, vv = q1 / q2;
+            const double ua = __dadd_rn(__dadd_rn(__dmul_rn(Ab[0], uu), __dmul_rn(Ab[1], vv)), Ab[2]);
+            const double va = __dadd_rn(__dadd_rn(__dmul_rn(Ab[3], uu), __dmul_rn(Ab[4], vv)), Ab[5]);
+            if (ua < umin) umin = ua;
+            if (ua > umax) umax = ua;
+            if (va < vmin) vmin = va;
+            if (va > vmax) vmax = va;
+        }
+        const double pw = __dsub_rn(umax, umin), ph = __dsub_rn(vmax, vmin);
+        double by1 = __dsub_rn(vp, ph);
+        if (!(by1 > 0)) by1 = 0;
+        double bx1 = __dsub_rn(up, pw / 2);
+        if (!(bx1 > 0)) bx1 = 0;
+        double bx2 = __dadd_rn(up, pw / 2);
+        if (!(bx2 < W)) bx2 = W;
+        long long y1 = (long long)rint(by1), y2 = (long long)rint(vp), x1 = (long long)rint(bx1),
+                  x2 = (long long)rint(bx2);
+        if (y2 > H) y2 = H;
+        if (x2 > W) x2 = W;
+        if (y1 < y2 && x1 < x2) {
+            r.ra = (int16_t)y1;
+            r.rb = (int16_t)y2;
+            r.ca = (int16_t)x1;
+            r.cb = (int16_t)x2;
+        }
+        r.v0 = (float)Z;
+        r.v1 = (float)pt[3];
+        r.v2 = (float)pt[4];
+    }
+    *dst = r;
+}
+
+cudaError_t launch_pillar_rects(const double* points, const int32_t* counts, int B, int Nmax, const double* cam,
+                                const double* calib, const double* A, int img_w, int img_h, int H, int W, double ph,
+                                double pw, double pl, double max_dist, double z_offset, PaintRec* recs,
+                                cudaStream_t st, int* launches) {
+    PillarParams p;
+    p.points = points;
+    p.cam = cam;
+    p.calib = calib;
+    p.A = A;
+    p.counts = counts;
+    p.B = B;
+    p.Nmax = Nmax;
+    p.img_w = img_w;
+    p.img_h = img_h;
+    p.H = H;
+    p.W = W;
+    // ddd.get3dBox -> pointcloud.get3DCorners NumPy branch: fp32 corner templates scaled by fp64 dims,
+    // i.e. the offsets are float32(0.5*l), float32(-h), float32(0.5*w)
+    p.ox = (double)(float)(0.5 * pl);
+    p.oy = (double)(float)(-1.0 * ph);
+    p.oz = (double)(float)(0.5 * pw);
+    p.max_dist = max_dist;
+    p.z_offset = z_offset;
+    p.recs = recs;
+    if (Nmax == 0) return cudaSuccess;
+    pillar_rects_kernel<<<dim3((Nmax + 127) / 128, B), 128, 0, st>>>(p);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) ++*launches;
+    return e;
+}
+
+}  // namespace cf

@@ -1,0 +1,155 @@
+/*
+ * cfd3d_b200.h -- C ABI of the B200-native CenterFusion fusion stage (libcfd3d_b200.so).
+ *
+ * One shared library, extern "C", plain pointers and sizes, no torch types.  Every pointer is a DEVICE
+ * pointer unless its name ends in `_host`.  All maps are fp32, NCHW, contiguous.  Every call is
+ * stream-ordered on `stream` (a cudaStream_t passed as void*), never allocates, never synchronises the
+ * host and keeps no global state other than a thread-local error string: the caller owns every buffer
+ * including the workspace (`cf_workspace_bytes`).  Return value: 0 = ok, >0 = the cudaError_t of a
+ * failed launch, <0 = argument error (CF_E_*); `cf_last_error()` describes the last failure.
+ *
+ * The reference (HengWeiBin/CenterFusionDetect3D) is pure Python and has no FFI; its boundary for this
+ * path is a set of Python callables.  Each entry point below names the reference callable it replaces
+ * (paths relative to the reference tree).  centerfusiondetect3d_b200/ops.py is the ctypes host side
+ * that restores the reference signatures on top of this ABI; INTEGRATION.md shows the binding.
+ */
+#ifndef CFD3D_B200_H
+#define CFD3D_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CF_API __attribute__((visibility("default")))
+
+enum {
+    CF_OK = 0,
+    CF_E_NULL = -1,      /* a required pointer is NULL */
+    CF_E_SHAPE = -2,     /* non-positive or unsupported dimension */
+    CF_E_K = -3,         /* K < 1, K > H*W (torch.topk would raise) or K > CF_MAX_K */
+    CF_E_WORKSPACE = -4, /* workspace missing, misaligned or smaller than cf_workspace_bytes() */
+    CF_E_ALIGN = -5,     /* a map pointer is not 4-byte aligned */
+    CF_E_RANGE = -6      /* index space does not fit 32 bits (C*H*W >= 2^31) */
+};
+
+#define CF_MAX_K 1024 /* largest K the selection kernels support (reference configs use 100 and 500) */
+
+CF_API int cf_version(void);
+CF_API const char* cf_last_error(void);
+
+/* Bytes of device workspace any entry point below needs for these dimensions (256-byte aligned base). */
+CF_API size_t cf_workspace_bytes(int B, int C, int H, int W, int K);
+
+/* ---- a1  nms(heatmap, kernel=3)                        src/lib/model/utils.py:112-128 ------------
+ * out = heat * (maxpool3x3(heat) == heat), -inf padding.  out must not alias heat. */
+CF_API int cf_nms(const float* heat, int B, int C, int H, int W, float* out, void* stream);
+
+/* ---- a2  topk(heatmap, K)                               src/lib/model/utils.py:6-38 ---------------
+ * Frame-wide top-K under the total order (score desc, class asc, flat index asc).  apply_nms != 0 selects
+ * on nms(heat) without materialising it (what fusionDecode does, src/lib/model/decode.py:38-39).
+ * Outputs (B,K), any may be NULL: scores f32, inds i64 in [0,H*W), classes i32, ys i64, xs i64. */
+CF_API int cf_peak_topk(const float* heat, int B, int C, int H, int W, int K, int apply_nms, float* scores,
+                        int64_t* inds, int32_t* classes, int64_t* ys, int64_t* xs, void* ws, size_t ws_bytes,
+                        void* stream);
+
+/* ---- a3  transposeAndGetFeature(feature, indices)       src/lib/model/utils.py:41-72 --------------
+ * out[b,m,c] = feat[b,c,inds[b,m]]  -- straight from NCHW, no transposed copy.  inds must lie in [0,HW). */
+CF_API int cf_gather_nchw(const float* feat, int B, int ch, int64_t HW, const int64_t* inds, int M, float* out,
+                          void* stream);
+
+/* ---- a4  get_alpha / getDistanceThresh                  src/lib/utils/pointcloud.py:195-328 -------
+ * rot (n,8) -> alpha (n);   calib (B,3,4), center (B,K,2), dim (B,K,3), alpha (B,K) -> thr (B,K). */
+CF_API int cf_get_alpha(const float* rot, int64_t n, float* alpha, void* stream);
+CF_API int cf_dist_thresh(const float* calib, const float* center, const float* dim, const float* alpha, int B,
+                          int K, float* thr, void* stream);
+
+/* ---- a7  getPcFrustumHeatmap(output, pc_dep, calib, config)   src/lib/utils/pointcloud.py:331-394 -
+ * heat (B,C,H,W) raw (no nms); wh (B,2,H,W); depth (B,1,H,W); dim (B,3,H,W); rot (B,8,H,W);
+ * pc_dep (B,3,H,W); calib (B,3,4).  Writes pc_hm (B,3,H,W) completely (zeros where nothing is painted).
+ * Optional outputs (NULL to skip): assoc (B,K) i32 = flat pixel y*W+x of the matched pc_dep pixel or -1;
+ * thr (B,K) distance thresholds; inds (B,K) i64 raw top-K indices. */
+CF_API int cf_frustum_pc_hm(const float* heat, const float* wh, const float* depth, const float* dim,
+                            const float* rot, const float* pc_dep, const float* calib, int B, int C, int H, int W,
+                            int K, float max_pc_dist, float* pc_hm, int32_t* assoc, float* thr, int64_t* inds,
+                            void* ws, size_t ws_bytes, void* stream);
+
+/* ---- a8  cvtPcDepthToHeatmap(pc_hm, pc_dep, depth, bbox, distanceThreshold, max_pc_dist)
+ *                                                               src/lib/utils/pointcloud.py:397-481 -
+ * One detection, IN PLACE on pc_hm (3,H,W).  depth (1), bbox (4) and thr (1) are device scalars (the
+ * reference passes tensors), so the call needs no host synchronisation.  assoc (1) i32 optional. */
+CF_API int cf_pc_dep_to_hm_single(float* pc_hm, const float* pc_dep, int H, int W, const float* depth,
+                                  const float* bbox, const float* thr, float max_pc_dist, int32_t* assoc,
+                                  void* stream);
+
+/* ---- a9  fusionDecode(outputs, outputSize, K, norm2d)   src/lib/model/decode.py:10-174 ------------
+ * Single pyramid layer.  Heads: any pointer except heatmap may be NULL (= key absent in the reference's
+ * dict).  `depth` is depth2 when the model has it, else depth (decode.py:101-110); `rot` likewise
+ * rotation2/rotation (:120-121) -- the host side resolves which to pass. */
+typedef struct {
+    const float* heatmap;      /* (B,C,H,W) */
+    const float* reg;          /* (B,2,H,W) or NULL */
+    const float* wh;           /* (B,2,H,W) or NULL */
+    const float* depth;        /* (B,1,H,W) or NULL */
+    const float* rot;          /* (B,8,H,W) or NULL */
+    const float* dim;          /* (B,3,H,W) or NULL */
+    const float* amodal;       /* (B,2,H,W) or NULL */
+    const float* nuscenes_att; /* (B,8,H,W) or NULL */
+    const float* velocity;     /* (B,3,H,W) or NULL */
+    const float* uncertainty;  /* (B,1,H,W) or NULL */
+} cf_decode_heads_t;
+
+typedef struct {
+    float* scores;       /* (B,K)   required */
+    float* class_ids;    /* (B,K)   required, class id as fp32 like the reference */
+    float* centers;      /* (B,K,2) required, normalised [x/W, y/H] */
+    float* bboxes;       /* (B,K,4) iff heads.wh */
+    float* depth;        /* (B,K,1) iff heads.depth */
+    float* rot;          /* (B,K,8) iff heads.rot */
+    float* dim;          /* (B,K,3) iff heads.dim */
+    float* amodal;       /* (B,K,2) iff heads.amodal */
+    float* nuscenes_att; /* (B,K,8) iff heads.nuscenes_att */
+    float* velocity;     /* (B,K,3) iff heads.velocity */
+    int64_t* inds;       /* (B,K)   optional: nms'd top-K flat indices */
+} cf_decode_out_t;
+
+CF_API int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W, int K, int out_h, int out_w,
+                            int norm2d, const cf_decode_out_t* out, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- a7 + a9 in one pass over the heat-map ------------------------------------------------------------
+ * What CenterFusionHead.forward (src/lib/model/networks/detectHeads.py:176-177) and the decode callers
+ * (src/lib/detector.py:414-424, src/lib/model/progressBar.py:96-101) compute between them, with the
+ * heat-map read once: the peak-select kernel emits the raw and the nms'd candidate lists together.
+ * Frustum inputs/outputs as in cf_frustum_pc_hm (frustum heads: wh, depth, dim, rot of the FIRST stage);
+ * decode heads/outputs as in cf_fusion_decode. */
+CF_API int cf_fusion_stage(const float* heat, const float* wh, const float* depth, const float* dim,
+                           const float* rot, const float* pc_dep, const float* calib, int B, int C, int H, int W,
+                           int K, float max_pc_dist, float* pc_hm, int32_t* assoc, float* thr, int64_t* inds,
+                           const cf_decode_heads_t* dec_heads, int out_h, int out_w, int norm2d,
+                           const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- a5 + a6  radar pillar expansion -> pc_dep -----------------------------------------------------------
+ * loadRadarPointCloud filters      src/lib/dataset/datasets/nuscenes.py:172-205
+ * map_pointcloud_to_image          src/lib/utils/pointcloud.py:17-49
+ * processPointCloud (pillars)      src/lib/dataset/generic_dataset.py:738-942
+ * drawPcHeat                       src/lib/dataset/datasets/nuscenes.py:234-263
+ * points (B,Nmax,5) fp64 [X right, Y down, Z forward, vx, vz] in the camera frame, each frame sorted
+ * ascending by Z by the caller (np.argsort in the reference is unstable: order is an input contract);
+ * counts (B) i32; cam (B,3,3) fp64 intrinsic; calib (B,3,4) fp64; A (B,2,3) fp64 output affine;
+ * pillar_dims_host: 3 doubles (h,w,l) on the HOST.  Writes pc_dep (B,3,H,W) fp32 completely; owner (B,H,W)
+ * i32 optional = index of the surviving point per pixel or -1. */
+CF_API size_t cf_pillars_workspace_bytes(int B, int Nmax);
+CF_API int cf_radar_pillars(const double* points, const int32_t* counts, int B, int Nmax, const double* cam,
+                            const double* calib, const double* A, int img_w, int img_h, int H, int W,
+                            const double* pillar_dims_host, double max_dist, double z_offset, float* pc_dep,
+                            int32_t* owner, void* ws, size_t ws_bytes, void* stream);
+
+/* Number of kernels the last successful call on this thread launched (bench.py's gpu_launches). */
+CF_API int cf_last_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CFD3D_B200_H */
