@@ -1,0 +1,498 @@
+#!/usr/bin/env python
+"""bench.py -- fusion-stage frames/s on N B200s (BASELINE.json metric), with the roofline of the dominant kernel,
+the end-to-end number through the public API from host buffers, and the host-CPU baseline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2|cfg3|cfg4|cfg5] [--impl native|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+One "step" = one pass of the fusion stage (getPcFrustumHeatmap + fusionDecode, one fused C-ABI call; cfg4 adds the
+radar pillar expansion) over one batch of B synthetic frames per GPU.  Frames are independent, so ranks own whole
+frames and the data path has no collective ("scaling": "weak": B frames per GPU at every N).
+
+Timing: CUDA events on the launching stream around exactly K steps, barrier + synchronize on both sides, max over
+ranks.  Cold-cache discipline: the step rotates through NSETS distinct resident input sets whose fully-read maps
+(heat-map + pc_dep) together exceed 2x the 126 MB L2, so no step finds its inputs in L2 ("l2": "rotating_inputs").
+The timed loop replays one CUDA graph per input set (4 kernels each); nothing is allocated or synchronised inside.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "fusion_stage_frames_per_s"
+UNIT = "frames/s"
+L2_BYTES = 126 * 1024 * 1024
+
+
+def algorithmic_bytes_per_frame(wl, with_pillars: bool) -> int:
+    """heat read + pc_dep read + pc_hm write + gathers (14 fwd + 29 decode ch) + 33 decoded floats
+    + calib; pillars add the pc_dep write and the fp64 points."""
+    HW = wl.H * wl.W
+    b = 4 * HW * (wl.C + 3 + 3) + 4 * wl.K * (14 + 29) + 4 * wl.K * 33 + 48
+    if with_pillars:
+        b += 4 * HW * 3 + 8 * 5 * wl.n_radar
+    return b
+
+
+def peak_select_bytes_per_frame(wl) -> int:
+    """Dominant kernel (peak_select): reads the heat-map once, writes two K-candidate lists per (class, band)."""
+    return 4 * wl.H * wl.W * wl.C
+
+
+# --------------------------------------------------------------------------------------------------------
+# clocks
+# --------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index: int, period_s: float = 0.004):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        self.period = period_s
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:  # pragma: no cover
+            self.nv = None
+            self.err = repr(e)
+
+    _NAMES = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+              0x80: "hw_power_brake_slowdown", 0x2: "applications_clocks_setting", 0x100: "display_clock_setting"}
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                try:
+                    r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                for bit, name in self._NAMES.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def __enter__(self):
+        if self.nv is not None:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._thr is not None:
+            self._thr.join()
+
+    def merge(self, other: "ClockSampler"):
+        self.samples += other.samples
+        self.reasons |= other.reasons
+
+    def summary(self) -> dict:
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# --------------------------------------------------------------------------------------------------------
+# inputs
+# --------------------------------------------------------------------------------------------------------
+def make_host_inputs(wl, B: int, seed: int):
+    """One batch of synthetic stage inputs (NumPy); pc_dep painted from the radar points by the oracle's pillar code
+    (input generation, not the measured path)."""
+    from centerfusiondetect3d_b200 import synthetic as syn
+    from oracle import binding as ob
+
+    gen_B = min(B, 8)  # generate 8 distinct frames, tile to B (values do not affect traffic; addresses do)
+    inp = syn.make_inputs(wl, seed=seed, B=gen_B)
+    ob.set_threads(min(ob.max_threads(), 16))
+    pc_dep, _ = ob.radar_pillars(inp["radar_points"], inp["radar_counts"], inp["cam"], inp["calib64"], inp["A_out"],
+                                 (wl.img_w, wl.img_h), (wl.H, wl.W), wl.pillar_dims, wl.max_pc_dist, want_owner=False)
+    inp["pc_dep"] = pc_dep
+    if gen_B < B:
+        reps = (B + gen_B - 1) // gen_B
+        for k, v in list(inp.items()):
+            if isinstance(v, np.ndarray) and v.ndim >= 1 and v.shape[0] == gen_B:
+                inp[k] = np.ascontiguousarray(np.concatenate([np.roll(v, r, axis=0) for r in range(reps)], axis=0)[:B])
+    return inp
+
+
+STAGE_KEYS = ("heatmap", "reg", "widthHeight", "depth", "depth2", "rotation", "rotation2", "dimension",
+              "amodal_offset", "nuscenes_att", "velocity")
+PILLAR_KEYS = ("radar_points", "radar_counts", "cam", "calib64", "A_out")
+
+
+class Cfg:
+    def __init__(self, K, max_pc_dist):
+        self.MODEL = type("M", (), {"K": K})()
+        self.DATASET = type("D", (), {"MAX_PC_DIST": max_pc_dist})()
+
+
+def run_stage(ops, wl, dev_in: dict, cfg):
+    """The measured step through the public API.  Returns (pc_hm, ret, launches)."""
+    n = 0
+    if wl.with_pillars:
+        pc_dep = ops.radar_to_pc_dep(dev_in["radar_points"], dev_in["radar_counts"], dev_in["cam"], dev_in["calib64"],
+                                     dev_in["A_out"], (wl.H, wl.W), (wl.img_w, wl.img_h), wl.pillar_dims,
+                                     wl.max_pc_dist)
+        n += ops.last_launch_count()
+    else:
+        pc_dep = dev_in["pc_dep"]
+    heads = {k: dev_in[k] for k in STAGE_KEYS}  # fresh dict: fusionDecode renames rotation2 -> rotation in it
+    pc_hm, ret = ops.fusion_stage(heads, pc_dep, dev_in["calib"], cfg)
+    n += ops.last_launch_count()
+    return pc_hm, ret, n
+
+
+# --------------------------------------------------------------------------------------------------------
+# CPU baseline (oracle port of the reference's algorithm; the reference itself is Python and cannot travel)
+# --------------------------------------------------------------------------------------------------------
+def cpu_stage(ob, wl, inp):
+    if wl.with_pillars:
+        pc_dep, _ = ob.radar_pillars(inp["radar_points"], inp["radar_counts"], inp["cam"], inp["calib64"],
+                                     inp["A_out"], (wl.img_w, wl.img_h), (wl.H, wl.W), wl.pillar_dims, wl.max_pc_dist,
+                                     want_owner=False)
+    else:
+        pc_dep = inp["pc_dep"]
+    ob.frustum_pc_hm(inp["heatmap"], inp["widthHeight"], inp["depth"], inp["dimension"], inp["rotation"], pc_dep,
+                     inp["calib"], wl.K, wl.max_pc_dist)
+    ob.fusion_decode({k: inp[k] for k in STAGE_KEYS}, (wl.H, wl.W), wl.K)
+
+
+def cpu_baseline(wl, inp, B, budget_s=12.0, min_reps=2):
+    from oracle import binding as ob
+
+    cores = os.cpu_count() or 1
+    threads = max(1, min(cores, ob.max_threads()))
+    ob.set_threads(threads)
+    cpu_stage(ob, wl, inp)  # warm-up
+    t0 = time.perf_counter()
+    reps = 0
+    while reps < min_reps or (time.perf_counter() - t0) < budget_s:
+        cpu_stage(ob, wl, inp)
+        reps += 1
+        if reps >= 10000:
+            break
+    dt = time.perf_counter() - t0
+    return {"value": B * reps / dt, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "%d passes over one %d-frame batch of %s (oracle/cfd3d_oracle.c, OpenMP over frames x classes, "
+                      "%.1f s)" % (reps, B, wl.name, dt)}
+
+
+def run_reference_arm(args, wl, B):
+    """--impl reference: the reference's CPU algorithm (oracle port) on the host cores, same config / metric."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import binding as ob
+
+    ob.build()
+    inp = make_host_inputs(wl, B, seed=1234)
+    cores = os.cpu_count() or 1
+    threads = max(1, min(cores, ob.max_threads()))
+    ob.set_threads(threads)
+    for _ in range(max(1, min(args.warmup, 3))):
+        cpu_stage(ob, wl, inp)
+    steps = args.steps
+    # bounded: never let the reference arm run longer than ~3 minutes whatever --steps says
+    t_probe = time.perf_counter()
+    cpu_stage(ob, wl, inp)
+    per = time.perf_counter() - t_probe
+    steps_eff = max(1, min(steps, int(150.0 / max(per, 1e-6))))
+    t0 = time.perf_counter()
+    for _ in range(steps_eff):
+        cpu_stage(ob, wl, inp)
+    dt = time.perf_counter() - t0
+    val = B * steps_eff / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps_eff,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / steps_eff, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl.name, "frames_per_step": B, "K": wl.K, "map": [wl.H, wl.W], "radar_points": wl.n_radar,
+                   "note": "reference algorithm on host CPU cores (C/OpenMP port in oracle/; the Python reference "
+                           "cannot travel to the GPU box); rank 0 only"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": "%d passes over one %d-frame batch" % (steps_eff, B)},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# --------------------------------------------------------------------------------------------------------
+# native arm
+# --------------------------------------------------------------------------------------------------------
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg3", "cfg4", "cfg5"])
+    ap.add_argument("--batch", type=int, default=0, help="frames per GPU per step (default: the workload's)")
+    ap.add_argument("--e2e-steps", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-graph", action="store_true", help="launch through ctypes every step instead of graph replay")
+    args = ap.parse_args()
+
+    from centerfusiondetect3d_b200 import synthetic as syn
+
+    wl = syn.WORKLOADS[args.workload]
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    # frames per GPU per step: cfg2 = 32; cfg3 = 256 total on one GPU at N=1, 32/GPU at N=8; cfg5 = 8/GPU; cfg4 = 64
+    B = args.batch or {"cfg2": 32, "cfg3": 256 // max(world, 1) if world > 1 else 256, "cfg4": 64, "cfg5": 8}[args.workload]
+
+    if args.impl == "reference":
+        return run_reference_arm(args, wl, B)
+
+    import torch
+    import torch.distributed as dist
+
+    assert torch.cuda.is_available(), "bench.py (native arm) needs a CUDA device: there is no CPU fallback"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from centerfusiondetect3d_b200 import _lib, ops
+
+    cfg = Cfg(wl.K, wl.max_pc_dist)
+    host = make_host_inputs(wl, B, seed=1234 + rank)
+    keys = STAGE_KEYS + ("calib", "pc_dep") + (PILLAR_KEYS if wl.with_pillars else ())
+    fully_read = 4 * B * wl.H * wl.W * (wl.C + 3)
+    nsets = max(2, -(-2 * L2_BYTES // fully_read) + 1)
+    nsets = min(nsets, 24)
+    sets = []
+    for j in range(nsets):
+        sets.append({k: torch.from_numpy(np.ascontiguousarray(np.roll(host[k], j, axis=0))).to(dev) for k in keys})
+    torch.cuda.synchronize()
+
+    # -- correctness guard: the bench measures a path that agrees with the oracle on its own inputs (small sample) --
+    if rank == 0:
+        from oracle import binding as ob
+
+        nb = min(B, 2)
+        sub = {k: (v[:nb] if isinstance(v, np.ndarray) and v.ndim and v.shape[0] == B else v) for k, v in host.items()}
+        d_sub = {k: torch.from_numpy(np.ascontiguousarray(sub[k])).to(dev) for k in keys}
+        hm, ret, _ = run_stage(ops, wl, d_sub, cfg)
+        ob.set_threads(min(ob.max_threads(), 8))
+        hm_o = ob.frustum_pc_hm(sub["heatmap"], sub["widthHeight"], sub["depth"], sub["dimension"], sub["rotation"],
+                                sub["pc_dep"], sub["calib"], wl.K, wl.max_pc_dist)[0]
+        ret_o = ob.fusion_decode({k: sub[k] for k in STAGE_KEYS}, (wl.H, wl.W), wl.K)
+        torch.cuda.synchronize()
+        check_ok = bool(np.array_equal(hm.cpu().numpy(), hm_o)) and all(
+            np.array_equal(v.cpu().numpy(), ret_o[k]) for k, v in ret.items() if k != "scores") and bool(
+            np.array_equal(ret["scores"].cpu().numpy(), ret_o["scores"]))
+    else:
+        check_ok = True
+
+    # -- capture one CUDA graph per input set -----------------------------------------------------------------
+    launches_per_step = 0
+    stream = torch.cuda.Stream(device=dev)
+    graphs, outs = [], []
+    with torch.cuda.stream(stream):
+        for s in sets:  # eager warm-up (workspace allocation, kernel attribute setup)
+            _, _, launches_per_step = run_stage(ops, wl, s, cfg)
+        stream.synchronize()
+        if not args.no_graph:
+            for s in sets:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=stream):
+                    o = run_stage(ops, wl, s, cfg)
+                graphs.append(g)
+                outs.append(o)
+
+    def step(i):
+        if graphs:
+            graphs[i % nsets].replay()
+        else:
+            run_stage(ops, wl, sets[i % nsets], cfg)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        for i in range(max(args.warmup, 3)):
+            step(i)
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        clocks = ClockSampler(local)
+        with clocks:
+            ev0.record(stream)
+            for i in range(args.steps):
+                step(i)
+            ev1.record(stream)
+            barrier()
+        ms = ev0.elapsed_time(ev1)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    frames_total = B * world * args.steps
+    value = frames_total / (ms_max * 1e-3)
+
+    # -- roofline leg: the dominant kernel (peak_select) timed alone with CUDA events inside live steps -------------
+    roof = None
+    if rank == 0:
+        n_roof = min(args.steps, 200)
+        flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device=dev)
+        pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_roof)]
+        L = _lib.lib()
+        with torch.cuda.stream(stream):
+            for i, (a, b) in enumerate(pairs):
+                flush.fill_(i & 0xff)  # keeps the GPU busy while the launches queue up, and evicts L2
+                # events must exist before their handles are read
+                a.record(stream)
+                b.record(stream)
+                L.cf_set_kernel_events(0, a.cuda_event, b.cuda_event)
+                run_stage(ops, wl, sets[i % nsets], cfg)
+                L.cf_set_kernel_events(-1, None, None)
+            stream.synchronize()
+        durs = np.array([a.elapsed_time(b) for a, b in pairs]) * 1e-3
+        dur = float(np.mean(durs))
+        peaks = {}
+        pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        peak, peak_src = 6650.0, "fallback"
+        if os.path.isfile(pk_path):
+            try:
+                peaks = json.load(open(pk_path))
+                peak, peak_src = float(peaks["hbm_gbs"]), "measured"
+            except Exception:
+                pass
+        alg = peak_select_bytes_per_frame(wl) * B
+        ach = alg / dur / 1e9
+        stage_alg = algorithmic_bytes_per_frame(wl, wl.with_pillars) * B
+        stage_ach = stage_alg / (ms_max * 1e-3 / args.steps) / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.isfile(tpath):
+            try:
+                traffic = json.load(open(tpath)).get(wl.name, {}).get("peak_select_dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        roof = {"bound": "hbm", "kernel": "peak_select_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
+                "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": alg, "kernel_us": dur * 1e6, "kernel_us_min": float(durs.min()) * 1e6,
+                "launches_timed": n_roof,
+                "stage": {"algorithmic_bytes_per_step": stage_alg, "achieved": stage_ach, "frac": stage_ach / peak}}
+
+    # -- e2e: public API from pinned host buffers, H2D + compute + D2H inside the timed region --------------------
+    e2e_steps = args.e2e_steps or max(10, min(args.steps, 100))
+    pinned = {k: torch.from_numpy(np.ascontiguousarray(host[k])).pin_memory() for k in keys if not (
+        wl.with_pillars and k == "pc_dep")}
+    e_keys = list(pinned.keys())
+    h2d = sum(v.numel() * v.element_size() for v in pinned.values())
+    NBUF = 3
+    dbuf = [{k: torch.empty_like(pinned[k], device=dev) for k in e_keys} for _ in range(NBUF)]
+    for k in e_keys:
+        dbuf[0][k].copy_(pinned[k])
+    hm0, ret0, _ = run_stage(ops, wl, dbuf[0], cfg)
+    res_names = ["pc_hm"] + list(ret0.keys())
+    hout = [{n: torch.empty_like(tns, device="cpu").pin_memory() for n, tns in zip(res_names, [hm0] + list(ret0.values()))}
+            for _ in range(NBUF)]
+    d2h = sum(v.numel() * v.element_size() for v in hout[0].values())
+    s_in, s_cmp, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    ev_in = [torch.cuda.Event() for _ in range(NBUF)]
+    ev_cmp = [torch.cuda.Event() for _ in range(NBUF)]
+    ev_out = [torch.cuda.Event() for _ in range(NBUF)]
+    results = [None] * NBUF
+
+    def e2e_step(i):
+        j = i % NBUF
+        with torch.cuda.stream(s_in):
+            s_in.wait_event(ev_cmp[j])  # buffer j free again once its previous compute finished
+            for k in e_keys:
+                dbuf[j][k].copy_(pinned[k], non_blocking=True)
+            ev_in[j].record(s_in)
+        with torch.cuda.stream(s_cmp):
+            s_cmp.wait_event(ev_in[j])
+            s_cmp.wait_event(ev_out[j])
+            hm, ret, _ = run_stage(ops, wl, dbuf[j], cfg)
+            results[j] = (hm, ret)
+            ev_cmp[j].record(s_cmp)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(ev_cmp[j])
+            hout[j]["pc_hm"].copy_(hm, non_blocking=True)
+            for n, v in ret.items():
+                hout[j][n].copy_(v, non_blocking=True)
+            ev_out[j].record(s_out)
+
+    for i in range(3):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(s_in)
+    for i in range(e2e_steps):
+        e2e_step(i)
+    s_out.wait_stream(s_cmp)
+    s_out.wait_stream(s_in)
+    e1.record(s_out)
+    barrier()
+    e2e_ms = max(e0.elapsed_time(e1), 0.0)
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    e2e_ms = max(e2e_ms, 0.0)
+    t = torch.tensor([e2e_ms, wall_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms_max = float(t[0].item())
+    e2e_val = B * world * e2e_steps / (e2e_ms_max * 1e-3)
+
+    if rank == 0:
+        cpu = None if args.no_cpu or world > 1 else cpu_baseline(wl, host, B)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl.name, "frames_per_gpu_per_step": B, "global_frames_per_step": B * world,
+                       "K": wl.K, "classes": wl.C, "map": [wl.H, wl.W], "radar_points": wl.n_radar,
+                       "stage": ("radar_pillars + " if wl.with_pillars else "") + "getPcFrustumHeatmap + fusionDecode",
+                       "l2": "rotating_inputs", "input_sets": nsets, "cuda_graph": not args.no_graph,
+                       "parallelism": "frames sharded across ranks, no data-path collective"},
+            "clocks": clocks.summary(),
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "steps": e2e_steps, "ms_per_step": e2e_ms_max / e2e_steps, "wall_ms_per_step": float(t[1].item()) / e2e_steps,
+                    "how": "ops.fusion_stage from pinned host buffers; 3-deep pipeline over copy-in / compute / "
+                           "copy-out streams; every step copies all inputs H2D and pc_hm + detections D2H"},
+            "gpu_launches": launches_per_step * args.steps,
+            "launches_per_step": launches_per_step,
+            "roofline": roof,
+            "cpu_baseline": cpu,
+            "parity_check": check_ok,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0 if check_ok else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())

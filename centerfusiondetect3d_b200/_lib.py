@@ -1,0 +1,92 @@
+"""ctypes binding of libcfd3d_b200.so (include/cfd3d_b200.h).
+
+The library is the product: there is NO CPU or PyTorch fallback.  If the shared object is missing or a
+symbol is absent, importing this module's `lib()` raises; the build recipe is
+`python -m centerfusiondetect3d_b200.build` (nvcc, sm_100a).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcfd3d_b200.so")
+
+_vp = C.c_void_p
+
+
+class DecodeHeads(C.Structure):
+    """cf_decode_heads_t"""
+    _fields_ = [(n, _vp) for n in ("heatmap", "reg", "wh", "depth", "rot", "dim", "amodal", "nuscenes_att",
+                                   "velocity", "uncertainty")]
+
+
+class DecodeOut(C.Structure):
+    """cf_decode_out_t"""
+    _fields_ = [(n, _vp) for n in ("scores", "class_ids", "centers", "bboxes", "depth", "rot", "dim", "amodal",
+                                   "nuscenes_att", "velocity", "inds")]
+
+
+# every symbol include/cfd3d_b200.h declares: name -> (restype, argtypes)
+_I, _F, _D, _Z, _L = C.c_int, C.c_float, C.c_double, C.c_size_t, C.c_int64
+SYMBOLS = {
+    "cf_version": (_I, []),
+    "cf_last_error": (C.c_char_p, []),
+    "cf_last_launch_count": (_I, []),
+    "cf_set_kernel_events": (_I, [_I, _vp, _vp]),
+    "cf_workspace_bytes": (_Z, [_I] * 5),
+    "cf_pillars_workspace_bytes": (_Z, [_I, _I]),
+    "cf_nms": (_I, [_vp, _I, _I, _I, _I, _vp, _vp]),
+    "cf_peak_topk": (_I, [_vp, _I, _I, _I, _I, _I, _I, _vp, _vp, _vp, _vp, _vp, _vp, _Z, _vp]),
+    "cf_gather_nchw": (_I, [_vp, _I, _I, _L, _vp, _I, _vp, _vp]),
+    "cf_get_alpha": (_I, [_vp, _L, _vp, _vp]),
+    "cf_dist_thresh": (_I, [_vp, _vp, _vp, _vp, _I, _I, _vp, _vp]),
+    "cf_frustum_pc_hm": (_I, [_vp] * 7 + [_I] * 5 + [_F] + [_vp] * 4 + [_vp, _Z, _vp]),
+    "cf_pc_dep_to_hm_single": (_I, [_vp, _vp, _I, _I, _vp, _vp, _vp, _F, _vp, _vp]),
+    "cf_fusion_decode": (_I, [C.POINTER(DecodeHeads), _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(DecodeOut), _vp, _Z,
+                              _vp]),
+    "cf_fusion_stage": (_I, [_vp] * 7 + [_I] * 5 + [_F] + [_vp] * 4 + [C.POINTER(DecodeHeads), _I, _I, _I,
+                                                                       C.POINTER(DecodeOut), _vp, _Z, _vp]),
+    "cf_radar_pillars": (_I, [_vp, _vp, _I, _I, _vp, _vp, _vp, _I, _I, _I, _I, C.POINTER(_D), _D, _D, _vp, _vp, _vp,
+                              _Z, _vp]),
+}
+
+_lib = None
+
+
+class CudaLibraryMissing(ImportError):
+    pass
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise CudaLibraryMissing(
+                "%s not found: build it with `python -m centerfusiondetect3d_b200.build` "
+                "(there is no CPU fallback for the fusion stage)" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)  # AttributeError if the .so does not export what the header declares
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+class CfError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__("libcfd3d_b200: %s (code %d)" % (msg, code))
+        self.code = code
+
+
+def check(rc: int) -> None:
+    """Maps the ABI's return code to the exception the reference's torch code would raise."""
+    if rc == 0:
+        return
+    msg = lib().cf_last_error().decode("utf-8", "replace")
+    if rc == -3:  # CF_E_K: torch.topk raises RuntimeError("selected index k out of range")
+        raise RuntimeError(msg)
+    if rc < 0:
+        raise ValueError("libcfd3d_b200: %s (code %d)" % (msg, rc))
+    raise CfError(rc, msg)

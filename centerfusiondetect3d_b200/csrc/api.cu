@@ -12,6 +12,20 @@ using namespace cf;
 static thread_local char g_err[512] = "";
 static thread_local int g_launches = 0;
 
+// measurement hook (cf_set_kernel_events)
+static thread_local int g_ev_kernel = -1;
+static thread_local cudaEvent_t g_ev_start = nullptr, g_ev_stop = nullptr;
+struct EvScope {
+    bool on;
+    cudaStream_t st;
+    EvScope(int id, cudaStream_t s) : on(id == g_ev_kernel && g_ev_start && g_ev_stop), st(s) {
+        if (on) cudaEventRecord(g_ev_start, st);
+    }
+    ~EvScope() {
+        if (on) cudaEventRecord(g_ev_stop, st);
+    }
+};
+
 static int fail(int code, const char* fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
@@ -26,6 +40,16 @@ static int cuda_fail(cudaError_t e, const char* what) {
 #define CF_CUDA(call, what)                         \
     do {                                            \
         cudaError_t e__ = (call);                   \
+        if (e__ != cudaSuccess) return cuda_fail(e__, what); \
+    } while (0)
+// same, with the measurement hook around kernel `id`
+#define CF_KERNEL(id, st, call, what)               \
+    do {                                            \
+        cudaError_t e__;                            \
+        {                                           \
+            EvScope ev__(id, st);                   \
+            e__ = (call);                           \
+        }                                           \
         if (e__ != cudaSuccess) return cuda_fail(e__, what); \
     } while (0)
 
@@ -53,6 +77,17 @@ extern "C" {
 int cf_version(void) { return 100; }
 const char* cf_last_error(void) { return g_err; }
 int cf_last_launch_count(void) { return g_launches; }
+int cf_set_kernel_events(int kernel_id, void* ev_start, void* ev_stop) {
+    if (kernel_id < 0 || !ev_start || !ev_stop) {
+        g_ev_kernel = -1;
+        g_ev_start = g_ev_stop = nullptr;
+        return 0;
+    }
+    g_ev_kernel = kernel_id;
+    g_ev_start = (cudaEvent_t)ev_start;
+    g_ev_stop = (cudaEvent_t)ev_stop;
+    return 0;
+}
 
 size_t cf_workspace_bytes(int B, int C, int H, int W, int K) {
     Plan plan;
@@ -124,13 +159,12 @@ int cf_peak_topk(const float* heat, int B, int C, int H, int W, int K, int apply
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
     const int list = apply_nms ? LIST_NMS : LIST_RAW;
-    CF_CUDA(launch_peak_select(heat, B, C, H, W, K, list, plan, w, st, &n), "peak_select");
+    CF_KERNEL(CF_KERNEL_PEAK_SELECT, st, launch_peak_select(heat, B, C, H, W, K, list, plan, w, st, &n), "peak_select");
     MergeJob job;
     memset(&job, 0, sizeof(job));
     job.epilogue = EPI_TOPK;
     job.topk = TopkOut{scores, inds, classes, ys, xs};
-    CF_CUDA(launch_merge(heat, B, C, H, W, K, plan, w, apply_nms ? nullptr : &job, apply_nms ? &job : nullptr, st, &n),
-            "merge");
+    CF_KERNEL(CF_KERNEL_MERGE, st, launch_merge(heat, B, C, H, W, K, plan, w, apply_nms ? nullptr : &job, apply_nms ? &job : nullptr, st, &n), "merge");
     g_launches = n;
     return 0;
 }
@@ -177,7 +211,7 @@ int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W,
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
-    CF_CUDA(launch_peak_select(heads->heatmap, B, C, H, W, K, LIST_NMS, plan, w, st, &n), "peak_select");
+    CF_KERNEL(CF_KERNEL_PEAK_SELECT, st, launch_peak_select(heads->heatmap, B, C, H, W, K, LIST_NMS, plan, w, st, &n), "peak_select");
     MergeJob job;
     memset(&job, 0, sizeof(job));
     job.epilogue = EPI_DECODE;
@@ -186,7 +220,7 @@ int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W,
     job.dec.out_h = out_h;
     job.dec.out_w = out_w;
     job.dec.norm2d = norm2d;
-    CF_CUDA(launch_merge(heads->heatmap, B, C, H, W, K, plan, w, nullptr, &job, st, &n), "merge");
+    CF_KERNEL(CF_KERNEL_MERGE, st, launch_merge(heads->heatmap, B, C, H, W, K, plan, w, nullptr, &job, st, &n), "merge");
     g_launches = n;
     return 0;
 }
@@ -230,9 +264,9 @@ int cf_fusion_stage(const float* heat, const float* wh, const float* depth, cons
         dj.dec.out_w = out_w;
         dj.dec.norm2d = norm2d;
     }
-    CF_CUDA(launch_merge(heat, B, C, H, W, K, plan, w, &fj, with_decode ? &dj : nullptr, st, &n), "merge");
-    CF_CUDA(launch_assoc(pc_dep, B, H, W, K, max_pc_dist, w, assoc, st, &n), "assoc");
-    CF_CUDA(launch_paint(w.recs, K, K, nullptr, B, H, W, pc_hm, nullptr, st, &n), "paint");
+    CF_KERNEL(CF_KERNEL_MERGE, st, launch_merge(heat, B, C, H, W, K, plan, w, &fj, with_decode ? &dj : nullptr, st, &n), "merge");
+    CF_KERNEL(CF_KERNEL_ASSOC, st, launch_assoc(pc_dep, B, H, W, K, max_pc_dist, w, assoc, st, &n), "assoc");
+    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint(w.recs, K, K, nullptr, B, H, W, pc_hm, nullptr, st, &n), "paint");
     g_launches = n;
     return 0;
 }
@@ -265,10 +299,9 @@ int cf_radar_pillars(const double* points, const int32_t* counts, int B, int Nma
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
-    CF_CUDA(launch_pillar_rects(points, counts, B, Nmax, cam, calib, A, img_w, img_h, H, W, pillar_dims_host[0],
-                                pillar_dims_host[1], pillar_dims_host[2], max_dist, z_offset, (PaintRec*)ws, st, &n),
-            "pillar_rects");
-    CF_CUDA(launch_paint((const PaintRec*)ws, Nmax, Nmax, nullptr, B, H, W, pc_dep, owner, st, &n), "paint");
+    CF_KERNEL(CF_KERNEL_PILLAR_RECTS, st, launch_pillar_rects(points, counts, B, Nmax, cam, calib, A, img_w, img_h, H, W, pillar_dims_host[0],
+                                pillar_dims_host[1], pillar_dims_host[2], max_dist, z_offset, (PaintRec*)ws, st, &n), "pillar_rects");
+    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint((const PaintRec*)ws, Nmax, Nmax, nullptr, B, H, W, pc_dep, owner, st, &n), "paint");
     g_launches = n;
     return 0;
 }

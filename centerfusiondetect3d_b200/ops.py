@@ -1,0 +1,407 @@
+"""Host side of the B200-native fusion stage: the reference's Python call signatures on top of the C ABI.
+
+Every function here validates its tensors, allocates outputs with torch (device memory + current stream
+only -- torch does no arithmetic on this path) and calls libcfd3d_b200.so through ctypes.  There is no
+CPU / PyTorch fallback: non-CUDA tensors raise, a missing library raises.
+
+Reference callables mirrored (paths relative to the reference tree):
+    nms, topk, getFeature, transposeAndGetFeature          src/lib/model/utils.py:6-128
+    get_alpha, getDistanceThresh                           src/lib/utils/pointcloud.py:195-328
+    getPcFrustumHeatmap, cvtPcDepthToHeatmap               src/lib/utils/pointcloud.py:331-481
+    fusionDecode                                           src/lib/model/decode.py:10-174
+    processPointCloud (pillars) -> radar_to_pc_dep         src/lib/dataset/generic_dataset.py:738-942
+Original CenterFusion names (_nms, _topk, _tranpose_and_gather_feat, generate_pc_hm, get_pc_hm,
+pc_dep_to_hm_torch, fusion_decode) are exported as aliases.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import DecodeHeads, DecodeOut
+
+__all__ = [
+    "nms", "topk", "getFeature", "transposeAndGetFeature", "get_alpha", "getDistanceThresh",
+    "getPcFrustumHeatmap", "cvtPcDepthToHeatmap", "fusionDecode", "radar_to_pc_dep", "fusion_stage",
+    "frustum_association", "last_launch_count",
+    "_nms", "_topk", "_gather_feat", "_tranpose_and_gather_feat", "generate_pc_hm", "get_pc_hm",
+    "pc_dep_to_hm_torch", "fusion_decode", "get_dist_thresh",
+]
+
+
+# ------------------------------------------------------------------------------------------------------
+# plumbing
+# ------------------------------------------------------------------------------------------------------
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _ptr(t) -> int | None:
+    return None if t is None else t.data_ptr()
+
+
+def _map(t, name: str, ndim: int = 4, dtype=torch.float32) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor):
+        raise TypeError("%s must be a torch.Tensor, got %s" % (name, type(t).__name__))
+    if not t.is_cuda:
+        raise ValueError("%s must be a CUDA tensor: the fusion stage has no CPU path" % name)
+    if t.dtype != dtype:
+        raise TypeError("%s must be %s, got %s" % (name, dtype, t.dtype))
+    if ndim is not None and t.dim() != ndim:
+        raise ValueError("%s must have %d dimensions, got shape %s" % (name, ndim, tuple(t.shape)))
+    return t.contiguous()  # the reference accepts any strides
+
+
+_ws_cache: dict = {}
+
+
+def _workspace(dev: torch.device, nbytes: int) -> torch.Tensor:
+    """Grow-only per-(device, stream) scratch buffer: no allocation on the steady-state path."""
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=dev)
+        _ws_cache[key] = buf
+    return buf
+
+
+def _stage_ws(dev, B, Cc, H, W, K):
+    n = _lib.lib().cf_workspace_bytes(B, Cc, H, W, K)
+    if n == 0:
+        # let the ABI produce the precise error (K range, geometry)
+        n = 256
+    ws = _workspace(dev, n)
+    return ws, ws.numel()
+
+
+def last_launch_count() -> int:
+    """Kernels launched by the last ABI call on this thread."""
+    return int(_lib.lib().cf_last_launch_count())
+
+
+# ------------------------------------------------------------------------------------------------------
+# a1-a3  heat-map peak decode primitives                                   src/lib/model/utils.py
+# ------------------------------------------------------------------------------------------------------
+def nms(heatmap: torch.Tensor, kernel: int = 3) -> torch.Tensor:
+    """utils.py:112-128 -- heat * (maxpool3x3(heat) == heat)."""
+    if kernel != 3:
+        raise NotImplementedError("nms: only kernel=3 is on the fusion path (the reference never passes another)")
+    heat = _map(heatmap, "heatmap")
+    B, Cc, H, W = heat.shape
+    out = torch.empty_like(heat)
+    _lib.check(_lib.lib().cf_nms(heat.data_ptr(), B, Cc, H, W, out.data_ptr(), _stream(heat)))
+    return out
+
+
+def topk(heatmap: torch.Tensor, K: int = 100, *, apply_nms: bool = False):
+    """utils.py:6-38 -- (scores f32, inds i64, classes i32, ys i64, xs i64), each (B,K), scores descending.
+    Ties are ordered (score desc, class asc, index asc); torch.topk leaves them unspecified.
+    apply_nms=True selects on nms(heatmap) without materialising it."""
+    heat = _map(heatmap, "heatmap")
+    B, Cc, H, W = heat.shape
+    K = int(K)
+    dev = heat.device
+    scores = torch.empty((B, K), dtype=torch.float32, device=dev)
+    inds = torch.empty((B, K), dtype=torch.int64, device=dev)
+    classes = torch.empty((B, K), dtype=torch.int32, device=dev)
+    ys = torch.empty((B, K), dtype=torch.int64, device=dev)
+    xs = torch.empty((B, K), dtype=torch.int64, device=dev)
+    ws, wsn = _stage_ws(dev, B, Cc, H, W, K)
+    _lib.check(_lib.lib().cf_peak_topk(heat.data_ptr(), B, Cc, H, W, K, int(bool(apply_nms)), scores.data_ptr(),
+                                       inds.data_ptr(), classes.data_ptr(), ys.data_ptr(), xs.data_ptr(),
+                                       ws.data_ptr(), wsn, _stream(heat)))
+    return scores, inds, classes, ys, xs
+
+
+def transposeAndGetFeature(feature: torch.Tensor, indices: torch.Tensor) -> torch.Tensor:
+    """utils.py:58-72 -- out[b,m,c] = feature[b,c,indices[b,m]] read straight from NCHW."""
+    feat = _map(feature, "feature")
+    ind = _map(indices, "indices", ndim=2, dtype=torch.int64)
+    B, ch, H, W = feat.shape
+    if ind.shape[0] != B:
+        raise ValueError("indices batch %d != feature batch %d" % (ind.shape[0], B))
+    M = ind.shape[1]
+    out = torch.empty((B, M, ch), dtype=torch.float32, device=feat.device)
+    _lib.check(_lib.lib().cf_gather_nchw(feat.data_ptr(), B, ch, H * W, ind.data_ptr(), M, out.data_ptr(),
+                                         _stream(feat)))
+    return out
+
+
+def getFeature(feature: torch.Tensor, indices: torch.Tensor) -> torch.Tensor:
+    """utils.py:41-55 -- feature (B,N,ch), indices (B,M) -> (B,M,ch).  Same kernel as the NCHW gather with the
+    roles of the strides swapped: served by viewing feature as (B*N... ) is not possible without a copy, so this
+    one is a transposed view into the NCHW gather: out[b,m,c] = feature[b,indices[b,m],c]."""
+    feat = _map(feature, "feature", ndim=3)
+    # (B,N,ch) -> NCHW-style (B,ch,N,1); only the small (B,N,ch) candidate tensors ever take this path
+    return transposeAndGetFeature(feat.permute(0, 2, 1).unsqueeze(-1), indices)
+
+
+# ------------------------------------------------------------------------------------------------------
+# a4  observation angle and frustum distance threshold                     src/lib/utils/pointcloud.py
+# ------------------------------------------------------------------------------------------------------
+def get_alpha(rotation: torch.Tensor) -> torch.Tensor:
+    """pointcloud.py:195-211 -- rotation (...,8) -> alpha (...)."""
+    rot = _map(rotation, "rotation", ndim=None)
+    if rot.shape[-1] != 8:
+        raise ValueError("rotation must end in 8 bins, got %s" % (tuple(rot.shape),))
+    out = torch.empty(rot.shape[:-1], dtype=torch.float32, device=rot.device)
+    _lib.check(_lib.lib().cf_get_alpha(rot.data_ptr(), out.numel(), out.data_ptr(), _stream(rot)))
+    return out
+
+
+def getDistanceThresh(calib: torch.Tensor, center: torch.Tensor, dim: torch.Tensor, alpha: torch.Tensor):
+    """pointcloud.py:299-328 -- calib (B,3,4), center (B,K,2), dim (B,K,3), alpha (B,K) -> (B,K)."""
+    center = _map(center, "center", ndim=3)
+    B, K, _ = center.shape
+    calib = _map(calib, "calib", ndim=None).view(-1, 3, 4)
+    if calib.shape[0] == 1 and B > 1:
+        calib = calib.expand(B, 3, 4).contiguous()
+    if calib.shape[0] != B:
+        raise ValueError("calib must be view-able to (%d,3,4)" % B)
+    dim = _map(dim, "dim", ndim=3)
+    alpha = _map(alpha, "alpha", ndim=None).reshape(B, K)
+    out = torch.empty((B, K), dtype=torch.float32, device=center.device)
+    _lib.check(_lib.lib().cf_dist_thresh(calib.data_ptr(), center.data_ptr(), dim.data_ptr(), alpha.data_ptr(), B, K,
+                                         out.data_ptr(), _stream(center)))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------
+# a7 / a8  frustum association -> pc_hm                                     src/lib/utils/pointcloud.py
+# ------------------------------------------------------------------------------------------------------
+_FWD_ALIASES = {"heatmap": "hm", "widthHeight": "wh", "depth": "dep", "dimension": "dim", "rotation": "rot"}
+
+
+def _head(output: dict, name: str) -> torch.Tensor:
+    if name in output:
+        return output[name]
+    alt = _FWD_ALIASES.get(name)
+    if alt is not None and alt in output:  # original CenterFusion head names
+        return output[alt]
+    raise KeyError(name)
+
+
+def _cfg_k_dist(config):
+    if hasattr(config, "MODEL"):
+        return int(config.MODEL.K), float(config.DATASET.MAX_PC_DIST)
+    return int(config.K), float(config.max_pc_dist)  # original CenterFusion `opt`
+
+
+def frustum_association(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, K: int, max_pc_dist: float):
+    """getPcFrustumHeatmap plus the by-products the reference computes but does not return:
+    (pc_hm (B,3,H,W), assoc (B,K) i32 matched pc_dep pixel or -1, thr (B,K), inds (B,K) i64)."""
+    heat = _map(_head(output, "heatmap"), "heatmap")
+    B, Cc, H, W = heat.shape
+    wh = _map(_head(output, "widthHeight"), "widthHeight")
+    dep = _map(_head(output, "depth"), "depth")
+    dim = _map(_head(output, "dimension"), "dimension")
+    rot = _map(_head(output, "rotation"), "rotation")
+    pcd = _map(pc_dep, "pc_dep")
+    if pcd.shape != (B, 3, H, W):
+        raise NotImplementedError("pc_dep must be (B,3,H,W) [depth, vx, vz]; ONE_HOT_PC is forbidden together with "
+                                  "FRUSTUM by the reference (detectHeads.py:48)")
+    for t, ch, nm in ((wh, 2, "widthHeight"), (dep, 1, "depth"), (dim, 3, "dimension"), (rot, 8, "rotation")):
+        if t.shape != (B, ch, H, W):
+            raise ValueError("%s must be (%d,%d,%d,%d), got %s" % (nm, B, ch, H, W, tuple(t.shape)))
+    cal = _map(calib, "calib", ndim=None).view(B, 3, 4)
+    dev = heat.device
+    pc_hm = torch.empty_like(pcd)
+    assoc = torch.empty((B, K), dtype=torch.int32, device=dev)
+    thr = torch.empty((B, K), dtype=torch.float32, device=dev)
+    inds = torch.empty((B, K), dtype=torch.int64, device=dev)
+    ws, wsn = _stage_ws(dev, B, Cc, H, W, K)
+    _lib.check(_lib.lib().cf_frustum_pc_hm(heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
+                                           rot.data_ptr(), pcd.data_ptr(), cal.data_ptr(), B, Cc, H, W, int(K),
+                                           float(max_pc_dist), pc_hm.data_ptr(), assoc.data_ptr(), thr.data_ptr(),
+                                           inds.data_ptr(), ws.data_ptr(), wsn, _stream(heat)))
+    return pc_hm, assoc, thr, inds
+
+
+def getPcFrustumHeatmap(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config) -> torch.Tensor:
+    """pointcloud.py:331-394 -- drop-in for the call at detectHeads.py:176-177.  Returns a new pc_hm tensor."""
+    K, max_pc_dist = _cfg_k_dist(config)
+    return frustum_association(output, pc_dep, calib, K, max_pc_dist)[0]
+
+
+def cvtPcDepthToHeatmap(pc_hm, pc_dep, depth, bbox, distanceThreshold, max_pc_dist) -> None:
+    """pointcloud.py:397-481 -- one detection, IN PLACE on pc_hm (3,H,W).  depth / distanceThreshold may be 0-d or
+    1-element tensors (as the reference passes them) or Python numbers."""
+    hm = pc_hm
+    if not (isinstance(hm, torch.Tensor) and hm.is_cuda and hm.dtype == torch.float32 and hm.dim() == 3
+            and hm.is_contiguous()):
+        raise ValueError("pc_hm must be a contiguous CUDA float32 (3,H,W) tensor (it is written in place)")
+    pcd = _map(pc_dep, "pc_dep", ndim=3)
+    if pcd.shape != hm.shape or hm.shape[0] != 3:
+        raise ValueError("pc_hm and pc_dep must both be (3,H,W)")
+    _, H, W = hm.shape
+    dev = hm.device
+
+    def scalar(v, name):
+        if isinstance(v, torch.Tensor):
+            return _map(v.reshape(-1)[:1], name, ndim=1)
+        return torch.tensor([float(v)], dtype=torch.float32, device=dev)
+
+    d = scalar(depth, "depth")
+    t = scalar(distanceThreshold, "distanceThreshold")
+    bb = _map(bbox, "bbox", ndim=1) if isinstance(bbox, torch.Tensor) else torch.tensor(
+        [float(v) for v in bbox], dtype=torch.float32, device=dev)
+    if bb.numel() != 4:
+        raise ValueError("bbox must have 4 elements")
+    _lib.check(_lib.lib().cf_pc_dep_to_hm_single(hm.data_ptr(), pcd.data_ptr(), H, W, d.data_ptr(), bb.data_ptr(),
+                                                 t.data_ptr(), float(max_pc_dist), None, _stream(hm)))
+
+
+# ------------------------------------------------------------------------------------------------------
+# a9  fusionDecode                                                          src/lib/model/decode.py:10-174
+# ------------------------------------------------------------------------------------------------------
+_DEC_CH = {"reg": 2, "widthHeight": 2, "depth": 1, "rotation": 8, "dimension": 3, "amodal_offset": 2,
+           "nuscenes_att": 8, "velocity": 3, "uncertainty": 1}
+_DEC_HEAD_FIELD = {"reg": "reg", "widthHeight": "wh", "depth": "depth", "rotation": "rot", "dimension": "dim",
+                   "amodal_offset": "amodal", "nuscenes_att": "nuscenes_att", "velocity": "velocity",
+                   "uncertainty": "uncertainty"}
+_DEC_OUT = (("widthHeight", "bboxes", 4, "bboxes"), ("depth", "depth", 1, "depth"), ("rotation", "rot", 8, "rotation"),
+            ("dimension", "dim", 3, "dimension"), ("amodal_offset", "amodal", 2, "amodal_offset"),
+            ("nuscenes_att", "nuscenes_att", 8, "nuscenes_att"), ("velocity", "velocity", 3, "velocity"))
+
+
+def _decode_structs(output: dict, K: int, keep: list):
+    """Builds the ABI structs for one layer dict; applies the reference's rotation2 -> rotation rename
+    (decode.py:120-121) to the caller's dict."""
+    heat = _map(output["heatmap"], "heatmap")
+    B, Cc, H, W = heat.shape
+    dev = heat.device
+    src = {}
+    for name in _DEC_CH:
+        key = name
+        if name == "depth" and "depth2" in output:  # decode.py:101-110
+            key = "depth2"
+        if name == "rotation" and "rotation2" in output:
+            key = "rotation2"
+        if key in output:
+            t = _map(output[key], key)
+            if t.shape != (B, _DEC_CH[name], H, W):
+                raise ValueError("%s must be (%d,%d,%d,%d), got %s" % (key, B, _DEC_CH[name], H, W, tuple(t.shape)))
+            src[name] = t
+    if "rotation2" in output:
+        output["rotation"] = output.pop("rotation2")
+    heads = DecodeHeads()
+    heads.heatmap = heat.data_ptr()
+    for name, t in src.items():
+        setattr(heads, _DEC_HEAD_FIELD[name], t.data_ptr())
+    ret = {
+        "scores": torch.empty((B, K), dtype=torch.float32, device=dev),
+        "classIds": torch.empty((B, K), dtype=torch.float32, device=dev),
+        "centers": torch.empty((B, K, 2), dtype=torch.float32, device=dev),
+    }
+    out = DecodeOut()
+    out.scores, out.class_ids, out.centers = ret["scores"].data_ptr(), ret["classIds"].data_ptr(), ret["centers"].data_ptr()
+    for head, field, ch, key in _DEC_OUT:
+        if head in src:
+            ret[key] = torch.empty((B, K, ch), dtype=torch.float32, device=dev)
+            setattr(out, field, ret[key].data_ptr())
+    keep.extend(src.values())
+    keep.append(heat)
+    return heads, out, ret, (B, Cc, H, W), heat
+
+
+def fusionDecode(outputs, outputSize=(112, 200), K=100, norm2d=False) -> dict:
+    """decode.py:10-174 -- drop-in.  Single pyramid layer (all the reference's networks emit one, dla.py:579)."""
+    assert isinstance(outputs, list), "output must be a list of dictionaries"
+    layers = [o for o in outputs if "heatmap" in o]
+    if not layers:
+        return {}
+    if len(layers) != 1 or len(outputs) != 1:
+        raise NotImplementedError("fusionDecode: multi-layer pyramid outputs are not produced by any reference "
+                                  "network (dla.py:579) and are not implemented")
+    K = int(K)
+    keep: list = []
+    heads, out, ret, (B, Cc, H, W), heat = _decode_structs(layers[0], K, keep)
+    ws, wsn = _stage_ws(heat.device, B, Cc, H, W, K)
+    _lib.check(_lib.lib().cf_fusion_decode(C.byref(heads), B, Cc, H, W, K, int(outputSize[0]), int(outputSize[1]),
+                                           int(bool(norm2d)), C.byref(out), ws.data_ptr(), wsn, _stream(heat)))
+    return ret
+
+
+def fusion_stage(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config, outputSize=None, norm2d=False,
+                 decode_output: dict | None = None):
+    """getPcFrustumHeatmap + fusionDecode with ONE pass over the heat-map (cf_fusion_stage).
+
+    `output` holds the first-stage heads (heatmap, widthHeight, depth, dimension, rotation); `decode_output` the dict
+    fusionDecode would receive (defaults to `output`, which then typically also carries reg, depth2, rotation2, ...).
+    Returns (pc_hm, ret) exactly as the two reference calls would."""
+    K, max_pc_dist = _cfg_k_dist(config)
+    heat = _map(_head(output, "heatmap"), "heatmap")
+    B, Cc, H, W = heat.shape
+    wh = _map(_head(output, "widthHeight"), "widthHeight")
+    dep = _map(_head(output, "depth"), "depth")
+    dim = _map(_head(output, "dimension"), "dimension")
+    rot = _map(_head(output, "rotation"), "rotation")
+    pcd = _map(pc_dep, "pc_dep")
+    if pcd.shape != (B, 3, H, W):
+        raise ValueError("pc_dep must be (B,3,H,W)")
+    cal = _map(calib, "calib", ndim=None).view(B, 3, 4)
+    dec = output if decode_output is None else decode_output
+    dec_in = dict(dec)
+    dec_in["heatmap"] = heat  # same storage: the ABI requires one heat-map
+    keep: list = []
+    heads, out, ret, _, _ = _decode_structs(dec_in, K, keep)
+    if "rotation2" in dec:
+        dec["rotation"] = dec.pop("rotation2")
+    if outputSize is None:
+        outputSize = (H, W)
+    pc_hm = torch.empty_like(pcd)
+    ws, wsn = _stage_ws(heat.device, B, Cc, H, W, K)
+    _lib.check(_lib.lib().cf_fusion_stage(heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
+                                          rot.data_ptr(), pcd.data_ptr(), cal.data_ptr(), B, Cc, H, W, K,
+                                          max_pc_dist, pc_hm.data_ptr(), None, None, None, C.byref(heads),
+                                          int(outputSize[0]), int(outputSize[1]), int(bool(norm2d)), C.byref(out),
+                                          ws.data_ptr(), wsn, _stream(heat)))
+    return pc_hm, ret
+
+
+# ------------------------------------------------------------------------------------------------------
+# a5 + a6  radar pillar expansion -> pc_dep          src/lib/dataset/generic_dataset.py:738-942 (processPointCloud)
+# ------------------------------------------------------------------------------------------------------
+def radar_to_pc_dep(points: torch.Tensor, counts: torch.Tensor, cam: torch.Tensor, calib: torch.Tensor,
+                    A_out: torch.Tensor, out_hw, img_wh=(1600, 900), pillar_dims=(1.5, 0.2, 0.2), max_dist=60.0,
+                    z_offset=0.0, return_owner=False):
+    """points (B,Nmax,5) f64 [X,Y,Z,vx,vz] camera frame, each frame sorted ascending by Z; counts (B,) i32;
+    cam (B,3,3) f64; calib (B,3,4) f64; A_out (B,2,3) f64 -> pc_dep (B,3,H,W) f32 [, owner (B,H,W) i32]."""
+    pts = _map(points, "points", ndim=3, dtype=torch.float64)
+    B, Nmax, five = pts.shape
+    if five != 5:
+        raise ValueError("points must be (B,Nmax,5) [X,Y,Z,vx,vz]")
+    cnt = _map(counts, "counts", ndim=1, dtype=torch.int32)
+    cam = _map(cam, "cam", ndim=None, dtype=torch.float64).view(B, 3, 3)
+    cal = _map(calib, "calib", ndim=None, dtype=torch.float64).view(B, 3, 4)
+    A = _map(A_out, "A_out", ndim=None, dtype=torch.float64).view(B, 2, 3)
+    if cnt.shape[0] != B:
+        raise ValueError("counts must be (B,)")
+    H, W = int(out_hw[0]), int(out_hw[1])
+    dev = pts.device
+    pc_dep = torch.empty((B, 3, H, W), dtype=torch.float32, device=dev)
+    owner = torch.empty((B, H, W), dtype=torch.int32, device=dev) if return_owner else None
+    n = _lib.lib().cf_pillars_workspace_bytes(B, Nmax)
+    ws = _workspace(dev, n)
+    pd = (C.c_double * 3)(*[float(v) for v in pillar_dims])
+    _lib.check(_lib.lib().cf_radar_pillars(_ptr(pts) if Nmax else None, cnt.data_ptr(), B, Nmax, cam.data_ptr(),
+                                           cal.data_ptr(), A.data_ptr(), int(img_wh[0]), int(img_wh[1]), H, W, pd,
+                                           float(max_dist), float(z_offset), pc_dep.data_ptr(), _ptr(owner),
+                                           ws.data_ptr(), ws.numel(), _stream(pts)))
+    return (pc_dep, owner) if return_owner else pc_dep
+
+
+# ------------------------------------------------------------------------------------------------------
+# original CenterFusion (mrnabati) names
+# ------------------------------------------------------------------------------------------------------
+_nms = nms
+_topk = topk
+_gather_feat = getFeature
+_tranpose_and_gather_feat = transposeAndGetFeature
+generate_pc_hm = getPcFrustumHeatmap
+get_pc_hm = cvtPcDepthToHeatmap
+pc_dep_to_hm_torch = cvtPcDepthToHeatmap
+fusion_decode = fusionDecode
+get_dist_thresh = getDistanceThresh

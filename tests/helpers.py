@@ -135,3 +135,43 @@ def ref_assoc_indices(ns, inp, pc_dep, K, max_pc_dist):
                 if rs[0] >= rs[1] or cs[0] >= cs[1]:
                     assoc[b, k] = -2
     return assoc, thr.numpy()
+
+
+# ----------------------------------------------------------------------------------------------
+# seeded parity cases shared by the GPU tests, smoke() and bench.py
+# ----------------------------------------------------------------------------------------------
+FWD_KEYS = ("heatmap", "widthHeight", "depth", "dimension", "rotation")
+DEC_KEYS = ("heatmap", "reg", "widthHeight", "depth", "depth2", "rotation", "rotation2", "dimension",
+            "amodal_offset", "nuscenes_att", "velocity")
+
+
+def make_case(wl, B: int, seed: int = 1234, margins: bool = True) -> dict:
+    """Synthetic stage inputs for workload `wl` at batch B: tie-free heat-map in the top-(K+32) region, pc_dep painted
+    by the oracle's pillar code from the radar points, association margins established (see ensure_margins)."""
+    from centerfusiondetect3d_b200 import synthetic as syn
+    from oracle import binding as ob
+
+    while True:
+        inp = syn.make_inputs(wl, seed=seed, B=B)
+        if tie_free(inp["heatmap"], wl.K + 32):
+            break
+        seed += 1
+    pc_dep, owner = ob.radar_pillars(inp["radar_points"], inp["radar_counts"], inp["cam"], inp["calib64"],
+                                     inp["A_out"], (wl.img_w, wl.img_h), (wl.H, wl.W), wl.pillar_dims,
+                                     wl.max_pc_dist)
+    inp["pc_dep"] = pc_dep
+    inp["owner"] = owner
+    inp["seed"] = seed
+    inp["nudged"] = ensure_margins(inp, pc_dep, wl.K, wl.max_pc_dist) if margins else 0
+    return inp
+
+
+def to_cuda(inp: dict, keys, device="cuda:0") -> dict:
+    import torch
+
+    return {k: torch.from_numpy(np.ascontiguousarray(inp[k])).to(device) for k in keys}
+
+
+def bits(a) -> np.ndarray:
+    a = np.ascontiguousarray(a)
+    return a.view(np.uint32) if a.dtype == np.float32 else a

