@@ -102,6 +102,7 @@ size_t cf_pillars_workspace_bytes(int B, int Nmax) {
 
 int cf_nms(const float* heat, int B, int C, int H, int W, float* out, void* stream) {
     g_launches = 0;
+    if (B == 0) return 0;
     if (!heat || !out) return fail(CF_E_NULL, "cf_nms: NULL pointer");
     if (int rc = check_dims(B, C, H, W)) return rc;
     if (B == 0) return 0;
@@ -146,6 +147,7 @@ int cf_dist_thresh(const float* calib, const float* center, const float* dim, co
 int cf_peak_topk(const float* heat, int B, int C, int H, int W, int K, int apply_nms, float* scores, int64_t* inds,
                  int32_t* classes, int64_t* ys, int64_t* xs, void* ws, size_t ws_bytes, void* stream) {
     g_launches = 0;
+    if (B == 0 && C >= 1 && H >= 1 && W >= 1) return check_k(K, H, W);  // empty batch: data pointers may be NULL
     if (!heat) return fail(CF_E_NULL, "cf_peak_topk: heat is NULL");
     if (int rc = check_dims(B, C, H, W)) return rc;
     if (int rc = check_k(K, H, W)) return rc;
@@ -200,6 +202,7 @@ int cf_frustum_pc_hm(const float* heat, const float* wh, const float* depth, con
 int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W, int K, int out_h, int out_w,
                      int norm2d, const cf_decode_out_t* out, void* ws, size_t ws_bytes, void* stream) {
     g_launches = 0;
+    if (B == 0) return 0;
     if (int rc = check_decode_args(heads, out)) return rc;
     if (int rc = check_dims(B, C, H, W)) return rc;
     if (int rc = check_k(K, H, W)) return rc;
@@ -231,6 +234,7 @@ int cf_fusion_stage(const float* heat, const float* wh, const float* depth, cons
                     int out_h, int out_w, int norm2d, const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes,
                     void* stream) {
     g_launches = 0;
+    if (B == 0) return 0;
     if (int rc = check_frustum_args(heat, wh, depth, dim, rot, pc_dep, calib, pc_hm)) return rc;
     const bool with_decode = dec_heads != nullptr;
     if (with_decode) {
@@ -248,8 +252,9 @@ int cf_fusion_stage(const float* heat, const float* wh, const float* depth, cons
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
-    CF_CUDA(launch_peak_select(heat, B, C, H, W, K, with_decode ? (LIST_RAW | LIST_NMS) : LIST_RAW, plan, w, st, &n),
-            "peak_select");
+    CF_KERNEL(CF_KERNEL_PEAK_SELECT, st,
+              launch_peak_select(heat, B, C, H, W, K, with_decode ? (LIST_RAW | LIST_NMS) : LIST_RAW, plan, w, st, &n),
+              "peak_select");
     MergeJob fj, dj;
     memset(&fj, 0, sizeof(fj));
     memset(&dj, 0, sizeof(dj));
