@@ -292,7 +292,7 @@ def main() -> int:
     torch.cuda.synchronize()
 
     # -- correctness guard: the bench measures a path that agrees with the oracle on its own inputs (small sample) --
-    if rank == 0:
+    if rank == 0 and not os.environ.get("CFD3D_STOP_AFTER"):
         from oracle import binding as ob
 
         nb = min(B, 2)

@@ -3,6 +3,7 @@
 // either launches the sm_100a kernels on the caller's stream or returns an error.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "kernels.cuh"
@@ -71,6 +72,16 @@ static int check_ws(void* ws, size_t ws_bytes, size_t need) {
     return 0;
 }
 static bool misaligned4(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 3u) != 0; }
+
+// clear [hist|ctr], bound pass (the HBM read of the heat-map), filter pass
+static int run_peak_passes(const float* heat, int B, int C, int H, int W, int K, int lists, const Plan& plan,
+                           const Workspace& w, cudaStream_t st, int* n, int stop = 1 << 30) {
+    CF_CUDA(launch_peak_clear(w, st), "peak_clear");
+    CF_KERNEL(CF_KERNEL_PEAK_SELECT, st, launch_peak_bound(heat, B, C, H, W, K, lists, plan, w, st, n), "peak_bound");
+    if (*n >= stop) return 0;
+    CF_KERNEL(CF_KERNEL_PEAK_FILTER, st, launch_peak_filter(heat, B, C, H, W, K, lists, plan, w, st, n), "peak_filter");
+    return 0;
+}
 
 extern "C" {
 
@@ -161,7 +172,7 @@ int cf_peak_topk(const float* heat, int B, int C, int H, int W, int K, int apply
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
     const int list = apply_nms ? LIST_NMS : LIST_RAW;
-    CF_KERNEL(CF_KERNEL_PEAK_SELECT, st, launch_peak_select(heat, B, C, H, W, K, list, plan, w, st, &n), "peak_select");
+    if (int rc = run_peak_passes(heat, B, C, H, W, K, list, plan, w, st, &n)) return rc;
     MergeJob job;
     memset(&job, 0, sizeof(job));
     job.epilogue = EPI_TOPK;
@@ -214,7 +225,7 @@ int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W,
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
-    CF_KERNEL(CF_KERNEL_PEAK_SELECT, st, launch_peak_select(heads->heatmap, B, C, H, W, K, LIST_NMS, plan, w, st, &n), "peak_select");
+    if (int rc = run_peak_passes(heads->heatmap, B, C, H, W, K, LIST_NMS, plan, w, st, &n)) return rc;
     MergeJob job;
     memset(&job, 0, sizeof(job));
     job.epilogue = EPI_DECODE;
@@ -252,9 +263,17 @@ int cf_fusion_stage(const float* heat, const float* wh, const float* depth, cons
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
-    CF_KERNEL(CF_KERNEL_PEAK_SELECT, st,
-              launch_peak_select(heat, B, C, H, W, K, with_decode ? (LIST_RAW | LIST_NMS) : LIST_RAW, plan, w, st, &n),
-              "peak_select");
+    // development aid: CFD3D_STOP_AFTER=<n> ends the call after n kernels (cumulative in-pipeline timings)
+    int stop = 1 << 30;
+    if (const char* e = getenv("CFD3D_STOP_AFTER")) stop = atoi(e);
+    if (stop == 0) {
+        CF_CUDA(launch_peak_clear(w, st), "peak_clear");
+        return 0;
+    }
+    if (int rc = run_peak_passes(heat, B, C, H, W, K, with_decode ? (LIST_RAW | LIST_NMS) : LIST_RAW, plan, w, st, &n,
+                                 stop))
+        return rc;
+    if (n >= stop) return 0;
     MergeJob fj, dj;
     memset(&fj, 0, sizeof(fj));
     memset(&dj, 0, sizeof(dj));
@@ -270,7 +289,9 @@ int cf_fusion_stage(const float* heat, const float* wh, const float* depth, cons
         dj.dec.norm2d = norm2d;
     }
     CF_KERNEL(CF_KERNEL_MERGE, st, launch_merge(heat, B, C, H, W, K, plan, w, &fj, with_decode ? &dj : nullptr, st, &n), "merge");
+    if (n >= stop) return 0;
     CF_KERNEL(CF_KERNEL_ASSOC, st, launch_assoc(pc_dep, B, H, W, K, max_pc_dist, w, assoc, st, &n), "assoc");
+    if (n >= stop) return 0;
     CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint(w.recs, K, K, nullptr, B, H, W, pc_hm, nullptr, st, &n), "paint");
     g_launches = n;
     return 0;

@@ -8,19 +8,22 @@
 
 namespace cf {
 
-// ---- launch plan of the peak-select kernel for one map geometry ------------------------------------
+// ---- launch plan of the two heat-map passes for one map geometry --------------------------------------
+// A frame is viewed as a (C*H) x W row matrix; a tile is R consecutive rows of it (+1 halo row each side).
 struct Plan {
-    int T;       // threads per CTA (512 or 1024)
-    int EI;      // float4 items per thread (compile-time bound of the instantiation)
-    int J;       // per-thread top-J feeding the warp bound
-    int R;       // rows per band
-    int S;       // bands per class plane
+    int T;       // threads per CTA of the heat-map passes
+    int R;       // rows per tile
+    int NT;      // tiles per frame
     int Wp;      // shared-memory row stride in floats (W rounded up to 4)
-    int NB;      // candidate lists per frame and kind = C * S
-    size_t smem; // dynamic shared memory of the peak-select kernel
+    size_t smem; // dynamic shared memory of the heat-map passes
 };
 // returns false when the geometry is unsupported
 bool make_plan(int C, int H, int W, int K, Plan* p);
+
+constexpr int HIST_SHIFT = 20;                       // histogram bin = key >> HIST_SHIFT (sign, exponent, 3 mantissa bits)
+constexpr int HIST_BINS = 1 << (32 - HIST_SHIFT);    // 4096
+constexpr int CAND_CAP = 2048;                       // survivor slots per (frame, list)
+constexpr int CTR_STRIDE = 4;                        // per (frame, list): [0] survivors appended, [1] bound tiles done
 
 // per-detection frustum parameters, produced by the merge kernel, consumed by the association kernel
 struct __align__(16) DetParam {
@@ -41,10 +44,14 @@ struct __align__(16) PaintRec {
 static_assert(sizeof(PaintRec) == 32, "PaintRec");
 
 struct Workspace {
-    unsigned long long* cand_raw;  // (B, NB, K)
-    unsigned long long* cand_nms;  // (B, NB, K)
-    DetParam* det;                 // (B, K)
-    PaintRec* recs;                // (B, K)
+    void* zero_base;            // [hist | ctr]: cleared by one memset at the start of every call
+    size_t zero_bytes;
+    uint32_t* hist;             // (B, 2, HIST_BINS) histogram of group maxima, list 0 = raw, 1 = nms'd
+    uint32_t* ctr;              // (B, 2, CTR_STRIDE)
+    uint32_t* tau;              // (B, 2) key threshold: every pixel of the frame's top-K has key >= tau
+    unsigned long long* cand;   // (B, 2, CAND_CAP) survivors (composites), unordered
+    DetParam* det;              // (B, K)
+    PaintRec* recs;             // (B, K)
 };
 size_t workspace_layout(int B, int C, int H, int W, int K, const Plan& plan, void* base, Workspace* out);
 
@@ -80,7 +87,12 @@ struct MergeJob {       // what the merge kernel does with one sorted list
 };
 
 // ---- launchers (each returns the cudaError_t of its launch; *launches += kernels launched) ----------
-cudaError_t launch_peak_select(const float* heat, int B, int C, int H, int W, int K, int lists, const Plan& plan,
+// the three steps of the peak decode ahead of the merge: clear [hist|ctr], bound pass (HBM read of the heat-map:
+// group maxima -> histogram -> tau), filter pass (re-read, L2-resident at the reference batch sizes: survivors)
+cudaError_t launch_peak_clear(const Workspace& ws, cudaStream_t st);
+cudaError_t launch_peak_bound(const float* heat, int B, int C, int H, int W, int K, int lists, const Plan& plan,
+                              const Workspace& ws, cudaStream_t st, int* launches);
+cudaError_t launch_peak_filter(const float* heat, int B, int C, int H, int W, int K, int lists, const Plan& plan,
                                const Workspace& ws, cudaStream_t st, int* launches);
 cudaError_t launch_merge(const float* heat, int B, int C, int H, int W, int K, const Plan& plan,
                          const Workspace& ws, const MergeJob* raw_job, const MergeJob* nms_job, cudaStream_t st,

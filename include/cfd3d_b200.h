@@ -153,11 +153,12 @@ CF_API int cf_last_launch_count(void);
  * call's stream right before kernel `kernel_id` and `ev_stop` right after it (both cudaEvent_t created by the
  * caller with timing enabled).  kernel_id < 0 or NULL events clear the hook.  No reference counterpart. */
 enum {
-    CF_KERNEL_PEAK_SELECT = 0, /* heat-map pass: 3x3 max + band-local top-K (the dominant kernel) */
-    CF_KERNEL_MERGE = 1,       /* frame-wide top-K + gathers + frustum geometry / decode epilogue */
+    CF_KERNEL_PEAK_SELECT = 0, /* bound pass: the HBM read of the heat-map, 3x3 max + group maxima -> tau (dominant) */
+    CF_KERNEL_MERGE = 1,       /* frame-wide sorted top-K + gathers + frustum geometry / decode epilogue */
     CF_KERNEL_ASSOC = 2,       /* per-ROI nearest-depth radar association */
     CF_KERNEL_PAINT = 3,       /* ordered pc_hm / pc_dep paint */
-    CF_KERNEL_PILLAR_RECTS = 4 /* radar point -> pillar rectangle */
+    CF_KERNEL_PILLAR_RECTS = 4, /* radar point -> pillar rectangle */
+    CF_KERNEL_PEAK_FILTER = 5   /* filter pass: re-read (L2) + survivors >= tau */
 };
 CF_API int cf_set_kernel_events(int kernel_id, void* ev_start, void* ev_stop);
 

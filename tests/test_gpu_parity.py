@@ -306,7 +306,9 @@ def test_full_size_properties(ops, cfg_name, B):
     assert (heat[torch.arange(B, device=DEV)[:, None], c.long(), y, x] == s).all()   # scores are the map values
     assert (i == y * wl.W + x).all()
     kth = s[:, -1:]
-    assert ((heat.view(B, -1) > kth).sum(dim=1) == wl.K - 1).all()          # exactly K-1 values beat the K-th
+    # the K-th score is the K-th largest value of the frame (torch.rand has ties: < K beat it, >= K reach it)
+    assert ((heat.view(B, -1) > kth).sum(dim=1) <= wl.K - 1).all()
+    assert ((heat.view(B, -1) >= kth).sum(dim=1) >= wl.K).all()
     n = ops.nms(heat)
     assert (ops.nms(n) == n).all() or True                                  # (nms of nms may differ on plateaus)
     s2, i2, c2, _, _ = ops.topk(heat, wl.K, apply_nms=True)
@@ -332,7 +334,8 @@ def test_full_size_properties(ops, cfg_name, B):
     assert (dsel[m] != 0).all()
     painted = hm[:, 0] != 0
     assert (hm[:, 1][painted] == 7.0).all() and (hm[:, 1][~painted] == 0).all()
-    allowed = torch.unique(dsel[m] / 60.0)
+    # true fp32 division on the CPU (torch's CUDA div-by-scalar multiplies by the reciprocal: 1 ulp off)
+    allowed = torch.unique(dsel[m].cpu() / 60.0).to(DEV)
     assert torch.isin(hm[:, 0][painted], allowed).all()
     hm_again = ops.frustum_association(out, pc_dep, calib, wl.K, 60.0)[0]
     assert (hm_again == hm).all()                                           # deterministic
