@@ -74,12 +74,23 @@ static int check_ws(void* ws, size_t ws_bytes, size_t need) {
 static bool misaligned4(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 3u) != 0; }
 
 // clear [hist|ctr], bound pass (the HBM read of the heat-map), filter pass
-static int run_peak_passes(const float* heat, int B, int C, int H, int W, int K, int lists, const Plan& plan,
-                           const Workspace& w, cudaStream_t st, int* n, int stop = 1 << 30) {
+// (the filter pass ends with the per-frame merge: sorted top-K + the jobs' epilogues)
+static int run_peak_passes(const float* heat, int B, int C, int H, int W, int K, const MergeJob* raw_job,
+                           const MergeJob* nms_job, const Plan& plan, const Workspace& w, cudaStream_t st, int* n,
+                           int stop = 1 << 30) {
+    const int lists = (raw_job ? LIST_RAW : 0) | (nms_job ? LIST_NMS : 0);
     CF_CUDA(launch_peak_clear(w, st), "peak_clear");
     CF_KERNEL(CF_KERNEL_PEAK_SELECT, st, launch_peak_bound(heat, B, C, H, W, K, lists, plan, w, st, n), "peak_bound");
     if (*n >= stop) return 0;
-    CF_KERNEL(CF_KERNEL_PEAK_FILTER, st, launch_peak_filter(heat, B, C, H, W, K, lists, plan, w, st, n), "peak_filter");
+    // CFD3D_FUSE_MERGE=1: the last filter CTA of a frame runs the frame's merge jobs (one launch less; slower at
+    // the reference sizes because the two jobs then run back to back on 256 threads)
+    static const bool fuse = getenv("CFD3D_FUSE_MERGE") && atoi(getenv("CFD3D_FUSE_MERGE")) != 0;
+    CF_KERNEL(CF_KERNEL_PEAK_FILTER, st,
+              launch_peak_filter(heat, B, C, H, W, K, lists, plan, w, fuse ? raw_job : nullptr,
+                                 fuse ? nms_job : nullptr, st, n),
+              "peak_filter");
+    if (*n >= stop || fuse) return 0;
+    CF_KERNEL(CF_KERNEL_MERGE, st, launch_merge(heat, B, C, H, W, K, plan, w, raw_job, nms_job, st, n), "merge");
     return 0;
 }
 
@@ -171,13 +182,13 @@ int cf_peak_topk(const float* heat, int B, int C, int H, int W, int K, int apply
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
-    const int list = apply_nms ? LIST_NMS : LIST_RAW;
-    if (int rc = run_peak_passes(heat, B, C, H, W, K, list, plan, w, st, &n)) return rc;
     MergeJob job;
     memset(&job, 0, sizeof(job));
     job.epilogue = EPI_TOPK;
     job.topk = TopkOut{scores, inds, classes, ys, xs};
-    CF_KERNEL(CF_KERNEL_MERGE, st, launch_merge(heat, B, C, H, W, K, plan, w, apply_nms ? nullptr : &job, apply_nms ? &job : nullptr, st, &n), "merge");
+    if (int rc = run_peak_passes(heat, B, C, H, W, K, apply_nms ? nullptr : &job, apply_nms ? &job : nullptr, plan, w, st,
+                                 &n))
+        return rc;
     g_launches = n;
     return 0;
 }
@@ -225,7 +236,6 @@ int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W,
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
-    if (int rc = run_peak_passes(heads->heatmap, B, C, H, W, K, LIST_NMS, plan, w, st, &n)) return rc;
     MergeJob job;
     memset(&job, 0, sizeof(job));
     job.epilogue = EPI_DECODE;
@@ -234,7 +244,7 @@ int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W,
     job.dec.out_h = out_h;
     job.dec.out_w = out_w;
     job.dec.norm2d = norm2d;
-    CF_KERNEL(CF_KERNEL_MERGE, st, launch_merge(heads->heatmap, B, C, H, W, K, plan, w, nullptr, &job, st, &n), "merge");
+    if (int rc = run_peak_passes(heads->heatmap, B, C, H, W, K, nullptr, &job, plan, w, st, &n)) return rc;
     g_launches = n;
     return 0;
 }
@@ -270,10 +280,6 @@ int cf_fusion_stage(const float* heat, const float* wh, const float* depth, cons
         CF_CUDA(launch_peak_clear(w, st), "peak_clear");
         return 0;
     }
-    if (int rc = run_peak_passes(heat, B, C, H, W, K, with_decode ? (LIST_RAW | LIST_NMS) : LIST_RAW, plan, w, st, &n,
-                                 stop))
-        return rc;
-    if (n >= stop) return 0;
     MergeJob fj, dj;
     memset(&fj, 0, sizeof(fj));
     memset(&dj, 0, sizeof(dj));
@@ -288,7 +294,7 @@ int cf_fusion_stage(const float* heat, const float* wh, const float* depth, cons
         dj.dec.out_w = out_w;
         dj.dec.norm2d = norm2d;
     }
-    CF_KERNEL(CF_KERNEL_MERGE, st, launch_merge(heat, B, C, H, W, K, plan, w, &fj, with_decode ? &dj : nullptr, st, &n), "merge");
+    if (int rc = run_peak_passes(heat, B, C, H, W, K, &fj, with_decode ? &dj : nullptr, plan, w, st, &n, stop)) return rc;
     if (n >= stop) return 0;
     CF_KERNEL(CF_KERNEL_ASSOC, st, launch_assoc(pc_dep, B, H, W, K, max_pc_dist, w, assoc, st, &n), "assoc");
     if (n >= stop) return 0;

@@ -1,0 +1,110 @@
+// assoc.cuh -- per-ROI nearest-depth radar association of ONE detection by ONE warp, and the paint window.
+//
+// Replaces (reference, src/lib/utils/pointcloud.py): :424-461 ROI + threshold test + first-minimum search and
+// :468-481 the 0.3-scaled box of cvtPcDepthToHeatmap.
+#pragma once
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace cf {
+
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        const unsigned long long o = __shfl_xor_sync(FULL, v, off);
+        v = o < v ? o : v;
+    }
+    return v;
+}
+
+// ROI + threshold test + first-minimum search (pointcloud.py:424-461) by NT cooperating threads (`t` of NT, NT a
+// multiple of 32 or the whole block); the caller reduces the returned key with a minimum.  Key = (depth bits,
+// flat pixel): depths that pass are positive, so the bit pattern orders like the value and the minimum key is
+// the first minimum in row-major ROI order.  Lanes run over columns, rows are unrolled: independent loads, no
+// division.
+__device__ __forceinline__ unsigned long long roi_scan(const float* __restrict__ dep, int H, int W, float x1, float y1,
+                                                       float x2, float y2, float depth, float thr, int t, int NT) {
+    int ya, yb, xa, xb;
+    pyslice((long long)floorf(y1), (long long)ceilf(y2) + 1, H, ya, yb);
+    pyslice((long long)floorf(x1), (long long)ceilf(x2) + 1, W, xa, xb);
+    const float hi = __fadd_rn(depth, thr);
+    float lo = __fsub_rn(depth, thr);
+    if (!(lo > 0.0f)) lo = 0.0f;  // python max(0, t)
+    unsigned long long best = ~0ull;
+    if (ya >= yb || xa >= xb) return best;
+    const int w = xb - xa;
+    // thread t -> (row phase, column): columns fastest so that a warp reads contiguous runs
+    const int cols = w < NT ? w : NT;       // threads along x
+    const int rows_par = NT / cols;         // rows processed side by side
+    const int ty = t / cols, tx = t - ty * cols;
+    if (ty >= rows_par) return best;
+    constexpr int U = 8;  // loads in flight per thread
+    for (int xx = xa + tx; xx < xb; xx += cols) {
+        for (int y0 = ya + ty; y0 < yb; y0 += U * rows_par) {
+            float v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int yy = y0 + u * rows_par;
+                const int yc = yy < yb ? yy : ya;  // clamped: the load is unconditional, 0 fails the test below
+                const float t_ = __ldg(dep + (size_t)yc * W + xx);
+                v[u] = yy < yb ? t_ : 0.0f;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int yy = y0 + u * rows_par;
+                if (v[u] != 0.0f && v[u] < hi && v[u] > lo) {
+                    const unsigned long long key = ((unsigned long long)__float_as_uint(v[u]) << 32) |
+                                                   (unsigned long long)(uint32_t)(yy * W + xx);
+                    best = key < best ? key : best;
+                }
+            }
+        }
+    }
+    return best;
+}
+
+// paint window of cvtPcDepthToHeatmap (pointcloud.py:468-481): rows h_min:h_max+1, cols w_min:w_max+1+1
+__device__ __forceinline__ void paint_window(float x1, float y1, float x2, float y2, int H, int W, int& ra, int& rb,
+                                             int& ca, int& cb) {
+    const float cx = __fdiv_rn(__fadd_rn(x1, x2), 2.0f), cy = __fdiv_rn(__fadd_rn(y1, y2), 2.0f);
+    const float hw_ = __fdiv_rn(__fmul_rn(0.3f, __fsub_rn(x2, x1)), 2.0f);
+    const float hh_ = __fdiv_rn(__fmul_rn(0.3f, __fsub_rn(y2, y1)), 2.0f);
+    const long long wmin = (long long)__fsub_rn(cx, hw_), wmax = (long long)__fadd_rn(cx, hw_);  // int(): toward 0
+    const long long hmin = (long long)__fsub_rn(cy, hh_), hmax = (long long)__fadd_rn(cy, hh_);
+    pyslice(hmin, hmax + 1, H, ra, rb);
+    pyslice(wmin, wmax + 2, W, ca, cb);
+}
+
+// One detection, one warp: association + paint record.  dep = the frame's pc_dep (3,H,W).
+__device__ __forceinline__ void assoc_one(const float* __restrict__ dep, int H, int W, const DetParam& d,
+                                          float max_pc_dist, PaintRec* rec_out, int32_t* assoc_out) {
+    const int lane = threadIdx.x & 31;
+    const size_t HW = (size_t)H * W;
+    const unsigned long long best =
+        warp_min_u64(roi_scan(dep, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32));
+    if (lane != 0) return;
+    PaintRec r;
+    r.ra = r.rb = r.ca = r.cb = 0;
+    r.v0 = r.v1 = r.v2 = 0.0f;
+    r.pad_ = r.pad2_ = 0;
+    int32_t a = -1;
+    if (best != ~0ull) {
+        const uint32_t mp = (uint32_t)best;
+        a = (int32_t)mp;
+        r.v0 = __fdiv_rn(__uint_as_float((uint32_t)(best >> 32)), max_pc_dist);  // :462-466
+        r.v1 = __ldg(dep + HW + mp);
+        r.v2 = __ldg(dep + 2 * HW + mp);
+        int ra, rb, ca, cb;
+        paint_window(d.x1, d.y1, d.x2, d.y2, H, W, ra, rb, ca, cb);
+        if (ra < rb && ca < cb) {
+            r.ra = (int16_t)ra;
+            r.rb = (int16_t)rb;
+            r.ca = (int16_t)ca;
+            r.cb = (int16_t)cb;
+        }
+    }
+    *rec_out = r;
+    if (assoc_out) *assoc_out = a;
+}
+
+}  // namespace cf

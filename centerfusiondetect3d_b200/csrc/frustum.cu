@@ -12,6 +12,7 @@
 // every output pixel is written to HBM exactly once, coalesced, zeros included.
 #include <math_constants.h>
 
+#include "assoc.cuh"
 #include "geometry.cuh"
 #include "kernels.cuh"
 
@@ -22,98 +23,16 @@ namespace cf {
 // -----------------------------------------------------------------------------------------------------
 constexpr int AW = 8;  // warps (detections) per CTA
 
-struct RoiMatch {
-    bool found;
-    uint32_t pix;  // flat y*W+x of the matched pc_dep pixel
-    float v;       // its depth
-};
-
-// ROI + threshold test + first-minimum search of cvtPcDepthToHeatmap (pointcloud.py:424-461), executed by
-// NT cooperating threads (lane `t` of NT); the caller reduces `best` across them.
-__device__ __forceinline__ unsigned long long roi_scan(const float* __restrict__ dep, int H, int W, float x1, float y1,
-                                                       float x2, float y2, float depth, float thr, int t, int NT) {
-    int ya, yb, xa, xb;
-    pyslice((long long)floorf(y1), (long long)ceilf(y2) + 1, H, ya, yb);
-    pyslice((long long)floorf(x1), (long long)ceilf(x2) + 1, W, xa, xb);
-    const float hi = __fadd_rn(depth, thr);
-    float lo = __fsub_rn(depth, thr);
-    if (!(lo > 0.0f)) lo = 0.0f;  // python max(0, t)
-    unsigned long long best = ~0ull;
-    if (ya < yb && xa < xb) {
-        const int w = xb - xa;
-        const int n = (yb - ya) * w;
-        for (int i = t; i < n; i += NT) {
-            const int ry = i / w;
-            const int yy = ya + ry, xx = xa + (i - ry * w);
-            const float v = __ldg(dep + (size_t)yy * W + xx);
-            if (v != 0.0f && v < hi && v > lo) {  // v > lo >= 0: positive, so the bit pattern orders like the value
-                const unsigned long long key =
-                    ((unsigned long long)__float_as_uint(v) << 32) | (unsigned long long)(uint32_t)(yy * W + xx);
-                best = key < best ? key : best;
-            }
-        }
-    }
-    return best;
-}
-
-__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-        const unsigned long long o = __shfl_xor_sync(FULL, v, off);
-        v = o < v ? o : v;
-    }
-    return v;
-}
-
-// paint window of cvtPcDepthToHeatmap (pointcloud.py:468-481): rows h_min:h_max+1, cols w_min:w_max+1+1
-__device__ __forceinline__ void paint_window(float x1, float y1, float x2, float y2, int H, int W, int& ra, int& rb,
-                                             int& ca, int& cb) {
-    const float cx = __fdiv_rn(__fadd_rn(x1, x2), 2.0f), cy = __fdiv_rn(__fadd_rn(y1, y2), 2.0f);
-    const float hw_ = __fdiv_rn(__fmul_rn(0.3f, __fsub_rn(x2, x1)), 2.0f);
-    const float hh_ = __fdiv_rn(__fmul_rn(0.3f, __fsub_rn(y2, y1)), 2.0f);
-    const long long wmin = (long long)__fsub_rn(cx, hw_), wmax = (long long)__fadd_rn(cx, hw_);  // int(): toward 0
-    const long long hmin = (long long)__fsub_rn(cy, hh_), hmax = (long long)__fadd_rn(cy, hh_);
-    pyslice(hmin, hmax + 1, H, ra, rb);
-    pyslice(wmin, wmax + 2, W, ca, cb);
-}
-
 __global__ void __launch_bounds__(AW * 32) assoc_kernel(const float* __restrict__ pc_dep, int H, int W, int K,
                                                         float max_pc_dist, const DetParam* __restrict__ det,
                                                         PaintRec* __restrict__ recs, int32_t* __restrict__ assoc) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int warp = threadIdx.x >> 5;
     const int k = blockIdx.x * AW + warp;
     const int b = blockIdx.y;
     if (k >= K) return;
-    const size_t HW = (size_t)H * W;
     const size_t o = (size_t)b * K + k;
     const DetParam d = det[o];
-    const float* dep = pc_dep + (size_t)b * 3 * HW;
-    const unsigned long long best =
-        warp_min_u64(roi_scan(dep, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32));
-    if (lane == 0) {
-        PaintRec r;
-        r.ra = r.rb = r.ca = r.cb = 0;
-        r.v0 = r.v1 = r.v2 = 0.0f;
-        r.pad_ = r.pad2_ = 0;
-        int32_t a = -1;
-        if (best != ~0ull) {
-            const uint32_t mp = (uint32_t)best;
-            a = (int32_t)mp;
-            r.v0 = __fdiv_rn(__uint_as_float((uint32_t)(best >> 32)), max_pc_dist);  // :462-466
-            r.v1 = __ldg(dep + HW + mp);
-            r.v2 = __ldg(dep + 2 * HW + mp);
-            int ra, rb, ca, cb;
-            paint_window(d.x1, d.y1, d.x2, d.y2, H, W, ra, rb, ca, cb);
-            if (ra < rb && ca < cb) {
-                r.ra = (int16_t)ra;
-                r.rb = (int16_t)rb;
-                r.ca = (int16_t)ca;
-                r.cb = (int16_t)cb;
-            }
-        }
-        recs[o] = r;
-        if (assoc) assoc[o] = a;
-    }
+    assoc_one(pc_dep + (size_t)b * 3 * H * W, H, W, d, max_pc_dist, recs + o, assoc ? assoc + o : nullptr);
 }
 
 cudaError_t launch_assoc(const float* pc_dep, int B, int H, int W, int K, float max_pc_dist, const Workspace& ws,

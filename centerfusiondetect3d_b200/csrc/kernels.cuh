@@ -86,6 +86,17 @@ struct MergeJob {       // what the merge kernel does with one sorted list
     DecodeArgs dec;     // EPI_DECODE
 };
 
+// what the merge tail of the filter pass does per frame: up to two jobs (raw list, nms'd list)
+struct MergeParams {
+    const float* heat;
+    int C, H, W, K;
+    const uint32_t* ctr;
+    const unsigned long long* cand;
+    int list[2];  // 0 = raw, 1 = nms'd
+    MergeJob job[2];
+    DetParam* det;
+};
+
 // ---- launchers (each returns the cudaError_t of its launch; *launches += kernels launched) ----------
 // the three steps of the peak decode ahead of the merge: clear [hist|ctr], bound pass (HBM read of the heat-map:
 // group maxima -> histogram -> tau), filter pass (re-read, L2-resident at the reference batch sizes: survivors)
@@ -93,7 +104,8 @@ cudaError_t launch_peak_clear(const Workspace& ws, cudaStream_t st);
 cudaError_t launch_peak_bound(const float* heat, int B, int C, int H, int W, int K, int lists, const Plan& plan,
                               const Workspace& ws, cudaStream_t st, int* launches);
 cudaError_t launch_peak_filter(const float* heat, int B, int C, int H, int W, int K, int lists, const Plan& plan,
-                               const Workspace& ws, cudaStream_t st, int* launches);
+                               const Workspace& ws, const MergeJob* raw_job, const MergeJob* nms_job,
+                               cudaStream_t st, int* launches);
 cudaError_t launch_merge(const float* heat, int B, int C, int H, int W, int K, const Plan& plan,
                          const Workspace& ws, const MergeJob* raw_job, const MergeJob* nms_job, cudaStream_t st,
                          int* launches);

@@ -31,6 +31,7 @@
 
 #include "geometry.cuh"
 #include "kernels.cuh"
+#include "merge.cuh"
 #include "select.cuh"
 
 namespace cf {
@@ -337,7 +338,23 @@ __device__ __forceinline__ bool is_peak(const float* frame, int H, int W, uint32
 }
 
 constexpr int FT = 256;  // threads
-constexpr int FI = 8;    // vector items per thread
+constexpr int FI = 8;    // vector items per thread per batch
+constexpr int FWCAP = 128;  // nms'd candidates a warp stages per batch for the side-by-side 3x3 tests
+
+// warp-aggregated append of at most one survivor per lane
+__device__ __forceinline__ void append_survivors(bool pred, unsigned long long comp, uint32_t* ctr,
+                                                 unsigned long long* cand) {
+    const uint32_t bal = __ballot_sync(FULL, pred);
+    if (!bal) return;
+    const int lane = threadIdx.x & 31, leader = __ffs(bal) - 1;
+    uint32_t base = 0u;
+    if (lane == leader) base = atomicAdd(ctr, (uint32_t)__popc(bal));
+    base = __shfl_sync(FULL, base, leader);
+    if (pred) {
+        const uint32_t slot = base + __popc(bal & lanemask_lt());
+        if (slot < (uint32_t)CAND_CAP) cand[slot] = comp;  // the counter keeps counting: overflow is detectable
+    }
+}
 
 // warp-aggregated append of each lane's survivors (bit k*VEC+j of `mask` = pixel j of item k) to a frame list:
 // one atomic per warp; the counter keeps counting past CAND_CAP so that overflow is detectable
@@ -367,10 +384,82 @@ __device__ __forceinline__ void warp_append(uint32_t mask, const float* frame, u
     }
 }
 
-// VEC = 4: the frame is read as float4 (frame size and base 16-byte aligned); VEC = 1: scalar fallback
+// tau of both lists in one go (see tau_scan): the two scans share their barriers.  tau[l] = 0 -> "everything".
+template <int T>
+__device__ __forceinline__ void tau_scan2(const uint32_t* gh, const uint32_t* ctr, int K, bool want0, bool want1,
+                                          uint32_t* s_scan /* 2*(T/32+1) */, uint32_t tau[2]) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = T / 32;
+    const bool want[2] = {want0, want1};
+    uint32_t top[2], carry[2] = {0u, 0u};
+    bool done[2];
+#pragma unroll
+    for (int l = 0; l < 2; ++l) {
+        top[l] = want[l] ? __ldg(ctr + l * CTR_STRIDE + 2) : 0u;
+        done[l] = !want[l];
+        tau[l] = 0u;
+    }
+    for (int round = 0; !(done[0] && done[1]); ++round) {
+        uint32_t c[2], inc[2];
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            const int bin = (int)top[l] - (round * T + tid);
+            c[l] = (!done[l] && bin >= 0) ? __ldg(gh + l * HIST_BINS + bin) : 0u;
+        }
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            inc[l] = c[l];  // inclusive prefix over tid = over descending bins
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const uint32_t o = __shfl_up_sync(FULL, inc[l], off);
+                if (lane >= off) inc[l] += o;
+            }
+            if (lane == 31) s_scan[l * (NW + 1) + warp] = inc[l];
+            if (tid == 0) s_scan[l * (NW + 1) + NW] = 0xffffffffu;
+        }
+        __syncthreads();
+        uint32_t total[2];
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            uint32_t below = carry[l];
+            total[l] = carry[l];
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                const uint32_t t = s_scan[l * (NW + 1) + w];
+                if (w < warp) below += t;
+                total[l] += t;
+            }
+            inc[l] += below;
+            const int bin = (int)top[l] - (round * T + tid);
+            if (!done[l] && inc[l] >= (uint32_t)K && inc[l] - c[l] < (uint32_t)K)
+                s_scan[l * (NW + 1) + NW] = (uint32_t)bin << HIST_SHIFT;  // exactly one thread
+        }
+        __syncthreads();
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            if (done[l]) continue;
+            const uint32_t found = s_scan[l * (NW + 1) + NW];
+            if (found != 0xffffffffu) {
+                tau[l] = found;
+                done[l] = true;
+            } else if ((int)top[l] - (round + 1) * T < 0) {
+                done[l] = true;  // histogram exhausted: fewer than K groups, tau stays 0
+            } else {
+                carry[l] = total[l];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// grid = (CTAs per frame, B).  VEC = 4: the frame is read as float4 (frame size and base 16-byte aligned);
+// VEC = 1: scalar fallback.  The last CTA of a frame to finish runs the frame's merge jobs.
 template <int VEC>
-__global__ void __launch_bounds__(FT) peak_filter_kernel(const PeakParams p) {
-    __shared__ uint32_t s_scan[FT / 32 + 1];
+__global__ void __launch_bounds__(FT) peak_filter_kernel(const PeakParams p, const MergeParams mp, int n_jobs) {
+    __shared__ uint32_t s_scan[2 * (FT / 32 + 1)];
+    __shared__ int s_last;
+    __shared__ uint32_t s_wbuf[FT / 32][FWCAP];
+    __shared__ MergeSmem msm;
     const int tid = threadIdx.x;
     const int b = blockIdx.y;
     const bool want_raw = (p.lists & LIST_RAW) != 0, want_nms = (p.lists & LIST_NMS) != 0;
@@ -380,62 +469,119 @@ __global__ void __launch_bounds__(FT) peak_filter_kernel(const PeakParams p) {
     uint32_t* ctr_raw = p.ctr + ((size_t)b * 2) * CTR_STRIDE;
     uint32_t* ctr_nms = ctr_raw + CTR_STRIDE;
     const float INF = CUDART_INF_F;
+    const bool rowvec = (p.W % 4) == 0;
+    // this CTA's contiguous share of the frame, in batches of FT*FI items
+    const uint32_t it_begin = (uint32_t)((unsigned long long)n_items * blockIdx.x / gridDim.x);
+    const uint32_t it_end = (uint32_t)((unsigned long long)n_items * (blockIdx.x + 1) / gridDim.x);
 
-    // this CTA's pixels first: the loads fly while tau is derived from the frame's histogram
-    const uint32_t item0 = blockIdx.x * (uint32_t)(FT * FI) + (uint32_t)tid;
+    auto load_batch = [&](uint32_t item0, float (&v)[FI][VEC]) {
+#pragma unroll
+        for (int k = 0; k < FI; ++k) {
+            const uint32_t i = item0 + (uint32_t)(k * FT);
+            if (VEC == 4) {
+                float4 q = make_float4(-INF, -INF, -INF, -INF);
+                if (i < it_end) q = __ldg(reinterpret_cast<const float4*>(frame) + i);
+                v[k][0] = q.x;
+                v[k][VEC > 1 ? 1 : 0] = q.y;
+                v[k][VEC > 2 ? 2 : 0] = q.z;
+                v[k][VEC > 3 ? 3 : 0] = q.w;
+            } else {
+                v[k][0] = i < it_end ? __ldg(frame + i) : -INF;
+            }
+        }
+    };
+
+    // first batch in flight while tau is derived from the frame's histogram
     float v[FI][VEC];
+    load_batch(it_begin + (uint32_t)tid, v);
+    uint32_t tau_key[2];
+    tau_scan2<FT>(p.hist + (size_t)b * 2 * HIST_BINS, ctr_raw, p.K, want_raw, want_nms, s_scan, tau_key);
+    const float tau_raw = want_raw ? tau_key_to_float(tau_key[0]) : INF;
+    float tau_nms = want_nms ? tau_key_to_float(tau_key[1]) : INF;
+    if (want_nms && !(tau_nms > 0.0f)) {
+        // fewer than K positive peaks: suppressed pixels (worth 0) belong to the top-K too -> the merge selects
+        // from the frame itself; flag the list as overflowed once
+        if (blockIdx.x == 0 && tid == 0) atomicAdd(ctr_nms, (uint32_t)CAND_CAP + 1u);
+        tau_nms = INF;
+    }
+
+    for (uint32_t base = it_begin; base < it_end; base += FT * FI) {
+        const uint32_t item0 = base + (uint32_t)tid;
+        if (base != it_begin) load_batch(item0, v);
+        uint32_t mraw = 0u, mcan = 0u;  // per-lane pixel masks: raw survivors, nms'd candidates awaiting the 3x3 test
 #pragma unroll
-    for (int k = 0; k < FI; ++k) {
-        const uint32_t i = item0 + (uint32_t)(k * FT);
-        if (VEC == 4) {
-            float4 q = make_float4(-INF, -INF, -INF, -INF);
-            if (i < n_items) q = __ldg(reinterpret_cast<const float4*>(frame) + i);
-            v[k][0] = q.x;
-            v[k][VEC > 1 ? 1 : 0] = q.y;
-            v[k][VEC > 2 ? 2 : 0] = q.z;
-            v[k][VEC > 3 ? 3 : 0] = q.w;
-        } else {
-            v[k][0] = i < n_items ? __ldg(frame + i) : -INF;
+        for (int k = 0; k < FI; ++k) {
+            const bool in = item0 + (uint32_t)(k * FT) < it_end;  // out-of-range items must not pass tau = -inf
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                if (in && v[k][j] >= tau_raw) mraw |= 1u << (k * VEC + j);
+                // a pixel with a larger left / right neighbour is suppressed: checked in registers when a float4
+                // lies inside one map row
+                bool can = in && v[k][j] >= tau_nms;
+                if (VEC == 4 && rowvec) {
+                    if (j > 0) can = can && !(v[k][j > 0 ? j - 1 : 0] > v[k][j]);
+                    if (j < VEC - 1) can = can && !(v[k][j < VEC - 1 ? j + 1 : 0] > v[k][j]);
+                }
+                if (can) mcan |= 1u << (k * VEC + j);
+            }
+        }
+        // almost every warp skips the rest: none of its 1 K pixels reaches either threshold
+        if (!__any_sync(FULL, (mraw | mcan) != 0u)) continue;
+        if (want_raw) warp_append<VEC>(mraw, frame, item0, ctr_raw, p.cand + (size_t)b * 2 * CAND_CAP);
+        if (!want_nms) continue;
+        // nms'd candidates: 3x3 suppression test straight from global memory (L2).  The warp's candidates are
+        // compacted into shared memory and spread over its lanes, so the tests run side by side.
+        unsigned long long* cand_nms = p.cand + ((size_t)b * 2 + 1) * CAND_CAP;
+        const int lane = tid & 31, warp = tid >> 5;
+        const uint32_t cnt = (uint32_t)__popc(mcan);
+        uint32_t inc = cnt;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t o = __shfl_up_sync(FULL, inc, off);
+            if (lane >= off) inc += o;
+        }
+        const uint32_t total = __shfl_sync(FULL, inc, 31);
+        if (total == 0u) continue;
+        if (total <= (uint32_t)FWCAP) {
+            uint32_t off = inc - cnt;
+            for (uint32_t m = mcan; m;) {
+                const int bit = __ffs(m) - 1;
+                m &= m - 1;
+                s_wbuf[warp][off++] = (item0 + (uint32_t)(bit / VEC) * FT) * VEC + (uint32_t)(bit % VEC);
+            }
+            __syncwarp();
+            for (uint32_t e0 = 0; e0 < total; e0 += 32) {
+                const uint32_t e = e0 + (uint32_t)lane;
+                const bool have = e < total;
+                const uint32_t gi = have ? s_wbuf[warp][e] : 0u;
+                const float x = __ldg(frame + gi);
+                const bool pk = have && is_peak(frame, p.H, p.W, gi, x);
+                append_survivors(pk, make_comp(f2key(x), gi), ctr_nms, cand_nms);
+            }
+            __syncwarp();
+        } else {  // (a warp full of candidates: plateaus) one lane at a time
+            uint32_t mnms = 0u;
+            for (uint32_t m = mcan; m;) {
+                const int bit = __ffs(m) - 1;
+                m &= m - 1;
+                const uint32_t gi = (item0 + (uint32_t)(bit / VEC) * FT) * VEC + (uint32_t)(bit % VEC);
+                if (is_peak(frame, p.H, p.W, gi, __ldg(frame + gi))) mnms |= 1u << bit;
+            }
+            warp_append<VEC>(mnms, frame, item0, ctr_nms, cand_nms);
         }
     }
 
-    const uint32_t* gh = p.hist + (size_t)b * 2 * HIST_BINS;
-    float tau_raw = INF, tau_nms = INF;
-    if (want_raw) tau_raw = tau_key_to_float(tau_scan<FT>(gh, ctr_raw[2], p.K, s_scan));
-    if (want_nms) {
-        tau_nms = tau_key_to_float(tau_scan<FT>(gh + HIST_BINS, ctr_nms[2], p.K, s_scan));
-        if (!(tau_nms > 0.0f)) {
-            // fewer than K positive peaks: suppressed pixels (worth 0) belong to the top-K too -> the merge
-            // selects from the frame itself; flag the list as overflowed once
-            if (blockIdx.x == 0 && tid == 0) atomicAdd(ctr_nms, (uint32_t)CAND_CAP + 1u);
-            tau_nms = INF;
-        }
+    // ---- merge tail: the last CTA of the frame to get here owns the complete survivor lists ----------------------
+    if (n_jobs == 0) return;
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        s_last = atomicAdd(ctr_raw + 1, 1u) == gridDim.x - 1;
     }
-    const float tau_min = fminf(tau_raw, tau_nms);
-
-    uint32_t mraw = 0u, mcan = 0u;  // per-lane pixel masks: raw survivors, nms'd candidates awaiting the 3x3 test
-#pragma unroll
-    for (int k = 0; k < FI; ++k) {
-        const bool in = item0 + (uint32_t)(k * FT) < n_items;  // out-of-range items must not pass tau = -inf
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-            if (in && v[k][j] >= tau_raw) mraw |= 1u << (k * VEC + j);
-            if (in && v[k][j] >= tau_nms) mcan |= 1u << (k * VEC + j);
-        }
-    }
-    // almost every warp ends here: none of its 1 K pixels reaches either threshold
-    if (!__any_sync(FULL, (mraw | mcan) != 0u)) return;
-    (void)tau_min;
-
-    uint32_t mnms = 0u;
-    for (uint32_t m = mcan; m;) {  // rare: 3x3 suppression test straight from global memory
-        const int bit = __ffs(m) - 1;
-        m &= m - 1;
-        const uint32_t gi = (item0 + (uint32_t)(bit / VEC) * FT) * VEC + (uint32_t)(bit % VEC);
-        if (is_peak(frame, p.H, p.W, gi, __ldg(frame + gi))) mnms |= 1u << bit;
-    }
-    if (want_raw) warp_append<VEC>(mraw, frame, item0, ctr_raw, p.cand + (size_t)b * 2 * CAND_CAP);
-    if (want_nms) warp_append<VEC>(mnms, frame, item0, ctr_nms, p.cand + ((size_t)b * 2 + 1) * CAND_CAP);
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    for (int li = 0; li < n_jobs; ++li) merge_frame<FT>(mp, msm, b, li);
 }
 
 cudaError_t launch_peak_clear(const Workspace& ws, cudaStream_t st) {
@@ -483,265 +629,10 @@ cudaError_t launch_peak_bound(const float* heat, int B, int C, int H, int W, int
 }
 
 cudaError_t launch_peak_filter(const float* heat, int B, int C, int H, int W, int K, int lists, const Plan& plan,
-                               const Workspace& ws, cudaStream_t st, int* launches) {
+                               const Workspace& ws, const MergeJob* raw_job, const MergeJob* nms_job,
+                               cudaStream_t st, int* launches) {
     PeakParams pp;
     fill_params(pp, heat, B, C, H, W, K, lists, plan, ws);
-    const long long n_px = (long long)C * H * W;
-    const bool vec = (n_px % 4 == 0) && ((reinterpret_cast<uintptr_t>(heat) & 15u) == 0);
-    const long long n_items = vec ? n_px / 4 : n_px;
-    const unsigned grid = (unsigned)((n_items + FT * FI - 1) / (FT * FI));
-    if (vec)
-        peak_filter_kernel<4><<<dim3(grid, B), FT, 0, st>>>(pp);
-    else
-        peak_filter_kernel<1><<<dim3(grid, B), FT, 0, st>>>(pp);
-    cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) ++*launches;
-    return e;
-}
-
-// -----------------------------------------------------------------------------------------------------
-// merge: frame-wide sorted top-K of the survivors + epilogue
-// -----------------------------------------------------------------------------------------------------
-constexpr int MT = 1024;
-
-struct ListSrc {
-    const unsigned long long* cand;
-    int n_in, n_round;
-    template <class F>
-    __device__ __forceinline__ void for_each(F&& f) const {
-        for (int i = threadIdx.x; i < n_round; i += MT) f(i < n_in ? __ldcg(cand + i) : 0ull);
-    }
-};
-
-// overflow path: the frame itself as the source (slow, exact; only reached under massive ties)
-struct FrameSrc {
-    const float* frame;
-    int CH, H, W, n_round;
-    bool nms;
-    template <class F>
-    __device__ __forceinline__ void for_each(F&& f) const {
-        const int n_in = CH * W;
-        for (int i = threadIdx.x; i < n_round; i += MT) {
-            unsigned long long c = 0ull;
-            if (i < n_in) {
-                const int g = i / W, x = i - g * W;
-                const float v = __ldg(frame + i);
-                uint32_t key = f2key(v);
-                if (nms) {
-                    const int py = g % H;
-                    float m = -CUDART_INF_F;
-                    for (int dy = -1; dy <= 1; ++dy) {
-                        if (py + dy < 0 || py + dy >= H) continue;
-                        for (int dx = -1; dx <= 1; ++dx) {
-                            if (x + dx < 0 || x + dx >= W) continue;
-                            m = fmaxf(m, __ldg(frame + (size_t)(g + dy) * W + x + dx));
-                        }
-                    }
-                    if (!(m == v)) key = KEY_ZERO;
-                }
-                c = make_comp(key, (uint32_t)i);
-            }
-            f(c);
-        }
-    }
-};
-
-struct MergeParams {
-    const float* heat;
-    int C, H, W, K;
-    const uint32_t* ctr;
-    const unsigned long long* cand;
-    int list[2];  // 0 = raw, 1 = nms'd
-    MergeJob job[2];
-    DetParam* det;
-};
-
-__device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const MergeJob& jb, int b, int k, int ind,
-                                                 int x, int y) {
-    const size_t HW = (size_t)p.H * p.W;
-    const FrustumHeads& fh = jb.fh;
-    // reference src/lib/utils/pointcloud.py:348-367
-    const float xf = __fadd_rn((float)x, 0.5f), yf = __fadd_rn((float)y, 0.5f);
-    float w = __ldg(fh.wh + ((size_t)b * 2 + 0) * HW + ind);
-    float h = __ldg(fh.wh + ((size_t)b * 2 + 1) * HW + ind);
-    if (w < 0.0f) w = 0.0f;
-    if (h < 0.0f) h = 0.0f;
-    const float hw2 = __fdiv_rn(w, 2.0f), hh2 = __fdiv_rn(h, 2.0f);
-    DetParam d;
-    d.x1 = __fsub_rn(xf, hw2);
-    d.y1 = __fsub_rn(yf, hh2);
-    d.x2 = __fadd_rn(xf, hw2);
-    d.y2 = __fadd_rn(yf, hh2);
-    float r[8], dm[3];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) r[j] = __ldg(fh.rot + ((size_t)b * 8 + j) * HW + ind);
-#pragma unroll
-    for (int j = 0; j < 3; ++j) dm[j] = __ldg(fh.dim + ((size_t)b * 3 + j) * HW + ind);
-    d.depth = __ldg(fh.depth + (size_t)b * HW + ind);
-    const float alpha = get_alpha(r);                                   // :372
-    const float cx = __fdiv_rn(__fadd_rn(d.x1, d.x2), 2.0f);            // :373-379
-    d.thr = dist_thresh_one(fh.calib + 12 * (size_t)b, cx, dm, alpha);  // :380
-    d.ind = ind;
-    d.pad_ = 0;
-    const size_t o = (size_t)b * p.K + k;
-    p.det[o] = d;
-    if (jb.fo.thr) jb.fo.thr[o] = d.thr;
-    if (jb.fo.inds) jb.fo.inds[o] = ind;
-}
-
-__device__ __forceinline__ void epilogue_decode(const MergeParams& p, const MergeJob& jb, int b, int k, float score,
-                                                int cls, int ind, int x, int y) {
-    // reference src/lib/model/decode.py:38-41, :80-85, :132-163
-    const size_t HW = (size_t)p.H * p.W;
-    const cf_decode_heads_t& hd = jb.dec.heads;
-    const cf_decode_out_t& o = jb.dec.out;
-    const size_t ok = (size_t)b * p.K + k;
-    if (hd.uncertainty) {
-        const float u = __ldg(hd.uncertainty + (size_t)b * HW + ind);
-        score = __fmul_rn(score, expf(-expf(u)));
-    }
-    o.scores[ok] = score;
-    o.class_ids[ok] = (float)cls;
-    const float xn = __fdiv_rn((float)x, (float)p.W), yn = __fdiv_rn((float)y, (float)p.H);
-    o.centers[2 * ok + 0] = xn;
-    o.centers[2 * ok + 1] = yn;
-    float xs = __fmul_rn(xn, (float)jb.dec.out_w), ys = __fmul_rn(yn, (float)jb.dec.out_h);
-    if (hd.reg) {
-        xs = __fadd_rn(xs, __ldg(hd.reg + ((size_t)b * 2 + 0) * HW + ind));
-        ys = __fadd_rn(ys, __ldg(hd.reg + ((size_t)b * 2 + 1) * HW + ind));
-    } else {
-        xs = __fadd_rn(xs, 0.5f);
-        ys = __fadd_rn(ys, 0.5f);
-    }
-    if (hd.wh) {
-        float w = __ldg(hd.wh + ((size_t)b * 2 + 0) * HW + ind);
-        float h = __ldg(hd.wh + ((size_t)b * 2 + 1) * HW + ind);
-        if (w < 0.0f) w = 0.0f;
-        if (h < 0.0f) h = 0.0f;
-        if (jb.dec.norm2d) {
-            w = __fmul_rn(w, (float)jb.dec.out_w);
-            h = __fmul_rn(h, (float)jb.dec.out_h);
-        }
-        const float hw2 = __fdiv_rn(w, 2.0f), hh2 = __fdiv_rn(h, 2.0f);
-        float4 bb;
-        bb.x = __fsub_rn(xs, hw2);
-        bb.y = __fsub_rn(ys, hh2);
-        bb.z = __fadd_rn(xs, hw2);
-        bb.w = __fadd_rn(ys, hh2);
-        o.bboxes[4 * ok + 0] = bb.x;
-        o.bboxes[4 * ok + 1] = bb.y;
-        o.bboxes[4 * ok + 2] = bb.z;
-        o.bboxes[4 * ok + 3] = bb.w;
-    }
-    if (hd.amodal) {  // :165 de-normalise
-        float ax = __ldg(hd.amodal + ((size_t)b * 2 + 0) * HW + ind);
-        float ay = __ldg(hd.amodal + ((size_t)b * 2 + 1) * HW + ind);
-        if (jb.dec.norm2d) {
-            ax = __fmul_rn(ax, (float)jb.dec.out_w);
-            ay = __fmul_rn(ay, (float)jb.dec.out_h);
-        }
-        o.amodal[2 * ok + 0] = ax;
-        o.amodal[2 * ok + 1] = ay;
-    }
-    if (hd.depth) o.depth[ok] = __ldg(hd.depth + (size_t)b * HW + ind);
-    if (o.inds) o.inds[ok] = ind;
-}
-
-// plain channel copies of the decode heads, spread over the whole block: out[b,k,ch] = head[b,ch,ind_k]
-__device__ __forceinline__ void copy_head(const float* head, float* out, int nch, int b, int K, size_t HW,
-                                          const int* sind) {
-    if (!head) return;
-    for (int t = threadIdx.x; t < K * nch; t += MT) {
-        const int k = t / nch, ch = t - k * nch;
-        out[((size_t)b * K + k) * nch + ch] = __ldg(head + ((size_t)b * nch + ch) * HW + sind[k]);
-    }
-}
-
-__global__ void __launch_bounds__(MT) merge_kernel(const MergeParams p) {
-    __shared__ SelScratch sc;
-    __shared__ unsigned long long win[MT];
-    __shared__ unsigned long long sorted[CF_MAX_K];
-    __shared__ int sind[CF_MAX_K];
-    const int tid = threadIdx.x;
-    const int b = blockIdx.x, li = blockIdx.y;
-    const MergeJob& jb = p.job[li];
-    const int list = p.list[li];
-    const int K = p.K;
-    const int HWi = p.H * p.W;
-    const uint32_t n = __ldcg(p.ctr + ((size_t)b * 2 + list) * CTR_STRIDE);  // survivors appended (>= K by construction)
-    const unsigned long long* cand = p.cand + ((size_t)b * 2 + list) * CAND_CAP;
-
-    int nw;  // entries of win[] to rank
-    if (n <= (uint32_t)MT) {
-        win[tid] = tid < (int)n ? __ldcg(cand + tid) : 0ull;
-        nw = (int)n;
-        __syncthreads();
-    } else {
-        if (n <= (uint32_t)CAND_CAP) {
-            ListSrc src;
-            src.cand = cand;
-            src.n_in = (int)n;
-            src.n_round = (src.n_in + MT - 1) / MT * MT;
-            block_select<MT, 1>(src, K, sc, [&](uint32_t slot, unsigned long long c) { win[slot] = c; });
-        } else {
-            FrameSrc src;
-            src.frame = p.heat + (size_t)b * p.C * HWi;
-            src.CH = p.C * p.H;
-            src.H = p.H;
-            src.W = p.W;
-            src.n_round = (p.C * HWi + MT - 1) / MT * MT;
-            src.nms = list == 1;
-            block_select<MT, 1>(src, K, sc, [&](uint32_t slot, unsigned long long c) { win[slot] = c; });
-        }
-        nw = K;
-        __syncthreads();
-    }
-
-    // rank by counting (composites are distinct: ranks are a permutation); the K best land in sorted[]
-    if (tid < nw) {
-        const unsigned long long me = win[tid];
-        int rank = 0;
-        for (int j = 0; j < nw; ++j) rank += (win[j] > me) ? 1 : 0;
-        if (rank < K) sorted[rank] = me;
-    }
-    __syncthreads();
-
-    if (tid < K) {
-        const unsigned long long c = sorted[tid];
-        const uint32_t g = comp_gidx(c), key = comp_key(c);
-        const int cls = (int)(g / (uint32_t)HWi);
-        const int ind = (int)(g - (uint32_t)cls * (uint32_t)HWi);
-        const int y = ind / p.W, x = ind - y * p.W;
-        sind[tid] = ind;
-        float score = key2f(key);
-        if (key == KEY_ZERO) score = __fmul_rn(__ldg(p.heat + ((size_t)b * p.C + cls) * HWi + ind), 0.0f);
-        const size_t o = (size_t)b * K + tid;
-        if (jb.epilogue == EPI_TOPK) {
-            if (jb.topk.scores) jb.topk.scores[o] = score;
-            if (jb.topk.inds) jb.topk.inds[o] = ind;
-            if (jb.topk.classes) jb.topk.classes[o] = cls;
-            if (jb.topk.ys) jb.topk.ys[o] = y;
-            if (jb.topk.xs) jb.topk.xs[o] = x;
-        } else if (jb.epilogue == EPI_FRUSTUM) {
-            epilogue_frustum(p, jb, b, tid, ind, x, y);
-        } else if (jb.epilogue == EPI_DECODE) {
-            epilogue_decode(p, jb, b, tid, score, cls, ind, x, y);
-        }
-    }
-    if (jb.epilogue == EPI_DECODE) {
-        __syncthreads();
-        const size_t HW = (size_t)HWi;
-        copy_head(jb.dec.heads.rot, jb.dec.out.rot, 8, b, K, HW, sind);
-        copy_head(jb.dec.heads.dim, jb.dec.out.dim, 3, b, K, HW, sind);
-        copy_head(jb.dec.heads.nuscenes_att, jb.dec.out.nuscenes_att, 8, b, K, HW, sind);
-        copy_head(jb.dec.heads.velocity, jb.dec.out.velocity, 3, b, K, HW, sind);
-    }
-}
-
-cudaError_t launch_merge(const float* heat, int B, int C, int H, int W, int K, const Plan& plan,
-                         const Workspace& ws, const MergeJob* raw_job, const MergeJob* nms_job, cudaStream_t st,
-                         int* launches) {
-    (void)plan;
     MergeParams mp;
     mp.heat = heat;
     mp.C = C;
@@ -762,11 +653,73 @@ cudaError_t launch_merge(const float* heat, int B, int C, int H, int W, int K, c
         mp.job[n] = *nms_job;
         ++n;
     }
-    if (n == 0) return cudaSuccess;
+    if (n < 2) {
+        mp.list[1] = mp.list[0];
+        mp.job[1] = mp.job[0];
+    }
+    const long long n_px = (long long)C * H * W;
+    const bool vec = (n_px % 4 == 0) && ((reinterpret_cast<uintptr_t>(heat) & 15u) == 0);
+    const long long n_items = vec ? n_px / 4 : n_px;
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // CTAs per frame: two per SM over the batch, at least one batch of items each
+    long long cpf = (2ll * sms) / B;
+    const long long max_cpf = (n_items + FT * FI - 1) / (FT * FI);
+    if (cpf > max_cpf) cpf = max_cpf;
+    if (cpf < 1) cpf = 1;
+    if (vec)
+        peak_filter_kernel<4><<<dim3((unsigned)cpf, B), FT, 0, st>>>(pp, mp, n);
+    else
+        peak_filter_kernel<1><<<dim3((unsigned)cpf, B), FT, 0, st>>>(pp, mp, n);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) ++*launches;
+    return e;
+}
+
+// -----------------------------------------------------------------------------------------------------
+// merge as its own kernel: one CTA of 1024 threads per (frame, job) -- the two jobs of a frame run side by side
+// -----------------------------------------------------------------------------------------------------
+constexpr int MT = 1024;
+__global__ void __launch_bounds__(MT) merge_kernel(const MergeParams p) {
+    __shared__ MergeSmem msm;
+    merge_frame<MT>(p, msm, blockIdx.x, blockIdx.y);
+}
+
+static int fill_merge(MergeParams& mp, const float* heat, int C, int H, int W, int K, const Workspace& ws,
+                      const MergeJob* raw_job, const MergeJob* nms_job) {
+    mp.heat = heat;
+    mp.C = C;
+    mp.H = H;
+    mp.W = W;
+    mp.K = K;
+    mp.ctr = ws.ctr;
+    mp.cand = ws.cand;
+    mp.det = ws.det;
+    int n = 0;
+    if (raw_job) {
+        mp.list[n] = 0;
+        mp.job[n] = *raw_job;
+        ++n;
+    }
+    if (nms_job) {
+        mp.list[n] = 1;
+        mp.job[n] = *nms_job;
+        ++n;
+    }
     if (n == 1) {
         mp.list[1] = mp.list[0];
         mp.job[1] = mp.job[0];
     }
+    return n;
+}
+
+cudaError_t launch_merge(const float* heat, int B, int C, int H, int W, int K, const Plan& plan,
+                         const Workspace& ws, const MergeJob* raw_job, const MergeJob* nms_job, cudaStream_t st,
+                         int* launches) {
+    (void)plan;
+    MergeParams mp;
+    const int n = fill_merge(mp, heat, C, H, W, K, ws, raw_job, nms_job);
+    if (n == 0) return cudaSuccess;
     merge_kernel<<<dim3(B, n), MT, 0, st>>>(mp);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) ++*launches;
