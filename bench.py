@@ -365,7 +365,9 @@ def main() -> int:
         n_roof = min(args.steps, 100)
         flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device=dev)
         L = _lib.lib()
-        kernel_ids = {"peak_bound": 0, "peak_filter": 5, "merge": 1, "assoc": 2, "paint": 3}
+        legacy = bool(os.environ.get("CFD3D_LEGACY"))
+        kernel_ids = ({"peak_bound": 0, "peak_filter": 5, "merge": 1, "assoc": 2, "paint": 3} if legacy
+                      else {"fusion_stage": 6})
         kernel_us = {}
         for kname, kid in kernel_ids.items():
             pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_roof)]
@@ -387,7 +389,8 @@ def main() -> int:
                 stream.synchronize()
             d = np.array([a.elapsed_time(b) for a, b in pairs]) * 1e3
             kernel_us[kname] = {"mean": float(d.mean()), "min": float(d.min()), "median": float(np.median(d))}
-        dur = kernel_us["peak_bound"]["mean"] * 1e-6
+        dom = "peak_bound" if legacy else "fusion_stage"
+        dur = kernel_us[dom]["mean"] * 1e-6
         peaks = {}
         pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         peak, peak_src = 6650.0, "fallback"
@@ -397,7 +400,8 @@ def main() -> int:
                 peak, peak_src = float(peaks["hbm_gbs"]), "measured"
             except Exception:
                 pass
-        alg = peak_select_bytes_per_frame(wl) * B
+        # the fused kernel is the whole stage (SURVEY.md 8d bytes per frame, pillar bytes excluded: separate kernels)
+        alg = (peak_select_bytes_per_frame(wl) if legacy else algorithmic_bytes_per_frame(wl, False)) * B
         ach = alg / dur / 1e9
         stage_alg = algorithmic_bytes_per_frame(wl, wl.with_pillars) * B
         stage_ach = stage_alg / (ms_max * 1e-3 / args.steps) / 1e9
@@ -405,10 +409,10 @@ def main() -> int:
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.isfile(tpath):
             try:
-                traffic = json.load(open(tpath)).get(wl.name, {}).get("peak_select_dram_bytes_per_launch")
+                traffic = json.load(open(tpath)).get(wl.name, {}).get("dominant_kernel_dram_bytes_per_launch")
             except Exception:
                 traffic = None
-        roof = {"bound": "hbm", "kernel": "peak_bound_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
+        roof = {"bound": "hbm", "kernel": dom + "_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
                 "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg, "kernel_us": dur * 1e6,
                 "launches_timed": n_roof, "l2": "flushed before every timed launch (252 MB fill)",

@@ -73,24 +73,14 @@ static int check_ws(void* ws, size_t ws_bytes, size_t need) {
 }
 static bool misaligned4(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 3u) != 0; }
 
-// clear [hist|ctr], bound pass (the HBM read of the heat-map), filter pass
-// (the filter pass ends with the per-frame merge: sorted top-K + the jobs' epilogues)
-static int run_peak_passes(const float* heat, int B, int C, int H, int W, int K, const MergeJob* raw_job,
-                           const MergeJob* nms_job, const Plan& plan, const Workspace& w, cudaStream_t st, int* n,
-                           int stop = 1 << 30) {
-    const int lists = (raw_job ? LIST_RAW : 0) | (nms_job ? LIST_NMS : 0);
-    CF_CUDA(launch_peak_clear(w, st), "peak_clear");
-    CF_KERNEL(CF_KERNEL_PEAK_SELECT, st, launch_peak_bound(heat, B, C, H, W, K, lists, plan, w, st, n), "peak_bound");
-    if (*n >= stop) return 0;
-    // CFD3D_FUSE_MERGE=1: the last filter CTA of a frame runs the frame's merge jobs (one launch less; slower at
-    // the reference sizes because the two jobs then run back to back on 256 threads)
-    static const bool fuse = getenv("CFD3D_FUSE_MERGE") && atoi(getenv("CFD3D_FUSE_MERGE")) != 0;
-    CF_KERNEL(CF_KERNEL_PEAK_FILTER, st,
-              launch_peak_filter(heat, B, C, H, W, K, lists, plan, w, fuse ? raw_job : nullptr,
-                                 fuse ? nms_job : nullptr, st, n),
-              "peak_filter");
-    if (*n >= stop || fuse) return 0;
-    CF_KERNEL(CF_KERNEL_MERGE, st, launch_merge(heat, B, C, H, W, K, plan, w, raw_job, nms_job, st, n), "merge");
+// the peak passes + merge jobs without the frustum tail (cf_peak_topk, cf_fusion_decode)
+static int run_peak_passes(const float* heat, int B, int C, int H, int W, int K, MergeJob* raw_job, MergeJob* nms_job,
+                           const Workspace& w, cudaStream_t st, int* n) {
+    if (raw_job) finish_job(raw_job);
+    if (nms_job) finish_job(nms_job);
+    CF_KERNEL(CF_KERNEL_STAGE, st,
+              launch_fusion_stage(heat, B, C, H, W, K, w, raw_job, nms_job, nullptr, 0.0f, nullptr, nullptr, st, n),
+              "fusion_stage");
     return 0;
 }
 
@@ -111,10 +101,13 @@ int cf_set_kernel_events(int kernel_id, void* ev_start, void* ev_stop) {
     return 0;
 }
 
+__attribute__((visibility("default"))) int cf_debug_read_prof(long long* out_host, int n_cta) {
+    return debug_read_prof(out_host, n_cta);
+}
+
 size_t cf_workspace_bytes(int B, int C, int H, int W, int K) {
-    Plan plan;
-    if (B < 0 || C < 1 || H < 1 || W < 1 || K < 1 || K > CF_MAX_K || !make_plan(C, H, W, K, &plan)) return 0;
-    return workspace_layout(B, C, H, W, K, plan, nullptr, nullptr) + 256;
+    if (B < 0 || C < 1 || H < 1 || W < 1 || K < 1 || K > CF_MAX_K) return 0;
+    return workspace_layout(B, K, nullptr, nullptr) + 256;
 }
 
 size_t cf_pillars_workspace_bytes(int B, int Nmax) {
@@ -174,10 +167,8 @@ int cf_peak_topk(const float* heat, int B, int C, int H, int W, int K, int apply
     if (int rc = check_dims(B, C, H, W)) return rc;
     if (int rc = check_k(K, H, W)) return rc;
     if (misaligned4(heat)) return fail(CF_E_ALIGN, "cf_peak_topk: heat not 4-byte aligned");
-    Plan plan;
-    if (!make_plan(C, H, W, K, &plan)) return fail(CF_E_SHAPE, "cf_peak_topk: unsupported map geometry %dx%d", H, W);
     Workspace w;
-    const size_t need = workspace_layout(B, C, H, W, K, plan, ws, &w);
+    const size_t need = workspace_layout(B, K, ws, &w);
     if (int rc = check_ws(ws, ws_bytes, need)) return rc;
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
@@ -186,8 +177,7 @@ int cf_peak_topk(const float* heat, int B, int C, int H, int W, int K, int apply
     memset(&job, 0, sizeof(job));
     job.epilogue = EPI_TOPK;
     job.topk = TopkOut{scores, inds, classes, ys, xs};
-    if (int rc = run_peak_passes(heat, B, C, H, W, K, apply_nms ? nullptr : &job, apply_nms ? &job : nullptr, plan, w, st,
-                                 &n))
+    if (int rc = run_peak_passes(heat, B, C, H, W, K, apply_nms ? nullptr : &job, apply_nms ? &job : nullptr, w, st, &n))
         return rc;
     g_launches = n;
     return 0;
@@ -228,10 +218,8 @@ int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W,
     if (int rc = check_decode_args(heads, out)) return rc;
     if (int rc = check_dims(B, C, H, W)) return rc;
     if (int rc = check_k(K, H, W)) return rc;
-    Plan plan;
-    if (!make_plan(C, H, W, K, &plan)) return fail(CF_E_SHAPE, "decode: unsupported map geometry %dx%d", H, W);
     Workspace w;
-    const size_t need = workspace_layout(B, C, H, W, K, plan, ws, &w);
+    const size_t need = workspace_layout(B, K, ws, &w);
     if (int rc = check_ws(ws, ws_bytes, need)) return rc;
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
@@ -244,7 +232,7 @@ int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W,
     job.dec.out_h = out_h;
     job.dec.out_w = out_w;
     job.dec.norm2d = norm2d;
-    if (int rc = run_peak_passes(heads->heatmap, B, C, H, W, K, nullptr, &job, plan, w, st, &n)) return rc;
+    if (int rc = run_peak_passes(heads->heatmap, B, C, H, W, K, nullptr, &job, w, st, &n)) return rc;
     g_launches = n;
     return 0;
 }
@@ -265,21 +253,12 @@ int cf_fusion_stage(const float* heat, const float* wh, const float* depth, cons
     }
     if (int rc = check_dims(B, C, H, W)) return rc;
     if (int rc = check_k(K, H, W)) return rc;
-    Plan plan;
-    if (!make_plan(C, H, W, K, &plan)) return fail(CF_E_SHAPE, "frustum: unsupported map geometry %dx%d", H, W);
     Workspace w;
-    const size_t need = workspace_layout(B, C, H, W, K, plan, ws, &w);
+    const size_t need = workspace_layout(B, K, ws, &w);
     if (int rc = check_ws(ws, ws_bytes, need)) return rc;
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
-    // development aid: CFD3D_STOP_AFTER=<n> ends the call after n kernels (cumulative in-pipeline timings)
-    int stop = 1 << 30;
-    if (const char* e = getenv("CFD3D_STOP_AFTER")) stop = atoi(e);
-    if (stop == 0) {
-        CF_CUDA(launch_peak_clear(w, st), "peak_clear");
-        return 0;
-    }
     MergeJob fj, dj;
     memset(&fj, 0, sizeof(fj));
     memset(&dj, 0, sizeof(dj));
@@ -294,11 +273,12 @@ int cf_fusion_stage(const float* heat, const float* wh, const float* depth, cons
         dj.dec.out_w = out_w;
         dj.dec.norm2d = norm2d;
     }
-    if (int rc = run_peak_passes(heat, B, C, H, W, K, &fj, with_decode ? &dj : nullptr, plan, w, st, &n, stop)) return rc;
-    if (n >= stop) return 0;
-    CF_KERNEL(CF_KERNEL_ASSOC, st, launch_assoc(pc_dep, B, H, W, K, max_pc_dist, w, assoc, st, &n), "assoc");
-    if (n >= stop) return 0;
-    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint(w.recs, K, K, nullptr, B, H, W, pc_hm, nullptr, st, &n), "paint");
+    finish_job(&fj);
+    if (with_decode) finish_job(&dj);
+    CF_KERNEL(CF_KERNEL_STAGE, st,
+              launch_fusion_stage(heat, B, C, H, W, K, w, &fj, with_decode ? &dj : nullptr, pc_dep, max_pc_dist, pc_hm,
+                                  assoc, st, &n),
+              "fusion_stage");
     g_launches = n;
     return 0;
 }

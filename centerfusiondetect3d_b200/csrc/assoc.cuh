@@ -18,11 +18,12 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
 }
 
 // ROI + threshold test + first-minimum search (pointcloud.py:424-461) by NT cooperating threads (`t` of NT, NT a
-// multiple of 32 or the whole block); the caller reduces the returned key with a minimum.  Key = (depth bits,
+// multiple of 32 or the whole block); the caller reduces the returned key with a minimum.  `dep` = the frame's depth
+// plane pc_dep[b,0] in global OR shared memory (generic loads: the fused stage kernel stages it).  Key = (depth bits,
 // flat pixel): depths that pass are positive, so the bit pattern orders like the value and the minimum key is
 // the first minimum in row-major ROI order.  Lanes run over columns, rows are unrolled: independent loads, no
 // division.
-__device__ __forceinline__ unsigned long long roi_scan(const float* __restrict__ dep, int H, int W, float x1, float y1,
+__device__ __forceinline__ unsigned long long roi_scan(const float* dep, int H, int W, float x1, float y1,
                                                        float x2, float y2, float depth, float thr, int t, int NT) {
     int ya, yb, xa, xb;
     pyslice((long long)floorf(y1), (long long)ceilf(y2) + 1, H, ya, yb);
@@ -46,7 +47,7 @@ __device__ __forceinline__ unsigned long long roi_scan(const float* __restrict__
             for (int u = 0; u < U; ++u) {
                 const int yy = y0 + u * rows_par;
                 const int yc = yy < yb ? yy : ya;  // clamped: the load is unconditional, 0 fails the test below
-                const float t_ = __ldg(dep + (size_t)yc * W + xx);
+                const float t_ = dep[(size_t)yc * W + xx];
                 v[u] = yy < yb ? t_ : 0.0f;
             }
 #pragma unroll
@@ -75,14 +76,11 @@ __device__ __forceinline__ void paint_window(float x1, float y1, float x2, float
     pyslice(wmin, wmax + 2, W, ca, cb);
 }
 
-// One detection, one warp: association + paint record.  dep = the frame's pc_dep (3,H,W).
-__device__ __forceinline__ void assoc_one(const float* __restrict__ dep, int H, int W, const DetParam& d,
-                                          float max_pc_dist, PaintRec* rec_out, int32_t* assoc_out) {
-    const int lane = threadIdx.x & 31;
+// The matched pixel of one detection -> paint record + association index (one thread).  best = the reduced roi_scan
+// key (~0 = no radar pixel in range), dep = the frame's pc_dep (3,H,W) in global memory (velocity channels).
+__device__ __forceinline__ PaintRec assoc_finalize(unsigned long long best, const float* __restrict__ dep, int H, int W,
+                                                   const DetParam& d, float max_pc_dist, int32_t* assoc_out) {
     const size_t HW = (size_t)H * W;
-    const unsigned long long best =
-        warp_min_u64(roi_scan(dep, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32));
-    if (lane != 0) return;
     PaintRec r;
     r.ra = r.rb = r.ca = r.cb = 0;
     r.v0 = r.v1 = r.v2 = 0.0f;
@@ -103,8 +101,8 @@ __device__ __forceinline__ void assoc_one(const float* __restrict__ dep, int H, 
             r.cb = (int16_t)cb;
         }
     }
-    *rec_out = r;
     if (assoc_out) *assoc_out = a;
+    return r;
 }
 
 }  // namespace cf

@@ -15,34 +15,9 @@
 #include "assoc.cuh"
 #include "geometry.cuh"
 #include "kernels.cuh"
+#include "paint.cuh"
 
 namespace cf {
-
-// -----------------------------------------------------------------------------------------------------
-// association: one warp per detection
-// -----------------------------------------------------------------------------------------------------
-constexpr int AW = 8;  // warps (detections) per CTA
-
-__global__ void __launch_bounds__(AW * 32) assoc_kernel(const float* __restrict__ pc_dep, int H, int W, int K,
-                                                        float max_pc_dist, const DetParam* __restrict__ det,
-                                                        PaintRec* __restrict__ recs, int32_t* __restrict__ assoc) {
-    const int warp = threadIdx.x >> 5;
-    const int k = blockIdx.x * AW + warp;
-    const int b = blockIdx.y;
-    if (k >= K) return;
-    const size_t o = (size_t)b * K + k;
-    const DetParam d = det[o];
-    assoc_one(pc_dep + (size_t)b * 3 * H * W, H, W, d, max_pc_dist, recs + o, assoc ? assoc + o : nullptr);
-}
-
-cudaError_t launch_assoc(const float* pc_dep, int B, int H, int W, int K, float max_pc_dist, const Workspace& ws,
-                         int32_t* assoc, cudaStream_t st, int* launches) {
-    assoc_kernel<<<dim3((K + AW - 1) / AW, B), AW * 32, 0, st>>>(pc_dep, H, W, K, max_pc_dist, ws.det, ws.recs,
-                                                                  assoc);
-    cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) ++*launches;
-    return e;
-}
 
 // -----------------------------------------------------------------------------------------------------
 // ordered rectangle paint: out (B,3,H,W) written completely; largest record index wins per pixel
@@ -53,85 +28,14 @@ __global__ void __launch_bounds__(PT) paint_kernel(const PaintRec* __restrict__ 
                                                    const int32_t* __restrict__ counts, int H, int W, int rows_per_cta,
                                                    float* __restrict__ out, int32_t* __restrict__ owner_out) {
     extern __shared__ int sown[];  // rows_per_cta x W owner indices
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.y;
     const int y0 = blockIdx.x * rows_per_cta;
     const int y1 = min(H, y0 + rows_per_cta);
-    const int npx = (y1 - y0) * W;
     int n = n_max;
     if (counts) n = min(n_max, counts[b]);
-    for (int i = tid; i < npx; i += PT) sown[i] = -1;
-    __syncthreads();
-
-    const PaintRec* fr = recs + (size_t)b * rec_stride;
-    for (int base = warp * 32; base < n; base += (PT / 32) * 32) {
-        const int k = base + lane;
-        int ra = 0, rb = 0, ca = 0, cb = 0;
-        if (k < n) {
-            const short4 q = __ldg(reinterpret_cast<const short4*>(fr + k));
-            ra = q.x;
-            rb = q.y;
-            ca = q.z;
-            cb = q.w;
-        }
-        const bool hit = rb > ra && cb > ca && ra < y1 && rb > y0;
-        uint32_t m = __ballot_sync(FULL, hit);
-        while (m) {
-            const int bit = __ffs(m) - 1;
-            m &= m - 1;
-            const int qa = max(__shfl_sync(FULL, ra, bit), y0), qb = min(__shfl_sync(FULL, rb, bit), y1);
-            const int xa = __shfl_sync(FULL, ca, bit), xb = __shfl_sync(FULL, cb, bit);
-            const int w = xb - xa;
-            const int cnt = (qb - qa) * w;
-            for (int t = lane; t < cnt; t += 32) {
-                const int ry = t / w;
-                atomicMax(&sown[(qa - y0 + ry) * W + xa + (t - ry * w)], base + bit);
-            }
-        }
-    }
-    __syncthreads();
-
     const size_t HW = (size_t)H * W;
-    float* o0 = out + ((size_t)b * 3) * HW + (size_t)y0 * W;
-    int32_t* oo = owner_out ? owner_out + (size_t)b * HW + (size_t)y0 * W : nullptr;
-    const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(out) & 15u) == 0) &&
-                     (!owner_out || (reinterpret_cast<uintptr_t>(owner_out) & 15u) == 0);
-    if (vec) {
-        for (int i = tid * 4; i < npx; i += PT * 4) {
-            const int4 ow = *reinterpret_cast<const int4*>(sown + i);
-            const int os[4] = {ow.x, ow.y, ow.z, ow.w};
-            float v[3][4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                v[0][j] = v[1][j] = v[2][j] = 0.0f;
-                if (os[j] >= 0) {
-                    const PaintRec* r = fr + os[j];
-                    v[0][j] = __ldg(&r->v0);
-                    v[1][j] = __ldg(&r->v1);
-                    v[2][j] = __ldg(&r->v2);
-                }
-            }
-#pragma unroll
-            for (int c = 0; c < 3; ++c)
-                *reinterpret_cast<float4*>(o0 + c * HW + i) = make_float4(v[c][0], v[c][1], v[c][2], v[c][3]);
-            if (oo) *reinterpret_cast<int4*>(oo + i) = ow;
-        }
-    } else {
-        for (int i = tid; i < npx; i += PT) {
-            const int ow = sown[i];
-            float v0 = 0.0f, v1 = 0.0f, v2 = 0.0f;
-            if (ow >= 0) {
-                const PaintRec* r = fr + ow;
-                v0 = __ldg(&r->v0);
-                v1 = __ldg(&r->v1);
-                v2 = __ldg(&r->v2);
-            }
-            o0[i] = v0;
-            o0[HW + i] = v1;
-            o0[2 * HW + i] = v2;
-            if (oo) oo[i] = ow;
-        }
-    }
+    paint_band<PT, false>(recs + (size_t)b * rec_stride, n, H, W, y0, y1, out + (size_t)b * 3 * HW,
+                   owner_out ? owner_out + (size_t)b * HW : nullptr, sown, rows_per_cta);
 }
 
 cudaError_t launch_paint(const PaintRec* recs, int n_per_frame, int rec_stride, const int32_t* counts, int B, int H,

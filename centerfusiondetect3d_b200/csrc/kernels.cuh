@@ -8,22 +8,10 @@
 
 namespace cf {
 
-// ---- launch plan of the two heat-map passes for one map geometry --------------------------------------
-// A frame is viewed as a (C*H) x W row matrix; a tile is R consecutive rows of it (+1 halo row each side).
-struct Plan {
-    int T;       // threads per CTA of the heat-map passes
-    int R;       // rows per tile
-    int NT;      // tiles per frame
-    int Wp;      // shared-memory row stride in floats (W rounded up to 4)
-    size_t smem; // dynamic shared memory of the heat-map passes
-};
-// returns false when the geometry is unsupported
-bool make_plan(int C, int H, int W, int K, Plan* p);
-
 constexpr int HIST_SHIFT = 20;                       // histogram bin = key >> HIST_SHIFT (sign, exponent, 3 mantissa bits)
 constexpr int HIST_BINS = 1 << (32 - HIST_SHIFT);    // 4096
 constexpr int CAND_CAP = 2048;                       // survivor slots per (frame, list)
-constexpr int CTR_STRIDE = 4;                        // per (frame, list): [0] survivors appended, [1] bound tiles done
+constexpr int CTR_STRIDE = 4;                        // per (frame, list): [0] survivors appended
 
 // per-detection frustum parameters, produced by the merge kernel, consumed by the association kernel
 struct __align__(16) DetParam {
@@ -44,16 +32,12 @@ struct __align__(16) PaintRec {
 static_assert(sizeof(PaintRec) == 32, "PaintRec");
 
 struct Workspace {
-    void* zero_base;            // [hist | ctr]: cleared by one memset at the start of every call
-    size_t zero_bytes;
-    uint32_t* hist;             // (B, 2, HIST_BINS) histogram of group maxima, list 0 = raw, 1 = nms'd
-    uint32_t* ctr;              // (B, 2, CTR_STRIDE)
-    uint32_t* tau;              // (B, 2) key threshold: every pixel of the frame's top-K has key >= tau
+    uint32_t* ctr;              // (B, 2, CTR_STRIDE) survivor counters, list 0 = raw, 1 = nms'd (cleared in-kernel)
     unsigned long long* cand;   // (B, 2, CAND_CAP) survivors (composites), unordered
     DetParam* det;              // (B, K)
     PaintRec* recs;             // (B, K)
 };
-size_t workspace_layout(int B, int C, int H, int W, int K, const Plan& plan, void* base, Workspace* out);
+size_t workspace_layout(int B, int K, void* base, Workspace* out);
 
 struct FrustumHeads {
     const float *wh, *depth, *dim, *rot, *calib;
@@ -75,6 +59,19 @@ struct DecodeArgs {
     int out_h, out_w, norm2d;
 };
 
+// head channels a merge job gathers at the K peak pixels: slot s reads base[s][(b*nch[s] + ch[s])*H*W + ind]
+// (base NULL = head absent).  Frustum slots: 0-1 wh, 2 depth, 3-5 dim, 6-13 rot.  Decode slots: 0-1 reg, 2-3 wh,
+// 4 depth, 5-12 rot, 13-15 dim, 16-17 amodal, 18-25 nuscenes_att, 26-28 velocity, 29 uncertainty.
+constexpr int MAX_GCH = 32;
+constexpr int GATH_STRIDE = 33;  // floats per detection in the shared-memory gather buffer (odd: conflict-free columns)
+struct GatherTab {
+    const float* base[MAX_GCH];
+    unsigned char nch[MAX_GCH], ch[MAX_GCH];
+    int n;
+};
+enum { FS_WH = 0, FS_DEPTH = 2, FS_DIM = 3, FS_ROT = 6, FS_N = 14 };
+enum { DS_REG = 0, DS_WH = 2, DS_DEPTH = 4, DS_ROT = 5, DS_DIM = 13, DS_AMODAL = 16, DS_ATT = 18, DS_VEL = 26, DS_UNC = 29, DS_N = 30 };
+
 enum { LIST_RAW = 1, LIST_NMS = 2 };
 enum { EPI_NONE = 0, EPI_TOPK = 1, EPI_FRUSTUM = 2, EPI_DECODE = 3 };
 
@@ -84,10 +81,13 @@ struct MergeJob {       // what the merge kernel does with one sorted list
     FrustumHeads fh;    // EPI_FRUSTUM
     FrustumOut fo;      // EPI_FRUSTUM
     DecodeArgs dec;     // EPI_DECODE
+    GatherTab gt;       // filled by finish_job() from fh / dec.heads
 };
+void finish_job(MergeJob* job);
 
 // what the merge tail of the filter pass does per frame: up to two jobs (raw list, nms'd list)
 struct MergeParams {
+    int prof;  // development aid (CFD3D_PROF)
     const float* heat;
     int C, H, W, K;
     const uint32_t* ctr;
@@ -98,19 +98,12 @@ struct MergeParams {
 };
 
 // ---- launchers (each returns the cudaError_t of its launch; *launches += kernels launched) ----------
-// the three steps of the peak decode ahead of the merge: clear [hist|ctr], bound pass (HBM read of the heat-map:
-// group maxima -> histogram -> tau), filter pass (re-read, L2-resident at the reference batch sizes: survivors)
-cudaError_t launch_peak_clear(const Workspace& ws, cudaStream_t st);
-cudaError_t launch_peak_bound(const float* heat, int B, int C, int H, int W, int K, int lists, const Plan& plan,
-                              const Workspace& ws, cudaStream_t st, int* launches);
-cudaError_t launch_peak_filter(const float* heat, int B, int C, int H, int W, int K, int lists, const Plan& plan,
-                               const Workspace& ws, const MergeJob* raw_job, const MergeJob* nms_job,
-                               cudaStream_t st, int* launches);
-cudaError_t launch_merge(const float* heat, int B, int C, int H, int W, int K, const Plan& plan,
-                         const Workspace& ws, const MergeJob* raw_job, const MergeJob* nms_job, cudaStream_t st,
-                         int* launches);
-cudaError_t launch_assoc(const float* pc_dep, int B, int H, int W, int K, float max_pc_dist, const Workspace& ws,
-                         int32_t* assoc, cudaStream_t st, int* launches);
+// the fused stage kernel (stage.cu): bound + filter + merge jobs (+ association + paint when raw_job is a frustum
+// job and pc_dep / pc_hm are given) in ONE launch, one thread-block cluster per frame
+cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, int K, const Workspace& ws,
+                                const MergeJob* raw_job, const MergeJob* nms_job, const float* pc_dep,
+                                float max_pc_dist, float* pc_hm, int32_t* assoc, cudaStream_t st, int* launches);
+int debug_read_prof(long long* out, int n_cta);
 cudaError_t launch_paint(const PaintRec* recs, int n_per_frame, int rec_stride, const int32_t* counts, int B, int H,
                          int W, float* out, int32_t* owner, cudaStream_t st, int* launches);
 cudaError_t launch_nms(const float* heat, int B, int C, int H, int W, float* out, cudaStream_t st, int* launches);

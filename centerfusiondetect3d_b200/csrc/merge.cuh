@@ -1,6 +1,10 @@
 // merge.cuh -- per-frame merge of the peak-decode survivors: exact sorted top-K under the total order
 // (score desc, class asc, index asc) + the topk / frustum / decode epilogue.  Device code, executed by ONE CTA of
-// T threads per (frame, list): the tail of the filter pass (last CTA of a frame to finish).
+// T threads per (frame, list) inside the fused stage kernel (stage.cu).
+//
+// Latency shape: the head values of the K peaks are gathered FIRST, all at once (every thread issues its loads
+// back to back into registers, then parks them in shared memory: one DRAM round trip for the whole job), the
+// epilogues then compute from shared memory and only store.
 //
 // Replaces (reference, src/lib/): model/utils.py:6-38 topk (second level), :41-72 transposeAndGetFeature; the
 // gathers + box / alpha / threshold block of utils/pointcloud.py:347-380; model/decode.py:47-172.
@@ -10,6 +14,10 @@
 #include "geometry.cuh"
 #include "kernels.cuh"
 #include "select.cuh"
+
+#ifndef CF_MERGE_PROF
+#define CF_MERGE_PROF(i) do { } while (0)
+#endif
 
 namespace cf {
 
@@ -60,192 +68,287 @@ struct FrameSrc {
     }
 };
 
-__device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const MergeJob& jb, int b, int k, int ind,
-                                                 int x, int y) {
-    const size_t HW = (size_t)p.H * p.W;
-    const FrustumHeads& fh = jb.fh;
-    // reference src/lib/utils/pointcloud.py:348-367
-    const float xf = __fadd_rn((float)x, 0.5f), yf = __fadd_rn((float)y, 0.5f);
-    float w = __ldg(fh.wh + ((size_t)b * 2 + 0) * HW + ind);
-    float h = __ldg(fh.wh + ((size_t)b * 2 + 1) * HW + ind);
-    if (w < 0.0f) w = 0.0f;
-    if (h < 0.0f) h = 0.0f;
-    const float hw2 = __fdiv_rn(w, 2.0f), hh2 = __fdiv_rn(h, 2.0f);
-    DetParam d;
-    d.x1 = __fsub_rn(xf, hw2);
-    d.y1 = __fsub_rn(yf, hh2);
-    d.x2 = __fadd_rn(xf, hw2);
-    d.y2 = __fadd_rn(yf, hh2);
-    float r[8], dm[3];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) r[j] = __ldg(fh.rot + ((size_t)b * 8 + j) * HW + ind);
-#pragma unroll
-    for (int j = 0; j < 3; ++j) dm[j] = __ldg(fh.dim + ((size_t)b * 3 + j) * HW + ind);
-    d.depth = __ldg(fh.depth + (size_t)b * HW + ind);
-    const float alpha = get_alpha(r);                                   // :372
-    const float cx = __fdiv_rn(__fadd_rn(d.x1, d.x2), 2.0f);            // :373-379
-    d.thr = dist_thresh_one(fh.calib + 12 * (size_t)b, cx, dm, alpha);  // :380
-    d.ind = ind;
-    d.pad_ = 0;
-    const size_t o = (size_t)b * p.K + k;
-    p.det[o] = d;
-    if (jb.fo.thr) jb.fo.thr[o] = d.thr;
-    if (jb.fo.inds) jb.fo.inds[o] = ind;
-}
-
-__device__ __forceinline__ void epilogue_decode(const MergeParams& p, const MergeJob& jb, int b, int k, float score,
-                                                int cls, int ind, int x, int y) {
-    // reference src/lib/model/decode.py:38-41, :80-85, :132-163
-    const size_t HW = (size_t)p.H * p.W;
-    const cf_decode_heads_t& hd = jb.dec.heads;
-    const cf_decode_out_t& o = jb.dec.out;
-    const size_t ok = (size_t)b * p.K + k;
-    if (hd.uncertainty) {
-        const float u = __ldg(hd.uncertainty + (size_t)b * HW + ind);
-        score = __fmul_rn(score, expf(-expf(u)));
-    }
-    o.scores[ok] = score;
-    o.class_ids[ok] = (float)cls;
-    const float xn = __fdiv_rn((float)x, (float)p.W), yn = __fdiv_rn((float)y, (float)p.H);
-    o.centers[2 * ok + 0] = xn;
-    o.centers[2 * ok + 1] = yn;
-    float xs = __fmul_rn(xn, (float)jb.dec.out_w), ys = __fmul_rn(yn, (float)jb.dec.out_h);
-    if (hd.reg) {
-        xs = __fadd_rn(xs, __ldg(hd.reg + ((size_t)b * 2 + 0) * HW + ind));
-        ys = __fadd_rn(ys, __ldg(hd.reg + ((size_t)b * 2 + 1) * HW + ind));
-    } else {
-        xs = __fadd_rn(xs, 0.5f);
-        ys = __fadd_rn(ys, 0.5f);
-    }
-    if (hd.wh) {
-        float w = __ldg(hd.wh + ((size_t)b * 2 + 0) * HW + ind);
-        float h = __ldg(hd.wh + ((size_t)b * 2 + 1) * HW + ind);
+// frustum geometry of the K detections from the gathered heads: 4 lanes per detection, the three atan2 and then
+// sin / cos evaluated side by side (fp64, rounded once: the parity contract of geometry.cuh)
+// reference src/lib/utils/pointcloud.py:348-380
+template <int T>
+__device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const MergeJob& jb, int b, const int* sind,
+                                                 const float* gath) {
+    const int K = p.K, W = p.W;
+    const int tid = threadIdx.x, j = tid & 3;
+    const float* calib = jb.fh.calib + 12 * (size_t)b;
+    const float cal0 = __ldg(calib + 0), cal2 = __ldg(calib + 2);
+    for (int k0 = 0; k0 < K; k0 += T / 4) {
+        const int k = k0 + (tid >> 2);
+        const bool live = k < K;
+        const float* g = gath + (live ? k : 0) * GATH_STRIDE;
+        const int ind = live ? sind[k] : 0;
+        const int y = ind / W, x = ind - y * W;
+        const float xf = __fadd_rn((float)x, 0.5f), yf = __fadd_rn((float)y, 0.5f);
+        float w = g[FS_WH], h = g[FS_WH + 1];
         if (w < 0.0f) w = 0.0f;
         if (h < 0.0f) h = 0.0f;
-        if (jb.dec.norm2d) {
-            w = __fmul_rn(w, (float)jb.dec.out_w);
-            h = __fmul_rn(h, (float)jb.dec.out_h);
-        }
         const float hw2 = __fdiv_rn(w, 2.0f), hh2 = __fdiv_rn(h, 2.0f);
-        float4 bb;
-        bb.x = __fsub_rn(xs, hw2);
-        bb.y = __fsub_rn(ys, hh2);
-        bb.z = __fadd_rn(xs, hw2);
-        bb.w = __fadd_rn(ys, hh2);
-        o.bboxes[4 * ok + 0] = bb.x;
-        o.bboxes[4 * ok + 1] = bb.y;
-        o.bboxes[4 * ok + 2] = bb.z;
-        o.bboxes[4 * ok + 3] = bb.w;
-    }
-    if (hd.amodal) {  // :165 de-normalise
-        float ax = __ldg(hd.amodal + ((size_t)b * 2 + 0) * HW + ind);
-        float ay = __ldg(hd.amodal + ((size_t)b * 2 + 1) * HW + ind);
-        if (jb.dec.norm2d) {
-            ax = __fmul_rn(ax, (float)jb.dec.out_w);
-            ay = __fmul_rn(ay, (float)jb.dec.out_h);
+        DetParam d;
+        d.x1 = __fsub_rn(xf, hw2);
+        d.y1 = __fsub_rn(yf, hh2);
+        d.x2 = __fadd_rn(xf, hw2);
+        d.y2 = __fadd_rn(yf, hh2);
+        const float cx = __fdiv_rn(__fadd_rn(d.x1, d.x2), 2.0f);  // :373-379
+        const float* r = g + FS_ROT;
+        // lane 0: atan2(rot2, rot3), lane 1: atan2(rot6, rot7), lane 2: the ray angle
+        const float ay = j == 0 ? r[2] : (j == 1 ? r[6] : __fsub_rn(cx, cal2));
+        const float ax = j == 0 ? r[3] : (j == 1 ? r[7] : cal0);
+        const float at = j < 3 ? f32_atan2(ay, ax) : 0.0f;
+        const int l0 = (tid & 31) & ~3;
+        const float at1 = __shfl_sync(FULL, at, l0), at2 = __shfl_sync(FULL, at, l0 + 1),
+                    ray = __shfl_sync(FULL, at, l0 + 2);
+        const float yaw = yaw_wrap(alpha_blend(r[1], r[5], at1, at2), ray);  // :372, :230-235
+        const float cs = j == 0 ? (float)cos((double)yaw) : (j == 1 ? (float)sin((double)yaw) : 0.0f);
+        const float c = __shfl_sync(FULL, cs, l0), s = __shfl_sync(FULL, cs, l0 + 1);
+        if (live && j == 0) {
+            d.depth = g[FS_DEPTH];
+            d.thr = thr_from_cs(c, s, g[FS_DIM + 1], g[FS_DIM + 2]);  // :380
+            d.ind = ind;
+            d.pad_ = 0;
+            const size_t o = (size_t)b * K + k;
+            p.det[o] = d;
+            if (jb.fo.thr) jb.fo.thr[o] = d.thr;
+            if (jb.fo.inds) jb.fo.inds[o] = ind;
         }
-        o.amodal[2 * ok + 0] = ax;
-        o.amodal[2 * ok + 1] = ay;
     }
-    if (hd.depth) o.depth[ok] = __ldg(hd.depth + (size_t)b * HW + ind);
-    if (o.inds) o.inds[ok] = ind;
 }
 
-// plain channel copies of the decode heads, spread over the whole block: out[b,k,ch] = head[b,ch,ind_k]
+// reference src/lib/model/decode.py:38-41, :80-85, :132-165
 template <int T>
-__device__ __forceinline__ void copy_head(const float* head, float* out, int nch, int b, int K, size_t HW,
-                                          const int* sind) {
+__device__ __forceinline__ void epilogue_decode(const MergeParams& p, const MergeJob& jb, int b,
+                                                const unsigned long long* sorted, const int* sind, const float* gath) {
+    const int K = p.K, HWi = p.H * p.W;
+    const cf_decode_heads_t& hd = jb.dec.heads;
+    const cf_decode_out_t& o = jb.dec.out;
+    for (int k = threadIdx.x; k < K; k += T) {
+        const unsigned long long c = sorted[k];
+        const uint32_t gi = comp_gidx(c), key = comp_key(c);
+        const int cls = (int)(gi / (uint32_t)HWi);
+        const int ind = sind[k];
+        const int y = ind / p.W, x = ind - y * p.W;
+        const float* g = gath + k * GATH_STRIDE;
+        float score = key2f(key);
+        if (key == KEY_ZERO) score = __fmul_rn(__ldg(p.heat + ((size_t)b * p.C + cls) * HWi + ind), 0.0f);
+        const size_t ok = (size_t)b * K + k;
+        if (hd.uncertainty) score = __fmul_rn(score, expf(-expf(g[DS_UNC])));
+        o.scores[ok] = score;
+        o.class_ids[ok] = (float)cls;
+        const float xn = __fdiv_rn((float)x, (float)p.W), yn = __fdiv_rn((float)y, (float)p.H);
+        o.centers[2 * ok + 0] = xn;
+        o.centers[2 * ok + 1] = yn;
+        float xs = __fmul_rn(xn, (float)jb.dec.out_w), ys = __fmul_rn(yn, (float)jb.dec.out_h);
+        if (hd.reg) {
+            xs = __fadd_rn(xs, g[DS_REG]);
+            ys = __fadd_rn(ys, g[DS_REG + 1]);
+        } else {
+            xs = __fadd_rn(xs, 0.5f);
+            ys = __fadd_rn(ys, 0.5f);
+        }
+        if (hd.wh) {
+            float w = g[DS_WH], h = g[DS_WH + 1];
+            if (w < 0.0f) w = 0.0f;
+            if (h < 0.0f) h = 0.0f;
+            if (jb.dec.norm2d) {
+                w = __fmul_rn(w, (float)jb.dec.out_w);
+                h = __fmul_rn(h, (float)jb.dec.out_h);
+            }
+            const float hw2 = __fdiv_rn(w, 2.0f), hh2 = __fdiv_rn(h, 2.0f);
+            o.bboxes[4 * ok + 0] = __fsub_rn(xs, hw2);
+            o.bboxes[4 * ok + 1] = __fsub_rn(ys, hh2);
+            o.bboxes[4 * ok + 2] = __fadd_rn(xs, hw2);
+            o.bboxes[4 * ok + 3] = __fadd_rn(ys, hh2);
+        }
+        if (hd.amodal) {  // :165 de-normalise
+            float ax = g[DS_AMODAL], ay = g[DS_AMODAL + 1];
+            if (jb.dec.norm2d) {
+                ax = __fmul_rn(ax, (float)jb.dec.out_w);
+                ay = __fmul_rn(ay, (float)jb.dec.out_h);
+            }
+            o.amodal[2 * ok + 0] = ax;
+            o.amodal[2 * ok + 1] = ay;
+        }
+        if (hd.depth) o.depth[ok] = g[DS_DEPTH];
+        if (o.inds) o.inds[ok] = ind;
+    }
+}
+
+// plain channel copies of the decode heads out of the gather buffer: out[b,k,ch] = gath[k][slot0 + ch]
+template <int T>
+__device__ __forceinline__ void copy_head(const float* head, float* out, int nch, int slot0, int b, int K,
+                                          const float* gath) {
     if (!head) return;
     for (int t = threadIdx.x; t < K * nch; t += T) {
         const int k = t / nch, ch = t - k * nch;
-        out[((size_t)b * K + k) * nch + ch] = __ldg(head + ((size_t)b * nch + ch) * HW + sind[k]);
+        out[((size_t)b * K + k) * nch + ch] = gath[k * GATH_STRIDE + slot0 + ch];
     }
 }
 
-// shared memory of merge_frame (static, one instance per CTA)
+// shared memory of merge_frame: this struct followed by the gather buffer (K * GATH_STRIDE floats)
 struct MergeSmem {
     SelScratch sc;
     unsigned long long win[MERGE_WIN];
     unsigned long long sorted[CF_MAX_K];
     int sind[CF_MAX_K];
 };
+// [MergeSmem | gather buffer K*GATH_STRIDE floats | peak indices of both jobs 2*K ints]
+__host__ __device__ inline size_t merge_gath_off() { return ((sizeof(MergeSmem) + 127) / 128) * 128; }
+__host__ __device__ inline size_t merge_ind_off(int K) {
+    return merge_gath_off() + (((size_t)K * GATH_STRIDE * sizeof(float) + 127) / 128) * 128;
+}
+__host__ __device__ inline size_t merge_smem_bytes(int K) {
+    return merge_ind_off(K) + (((size_t)2 * K * sizeof(int) + 127) / 128) * 128;
+}
 
+// more survivors than the rank window (dense ties), or a list flagged overflowed: exact block-level selection of the
+// K best into win[] from the list or, failing that, from the frame itself.  Slow, exact, rare -> never inlined.
 template <int T>
-__device__ __forceinline__ void merge_frame(const MergeParams& p, MergeSmem& sm, int b, int li) {
+__device__ __noinline__ void select_overflow(const MergeParams& p, MergeSmem& sm, int b, int list, uint32_t n,
+                                             const unsigned long long* cand) {
+    const int K = p.K, HWi = p.H * p.W;
+    if (n <= (uint32_t)CAND_CAP) {
+        ListSrc<T> src;
+        src.cand = cand;
+        src.n_in = (int)n;
+        src.n_round = (src.n_in + T - 1) / T * T;
+        block_select<T, 1>(src, K, sm.sc, [&](uint32_t slot, unsigned long long c) { sm.win[slot] = c; });
+    } else {
+        FrameSrc<T> src;
+        src.frame = p.heat + (size_t)b * p.C * HWi;
+        src.CH = p.C * p.H;
+        src.H = p.H;
+        src.W = p.W;
+        src.n_round = (p.C * HWi + T - 1) / T * T;
+        src.nms = list == 1;
+        block_select<T, 1>(src, K, sm.sc, [&](uint32_t slot, unsigned long long c) { sm.win[slot] = c; });
+    }
+    __syncthreads();
+}
+
+// step 1 of a job: the K best survivors, sorted, into sm.sorted[] / sm.sind[] (flat pixel of each peak)
+template <int T>
+__device__ __forceinline__ void merge_select(const MergeParams& p, MergeSmem& sm, int b, int li) {
     const int tid = threadIdx.x;
-    const MergeJob& jb = p.job[li];
     const int list = p.list[li];
     const int K = p.K;
     const int HWi = p.H * p.W;
+    CF_MERGE_PROF(0);
     const uint32_t n = __ldcg(p.ctr + ((size_t)b * 2 + list) * CTR_STRIDE);  // survivors appended (>= K by construction)
     const unsigned long long* cand = p.cand + ((size_t)b * 2 + list) * CAND_CAP;
 
     int nw;  // entries of win[] to rank
     if (n <= (uint32_t)MERGE_WIN) {
-        for (int t = tid; t < MERGE_WIN; t += T) sm.win[t] = t < (int)n ? __ldcg(cand + t) : 0ull;
+        for (int t = tid; t < (int)n; t += T) sm.win[t] = __ldcg(cand + t);
         nw = (int)n;
         __syncthreads();
     } else {
-        if (n <= (uint32_t)CAND_CAP) {
-            ListSrc<T> src;
-            src.cand = cand;
-            src.n_in = (int)n;
-            src.n_round = (src.n_in + T - 1) / T * T;
-            block_select<T, 1>(src, K, sm.sc, [&](uint32_t slot, unsigned long long c) { sm.win[slot] = c; });
-        } else {
-            FrameSrc<T> src;
-            src.frame = p.heat + (size_t)b * p.C * HWi;
-            src.CH = p.C * p.H;
-            src.H = p.H;
-            src.W = p.W;
-            src.n_round = (p.C * HWi + T - 1) / T * T;
-            src.nms = list == 1;
-            block_select<T, 1>(src, K, sm.sc, [&](uint32_t slot, unsigned long long c) { sm.win[slot] = c; });
-        }
+        select_overflow<T>(p, sm, b, list, n, cand);  // rare, out of line: keeps the common path's code small
         nw = K;
-        __syncthreads();
     }
 
-    // rank by counting (composites are distinct: ranks are a permutation); the K best land in sorted[]
+    CF_MERGE_PROF(1);
+    // rank by counting (composites are distinct: ranks are a permutation); the K best land in sorted[].  Four
+    // independent partial counts per thread keep the shared-memory broadcasts in flight.
     for (int t = tid; t < nw; t += T) {
         const unsigned long long me = sm.win[t];
-        int rank = 0;
-        for (int j = 0; j < nw; ++j) rank += (sm.win[j] > me) ? 1 : 0;
-        if (rank < K) sm.sorted[rank] = me;
+        int r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+        int jx = 0;
+        for (; jx + 4 <= nw; jx += 4) {
+            r0 += (sm.win[jx] > me) ? 1 : 0;
+            r1 += (sm.win[jx + 1] > me) ? 1 : 0;
+            r2 += (sm.win[jx + 2] > me) ? 1 : 0;
+            r3 += (sm.win[jx + 3] > me) ? 1 : 0;
+        }
+        for (; jx < nw; ++jx) r0 += (sm.win[jx] > me) ? 1 : 0;
+        const int rank = (r0 + r1) + (r2 + r3);
+        if (rank < K) {
+            sm.sorted[rank] = me;
+            const uint32_t g = comp_gidx(me);
+            sm.sind[rank] = (int)(g % (uint32_t)HWi);
+        }
     }
     __syncthreads();
+    CF_MERGE_PROF(2);
+}
 
-    for (int k = tid; k < K; k += T) {
-        const unsigned long long c = sm.sorted[k];
-        const uint32_t g = comp_gidx(c), key = comp_key(c);
-        const int cls = (int)(g / (uint32_t)HWi);
-        const int ind = (int)(g - (uint32_t)cls * (uint32_t)HWi);
-        const int y = ind / p.W, x = ind - y * p.W;
-        sm.sind[k] = ind;
-        float score = key2f(key);
-        if (key == KEY_ZERO) score = __fmul_rn(__ldg(p.heat + ((size_t)b * p.C + cls) * HWi + ind), 0.0f);
-        const size_t o = (size_t)b * K + k;
-        if (jb.epilogue == EPI_TOPK) {
+// this CTA's share (pairs t = first, first + stride, ...) of the head gathers of one job: values go straight into the
+// gather buffer of the CTA that owns the job (st.shared::cluster; `gath_remote` = its shared::cluster address).
+// One SM sustains only a few hundred outstanding scattered loads, so the K * N loads of a job are spread over the
+// whole cluster.
+template <int T, int N>
+__device__ __forceinline__ void gather_share(const GatherTab& gt, int b, int K, size_t HW, const int* inds,
+                                             uint32_t gath_remote, int first, int stride) {
+    const int total = K * N;
+    constexpr int U = 4;
+    for (int t0 = first; t0 < total; t0 += stride * U) {
+        float v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int t = t0 + u * stride;
+            v[u] = 0.0f;
+            if (t < total) {
+                const int k = t / N, s = t - k * N;
+                const float* base = gt.base[s];
+                if (base) v[u] = __ldg(base + ((size_t)b * gt.nch[s] + gt.ch[s]) * HW + inds[k]);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int t = t0 + u * stride;
+            if (t < total) {
+                const int k = t / N, s = t - k * N;
+                asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(gath_remote + 4u * (uint32_t)(k * GATH_STRIDE + s)),
+                             "f"(v[u])
+                             : "memory");
+            }
+        }
+    }
+}
+
+// step 3 of a job: epilogue from the gathered heads
+template <int T>
+__device__ __forceinline__ void merge_epilogue(const MergeParams& p, MergeSmem& sm, int b, int li) {
+    const int tid = threadIdx.x;
+    const MergeJob& jb = p.job[li];
+    const int K = p.K;
+    const int HWi = p.H * p.W;
+    const float* gath = reinterpret_cast<const float*>(reinterpret_cast<unsigned char*>(&sm) + merge_gath_off());
+    CF_MERGE_PROF(3);
+    if (jb.epilogue == EPI_TOPK) {
+        for (int k = tid; k < K; k += T) {
+            const unsigned long long c = sm.sorted[k];
+            const uint32_t g = comp_gidx(c), key = comp_key(c);
+            const int cls = (int)(g / (uint32_t)HWi);
+            const int ind = sm.sind[k];
+            const int y = ind / p.W, x = ind - y * p.W;
+            float score = key2f(key);
+            if (key == KEY_ZERO) score = __fmul_rn(__ldg(p.heat + ((size_t)b * p.C + cls) * HWi + ind), 0.0f);
+            const size_t o = (size_t)b * K + k;
             if (jb.topk.scores) jb.topk.scores[o] = score;
             if (jb.topk.inds) jb.topk.inds[o] = ind;
             if (jb.topk.classes) jb.topk.classes[o] = cls;
             if (jb.topk.ys) jb.topk.ys[o] = y;
             if (jb.topk.xs) jb.topk.xs[o] = x;
-        } else if (jb.epilogue == EPI_FRUSTUM) {
-            epilogue_frustum(p, jb, b, k, ind, x, y);
-        } else if (jb.epilogue == EPI_DECODE) {
-            epilogue_decode(p, jb, b, k, score, cls, ind, x, y);
+        }
+    } else if (jb.epilogue == EPI_FRUSTUM || jb.epilogue == EPI_DECODE) {
+        if (jb.epilogue == EPI_FRUSTUM) {
+            epilogue_frustum<T>(p, jb, b, sm.sind, gath);
+        } else {
+            epilogue_decode<T>(p, jb, b, sm.sorted, sm.sind, gath);
+            copy_head<T>(jb.dec.heads.rot, jb.dec.out.rot, 8, DS_ROT, b, K, gath);
+            copy_head<T>(jb.dec.heads.dim, jb.dec.out.dim, 3, DS_DIM, b, K, gath);
+            copy_head<T>(jb.dec.heads.nuscenes_att, jb.dec.out.nuscenes_att, 8, DS_ATT, b, K, gath);
+            copy_head<T>(jb.dec.heads.velocity, jb.dec.out.velocity, 3, DS_VEL, b, K, gath);
         }
     }
-    if (jb.epilogue == EPI_DECODE) {
-        __syncthreads();
-        const size_t HW = (size_t)HWi;
-        copy_head<T>(jb.dec.heads.rot, jb.dec.out.rot, 8, b, K, HW, sm.sind);
-        copy_head<T>(jb.dec.heads.dim, jb.dec.out.dim, 3, b, K, HW, sm.sind);
-        copy_head<T>(jb.dec.heads.nuscenes_att, jb.dec.out.nuscenes_att, 8, b, K, HW, sm.sind);
-        copy_head<T>(jb.dec.heads.velocity, jb.dec.out.velocity, 3, b, K, HW, sm.sind);
-    }
+    CF_MERGE_PROF(4);
     __syncthreads();  // sm is reused by the next job of this CTA
+    CF_MERGE_PROF(5);
 }
 
 }  // namespace cf

@@ -1,0 +1,930 @@
+// stage.cu -- the fused fusion-stage kernel: ONE launch per call, one thread-block cluster per frame.
+//
+// Replaces (reference, src/lib/): model/utils.py:112-128 nms, :6-38 topk, :41-72 transposeAndGetFeature;
+// utils/pointcloud.py:331-394 getPcFrustumHeatmap with :397-481 cvtPcDepthToHeatmap under its B x K loop;
+// model/decode.py:10-174 fusionDecode.
+//
+// A frame's heat-map is a (C*H) x W row matrix.  The CS CTAs of a cluster (CS = 1..16, chosen by the host so that
+// the batch covers the chip in one wave) split its rows; each CTA streams its share from HBM ONCE with 1-D TMA bulk
+// copies (cp.async.bulk + mbarrier complete_tx) into shared-memory slots and KEEPS it there: at the reference
+// sizes (448x800 input, batch 32: 4 CTAs x 224 000 B) the whole batch of heat-maps sits in the chip's shared
+// memory between the two looks the exact selection needs.  Per frame:
+//
+//   A  bound    every lane takes the maximum of its own float4 items of a chunk; the lane groups of a frame are
+//               disjoint, so the K-th largest group maximum is a lower bound of the K-th largest pixel (for the
+//               nms'd list a group maximum only counts if that pixel survives the 3x3 suppression).  Group maxima
+//               go into a 4096-bin histogram DISTRIBUTED over the cluster's shared memory (bin -> CTA bin % CS,
+//               16-bit counters, red.shared::cluster).
+//   -- cluster barrier --
+//      tau      every CTA scans the distributed histogram top-down (ld.shared::cluster): tau = lower edge of the
+//               bin holding the K-th largest group maximum.
+//   B  filter   second look, from shared memory: pixels >= tau (and, nms'd list, surviving the 3x3 test) are staged
+//               per CTA and appended to the frame's survivor list (typically 1.1-3 x K entries).
+//   -- cluster barrier --
+//   C  merge    CTA 0: exact sorted top-K of the raw list + NCHW gathers + frustum geometry; CTA 1: the same for
+//               the nms'd list + the fusionDecode epilogue (merge.cuh).  Meanwhile every CTA stages the frame's
+//               radar depth plane pc_dep[b,0] in the shared memory the heat-map no longer needs (one bulk copy).
+//   -- cluster barrier --
+//   D  assoc    one warp per detection over the whole cluster: ROI scan of the staged depth plane, warp-shuffle
+//               lexicographic (depth, pixel) minimum (assoc.cuh).
+//   -- cluster barrier --
+//   E  paint    each CTA paints its band of rows of pc_hm: owner map in shared memory, every pixel written once.
+//
+// Shares that do not fit (full-resolution maps, single-CTA clusters) run the same code as a ring: the slots are
+// recycled in pass A, the last S chunks stay resident, and pass B re-fetches the others (L2 hits) through the slots
+// it frees.  The warp that finishes with a slot issues the next bulk copy into it, so there is no producer warp and
+// no "empty" barrier.  Inputs the TMA cannot take (W % 4 != 0, unaligned base) are staged by the consuming warp.
+#include <math_constants.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "assoc.cuh"
+#include "geometry.cuh"
+#include "kernels.cuh"
+#include "paint.cuh"
+#include "select.cuh"
+
+namespace cf {
+
+constexpr int ST = 512;          // threads per CTA
+constexpr int SNW = ST / 32;     // warps
+constexpr int WL_CAP = 640;      // pass-B work list: candidate pixels a CTA parks before it tests them side by side
+constexpr int MAX_SLOTS = 64;
+constexpr int MAX_CS = 16;
+constexpr size_t SMEM_DYN_CAP = 227 * 1024 - 1536;  // leaves room for the kernel's static shared memory
+
+// ---- cluster primitives ------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cl_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t cl_size() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+    return r;
+}
+// all threads of all CTAs of the cluster; release/acquire at cluster scope (shared::cluster and global memory)
+__device__ __forceinline__ void cl_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cl_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cl_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+__device__ __forceinline__ uint32_t cl_map(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void cl_red_add(uint32_t raddr, uint32_t v) {
+    asm volatile("red.shared::cluster.add.u32 [%0], %1;" ::"r"(raddr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t cl_ld(uint32_t raddr) {
+    uint32_t v;
+    asm volatile("ld.shared::cluster.u32 %0, [%1];" : "=r"(v) : "r"(raddr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void cl_st(uint32_t raddr, uint32_t v) {
+    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(raddr), "r"(v) : "memory");
+}
+// generic-proxy accesses to shared memory before this fence are ordered before later async-proxy (TMA) accesses
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// development aid (CFD3D_PROF=1): per-CTA clock64 stamps at the phase boundaries of the last frame a CTA processed
+constexpr int PROF_PTS = 32;
+__device__ long long g_prof[1024 * PROF_PTS];
+#define CF_MERGE_PROF(i)                                                                                  \
+    do {                                                                                                  \
+        if (p.prof && threadIdx.x == 0 && blockIdx.x < 1024) g_prof[blockIdx.x * PROF_PTS + 16 + (i)] = clock64(); \
+    } while (0)
+#define PROF(i)                                                                              \
+    do {                                                                                     \
+        if (p.prof && tid == 0 && blockIdx.x < 1024) g_prof[blockIdx.x * PROF_PTS + (i)] = clock64(); \
+    } while (0)
+
+}  // namespace cf
+#include "merge.cuh"
+namespace cf {
+
+struct StageParams {
+    int prof;
+    const float* heat;
+    int B, C, H, W, Wp, K;
+    int R;             // rows per chunk
+    int S;             // shared-memory slots
+    int slot_floats;   // floats per slot (stride)
+    int lists;         // LIST_RAW | LIST_NMS
+    int use_tma;
+    int cs_log2;       // log2(cluster size)
+    int hist_words;    // 32-bit words of this CTA's part of the histogram (both lists)
+    int slot_area;     // bytes of the slot area (also hosts the merge scratch, the depth plane and the owner map)
+    int dep_off;       // byte offset of the staged depth plane inside the slot area, -1: read it from global memory
+    uint32_t* ctr;
+    unsigned long long* cand;
+    MergeParams mp;
+    int n_jobs;
+    int do_frustum;
+    const float* pc_dep;
+    float max_pc_dist;
+    float* pc_hm;
+    int32_t* assoc;
+    PaintRec* recs;
+};
+
+// order-preserving key -> the float it encodes; key 0 ("everything") -> -inf
+__device__ __forceinline__ float tau_to_float(uint32_t key) { return key ? key2f(key) : -CUDART_INF_F; }
+
+// group maximum -> distributed histogram: one remote reduction per distinct bin per warp
+__device__ __forceinline__ void hist_add_cluster(uint32_t hist_saddr, int list_words, int list, uint32_t key,
+                                                 int cs_log2) {
+    const uint32_t bin = key ? (key >> HIST_SHIFT) : 0xffffffffu;
+    const uint32_t peers = __match_any_sync(FULL, bin);
+    if (key && (threadIdx.x & 31) == __ffs(peers) - 1) {
+        const uint32_t owner = bin & ((1u << cs_log2) - 1u), lb = bin >> cs_log2;
+        const uint32_t word = (uint32_t)(list * list_words) + (lb >> 1);
+        cl_red_add(cl_map(hist_saddr + word * 4u, owner), (uint32_t)__popc(peers) << (16u * (lb & 1u)));
+    }
+}
+__device__ __forceinline__ uint32_t hist_read_cluster(uint32_t hist_saddr, int list_words, int list, int bin,
+                                                      int cs_log2) {
+    const uint32_t owner = (uint32_t)bin & ((1u << cs_log2) - 1u), lb = (uint32_t)bin >> cs_log2;
+    const uint32_t word = (uint32_t)(list * list_words) + (lb >> 1);
+    return (cl_ld(cl_map(hist_saddr + word * 4u, owner)) >> (16u * (lb & 1u))) & 0xffffu;
+}
+
+// tau of both lists: lower edge of the highest bin b* with count(bins >= b*) >= K, 0 ("everything") when the frame
+// has fewer than K groups.  Scans downwards from the top occupied bin, ST bins per round, both lists side by side.
+__device__ __forceinline__ void tau_scan_cluster(uint32_t hist_saddr, int list_words, int cs_log2, const uint32_t top_in[2],
+                                                 int K, bool want0, bool want1, uint32_t* s_scan, uint32_t tau[2]) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = SNW;
+    const bool want[2] = {want0, want1};
+    uint32_t top[2], carry[2] = {0u, 0u};
+    bool done[2];
+#pragma unroll
+    for (int l = 0; l < 2; ++l) {
+        top[l] = want[l] ? top_in[l] : 0u;
+        done[l] = !want[l];
+        tau[l] = 0u;
+    }
+    for (int round = 0; !(done[0] && done[1]); ++round) {
+        uint32_t c[2], inc[2];
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            const int bin = (int)top[l] - (round * ST + tid);
+            c[l] = (!done[l] && bin >= 0) ? hist_read_cluster(hist_saddr, list_words, l, bin, cs_log2) : 0u;
+        }
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            inc[l] = c[l];  // inclusive prefix over tid = over descending bins
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const uint32_t o = __shfl_up_sync(FULL, inc[l], off);
+                if (lane >= off) inc[l] += o;
+            }
+            if (lane == 31) s_scan[l * (NW + 1) + warp] = inc[l];
+            if (tid == 0) s_scan[l * (NW + 1) + NW] = 0xffffffffu;
+        }
+        __syncthreads();
+        uint32_t total[2];
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            uint32_t below = carry[l];
+            total[l] = carry[l];
+#pragma unroll
+            for (int w = 0; w < NW; ++w) {
+                const uint32_t t = s_scan[l * (NW + 1) + w];
+                if (w < warp) below += t;
+                total[l] += t;
+            }
+            inc[l] += below;
+            const int bin = (int)top[l] - (round * ST + tid);
+            if (!done[l] && inc[l] >= (uint32_t)K && inc[l] - c[l] < (uint32_t)K)
+                s_scan[l * (NW + 1) + NW] = (uint32_t)bin << HIST_SHIFT;  // exactly one thread
+        }
+        __syncthreads();
+#pragma unroll
+        for (int l = 0; l < 2; ++l) {
+            if (done[l]) continue;
+            const uint32_t found = s_scan[l * (NW + 1) + NW];
+            if (found != 0xffffffffu) {
+                tau[l] = found;
+                done[l] = true;
+            } else if ((int)top[l] - (round + 1) * ST < 0) {
+                done[l] = true;  // histogram exhausted: fewer than K groups, tau stays 0
+            } else {
+                carry[l] = total[l];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_constant__ StageParams p) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ uint64_t full[MAX_SLOTS];
+    __shared__ uint64_t dep_bar;
+    __shared__ uint32_t s_scan[2 * (SNW + 1)];
+    __shared__ uint32_t s_tops[2][MAX_CS];
+    __shared__ uint32_t s_mytop[2];
+    __shared__ uint32_t s_nwl;  // entries of the pass-B work list
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t rank = cl_rank(), cs = cl_size();
+    const int cluster_id = (int)(blockIdx.x >> p.cs_log2), n_clusters = (int)(gridDim.x >> p.cs_log2);
+    const int C = p.C, H = p.H, W = p.W, Wp = p.Wp, R = p.R, S = p.S, K = p.K;
+    const int CH = C * H, W4 = Wp >> 2;
+    const size_t HW = (size_t)H * W;
+    const bool want_raw = (p.lists & LIST_RAW) != 0, want_nms = (p.lists & LIST_NMS) != 0;
+    const bool use_tma = p.use_tma != 0;
+
+    float* slots = reinterpret_cast<float*>(smem);
+    uint32_t* hist = reinterpret_cast<uint32_t*>(smem + p.slot_area);
+    uint32_t* wl = hist + p.hist_words;  // pass-B work list, WL_CAP entries
+    const uint32_t hist_saddr = smem_u32(hist);
+    const int list_words = p.hist_words >> 1;
+
+    // this CTA's rows of the frame matrix, in chunks of R rows
+    const int row_begin = (int)((long long)CH * rank / cs), row_end = (int)((long long)CH * (rank + 1) / cs);
+    const int n = (row_end - row_begin + R - 1) / R;   // chunks
+    const int n_res = n < S ? n : S;                   // chunks still resident when pass B starts
+    const int n_ref = n - n_res;                       // chunks pass B fetches again
+    const int LPF = n + n_ref;                         // bulk copies per frame
+    const bool resident = use_tma && n_ref == 0;
+
+    if (tid == 0) {
+        for (int s = 0; s < S; ++s) mbar_init(&full[s], 1);
+        mbar_init(&dep_bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    int it = 0;
+    for (int b = cluster_id; b < p.B; b += n_clusters, ++it) {
+        const float* frame = p.heat + (size_t)b * CH * W;
+        uint32_t* ctr_raw = p.ctr + ((size_t)b * 2) * CTR_STRIDE;
+        uint32_t* ctr_nms = ctr_raw + CTR_STRIDE;
+        unsigned long long* cand_raw = p.cand + (size_t)b * 2 * CAND_CAP;
+        unsigned long long* cand_nms = cand_raw + CAND_CAP;
+
+        auto issue_load = [&](int L) {  // one thread: bulk copy L of this frame (L >= n: pass-B re-fetch)
+            const int q = L < n ? L : L - n;
+            const int s = L % S;
+            const int rr = row_begin + q * R, nr = min(R, row_end - rr);
+            const uint32_t bytes = (uint32_t)nr * (uint32_t)W * 4u;
+            mbar_expect_tx(&full[s], bytes);
+            tma_bulk_g2s(slots + (size_t)s * p.slot_floats, frame + (size_t)rr * W, bytes, &full[s]);
+        };
+        auto load_parity = [&](int L) -> uint32_t {  // phase parity of bulk copy L on its slot's barrier
+            const int s = L % S;
+            const int per_frame = (LPF - 1 - s) / S + 1;
+            return (uint32_t)(it * per_frame + L / S) & 1u;
+        };
+        // consuming warp stages a chunk itself (inputs the TMA cannot take): padded row stride, -inf padding
+        auto manual_fill = [&](float* tile, int rr, int nr) {
+            const int cnt = nr * Wp;
+            for (int i = lane; i < cnt; i += 32) {
+                const int row = i / Wp, x = i - row * Wp;
+                tile[i] = x < W ? __ldg(frame + (size_t)(rr + row) * W + x) : -CUDART_INF_F;
+            }
+            __syncwarp();
+        };
+        // a row of the frame matrix: shared memory when it is one of this CTA's resident rows, else global (L2)
+        auto row_ptr = [&](int g) -> const float* {
+            if (resident && g >= row_begin && g < row_end) return slots + (size_t)(g - row_begin) * Wp;  // slots are contiguous
+            return frame + (size_t)g * W;
+        };
+
+        PROF(0);
+        // ---- frame start: clear this CTA's histogram part and counters, start the first S bulk copies ------------
+        for (int i = tid; i < p.hist_words; i += ST) hist[i] = 0u;
+        if (tid < 2 * MAX_CS) (&s_tops[0][0])[tid] = 0u;
+        if (tid < 2) s_mytop[tid] = 0u;
+        if (tid == 0) s_nwl = 0u;
+        fence_async_smem();  // the previous frame's merge scratch / owner map were generic writes to the slot area
+        __syncthreads();
+        // "this CTA runs and its histogram part is clear": arrive now, wait right before the first remote reduction
+        // (the release fence of the arrival then has nothing outstanding to wait for)
+        cl_arrive();
+        if (use_tma && tid < (LPF < S ? LPF : S)) issue_load(tid);
+        if (rank == 0 && tid < 2 * CTR_STRIDE) ctr_raw[tid] = 0u;  // ordered before any append by the next barrier
+        if (p.do_frustum) {  // the association's radar maps: into L2 while the heat-map streams
+            const char* pd = reinterpret_cast<const char*>(p.pc_dep + (size_t)b * 3 * HW);
+            const size_t lines = (3 * HW * 4 + 127) / 128;
+            for (size_t l = (size_t)rank * ST + tid; l < lines; l += (size_t)cs * ST)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(pd + l * 128));
+        }
+        PROF(15);
+        cl_wait();
+        PROF(1);
+
+        // ---- pass A: group maxima -> distributed histogram ------------------------------------------------------
+        {
+            const float inv_w4 = 1.0f / (float)W4;
+            uint32_t tkraw = 0u, tknms = 0u;
+            for (int q = warp; q < n; q += SNW) {
+                const int rr = row_begin + q * R, nr = min(R, row_end - rr);
+                float* tile;
+                if (use_tma) {
+                    const int s = q % S;
+                    mbar_wait(&full[s], load_parity(q));
+                    tile = slots + (size_t)s * p.slot_floats;
+                } else {
+                    tile = slots + (size_t)warp * p.slot_floats;
+                    manual_fill(tile, rr, nr);
+                }
+                const int n_items = nr * W4;
+                const float4* c4p = reinterpret_cast<const float4*>(tile);
+                float best = -CUDART_INF_F;
+                int bi = lane;
+#pragma unroll 4
+                for (int i = lane; i < n_items; i += 32) {
+                    const float4 v = c4p[i];
+                    const float m = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+                    if (m > best) {
+                        best = m;
+                        bi = i;
+                    }
+                }
+                uint32_t kraw = 0u, knms = 0u;
+                int r = 0, x = -1;
+                if (lane < n_items) {
+                    r = (int)(((float)bi + 0.5f) * inv_w4);  // bi / W4, exact for bi < 2^21
+                    int cc = bi - r * W4;
+                    if (cc < 0) {
+                        --r;
+                        cc += W4;
+                    } else if (cc >= W4) {
+                        ++r;
+                        cc -= W4;
+                    }
+                    const float4 v = c4p[bi];
+                    const float cv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int j = 3; j >= 0; --j)
+                        if (cv[j] == best && 4 * cc + j < W) x = 4 * cc + j;
+                    if (x >= 0) kraw = f2key(best);  // (x < 0: all -inf in a padded float4)
+                }
+                if (want_nms) {
+                    // the group maximum backs the nms'd bound only if that pixel survives the 3x3 suppression; a
+                    // group whose maximum is suppressed contributes nothing (weaker bound, still a bound)
+                    const bool have = x >= 0;
+                    if (resident) {  // rows above / below may sit in the neighbouring chunks: wait for their copies
+                        if (__any_sync(FULL, have && r == 0 && q > 0)) mbar_wait(&full[(q - 1) % S], load_parity(q - 1));
+                        if (__any_sync(FULL, have && r == nr - 1 && q < n - 1))
+                            mbar_wait(&full[(q + 1) % S], load_parity(q + 1));
+                    }
+                    if (have) {
+                        const int g = rr + r;   // frame-matrix row
+                        const int py = g % H;   // row inside its class plane: planes do not see each other
+                        const float* rows[3];
+                        rows[0] = r > 0 ? tile + (r - 1) * Wp : row_ptr(g - 1);
+                        rows[1] = tile + r * Wp;
+                        rows[2] = r < nr - 1 ? tile + (r + 1) * Wp : row_ptr(g + 1);
+                        float nb = -CUDART_INF_F;
+#pragma unroll
+                        for (int dy = -1; dy <= 1; ++dy) {
+                            const bool yok = py + dy >= 0 && py + dy < H;
+#pragma unroll
+                            for (int dx = -1; dx <= 1; ++dx) {
+                                const bool ok = yok && x + dx >= 0 && x + dx < W;
+                                const float t = ok ? rows[dy + 1][x + dx] : -CUDART_INF_F;
+                                nb = fmaxf(nb, t);
+                            }
+                        }
+                        knms = (nb > best) ? 0u : kraw;
+                    }
+                }
+                if (want_raw) hist_add_cluster(hist_saddr, list_words, 0, kraw, p.cs_log2);
+                if (want_nms) hist_add_cluster(hist_saddr, list_words, 1, knms, p.cs_log2);
+                tkraw = max(tkraw, kraw);
+                tknms = max(tknms, knms);
+                // a chunk that will not stay resident frees its slot: this warp starts the copy that reuses it
+                if (use_tma && q < n - n_res) {
+                    __syncwarp();
+                    if (lane == 0 && q + S < LPF) issue_load(q + S);
+                }
+            }
+            tkraw = __reduce_max_sync(FULL, tkraw);
+            tknms = __reduce_max_sync(FULL, tknms);
+            if (lane == 0) {
+                if (tkraw) atomicMax(&s_mytop[0], tkraw >> HIST_SHIFT);
+                if (tknms) atomicMax(&s_mytop[1], tknms >> HIST_SHIFT);
+            }
+            __syncthreads();
+            if (tid < 2 * (int)cs) {  // publish this CTA's top occupied bins to every CTA of the cluster
+                const int l = tid / (int)cs, r = tid - l * (int)cs;
+                cl_st(cl_map(smem_u32(&s_tops[l][rank]), (uint32_t)r), s_mytop[l]);
+            }
+        }
+        PROF(2);
+        cl_sync();  // histogram complete
+        PROF(3);
+
+        // ---- tau ---------------------------------------------------------------------------------------------------
+        uint32_t top[2] = {0u, 0u}, tau_key[2];
+        for (uint32_t r = 0; r < cs; ++r) {
+            top[0] = max(top[0], s_tops[0][r]);
+            top[1] = max(top[1], s_tops[1][r]);
+        }
+        tau_scan_cluster(hist_saddr, list_words, p.cs_log2, top, K, want_raw, want_nms, s_scan, tau_key);
+        PROF(4);
+        const float INF = CUDART_INF_F;
+        float tau_raw = want_raw ? tau_to_float(tau_key[0]) : INF;
+        float tau_nms = want_nms ? tau_to_float(tau_key[1]) : INF;
+        if (want_raw && tau_key[0] == 0u) {
+            // fewer than K groups: no useful bound -> the merge selects from the frame itself (list flagged overflowed)
+            if (rank == 0 && tid == 0) atomicAdd(ctr_raw, (uint32_t)CAND_CAP + 1u);
+            tau_raw = INF;
+        }
+        if (want_nms && !(tau_nms > 0.0f)) {
+            // fewer than K positive peaks: suppressed pixels (worth 0) belong to the top-K too -> same
+            if (rank == 0 && tid == 0) atomicAdd(ctr_nms, (uint32_t)CAND_CAP + 1u);
+            tau_nms = INF;
+        }
+
+        // ---- pass B: survivors >= tau, from shared memory ----------------------------------------------------------
+        // B1 scans (one vote per 512 pixels) and parks the few candidate pixels in a CTA-wide work list; B2 tests
+        // them side by side, one candidate per thread.  (Code executed once per launch is latency bound: a lane
+        // working through a blob's pixels on its own would cost microseconds.)
+        {
+            const float tau_min = fminf(tau_raw, tau_nms);
+            const float inv_w4 = 1.0f / (float)W4;
+            constexpr int FU = 4;  // float4 items per lane per block
+            // candidate (chunk q, pixel px of its tile) -> value, frame-flat pixel, list membership
+            auto cand_eval = [&](uint32_t code, float& v, uint32_t& gi, bool& sraw, bool& snms) {
+                const int q = (int)(code >> 16), px = (int)(code & 0xffffu);
+                const int i = px >> 2, j = px & 3;
+                int r = (int)(((float)i + 0.5f) * inv_w4);  // i / W4, exact for i < 2^21
+                int cc = i - r * W4;
+                if (cc < 0) {
+                    --r;
+                    cc += W4;
+                } else if (cc >= W4) {
+                    ++r;
+                    cc -= W4;
+                }
+                const int x = 4 * cc + j;
+                sraw = snms = false;
+                v = 0.0f;
+                gi = 0u;
+                if (x >= W) return;  // padded pixel (manual staging)
+                const int g = row_begin + q * R + r;
+                int py = g;  // row inside its class plane (at most C subtractions instead of a division)
+                while (py >= H) py -= H;
+                // 3x3 neighbourhood, branch-free: out-of-plane neighbours are replaced by in-plane pixels of the same
+                // window (clamped coordinates), which cannot change the maximum
+                const float* row0 = row_ptr(g);
+                const float* rowm = py > 0 ? row_ptr(g - 1) : row0;
+                const float* rowp = py < H - 1 ? row_ptr(g + 1) : row0;
+                const int xl = max(x - 1, 0), xr = min(x + 1, W - 1);
+                v = row0[x];
+                const float nb = fmaxf(fmaxf(fmax3(rowm[xl], rowm[x], rowm[xr]), fmaxf(row0[xl], row0[xr])),
+                                       fmax3(rowp[xl], rowp[x], rowp[xr]));
+                gi = (uint32_t)g * (uint32_t)W + (uint32_t)x;
+                sraw = want_raw && v >= tau_raw;
+                snms = want_nms && v >= tau_nms && !(nb > v);
+            };
+            // Visits: resident -> ONE visit, the whole share as one contiguous tile, 128-item blocks interleaved over
+            // the warps; ring / manual -> one visit per chunk per warp.
+            const int n_vis = resident ? 1 : n;
+            for (int vb = resident ? 0 : warp; vb < n_vis; vb += SNW) {
+                int L = 0, q = 0, nr = row_end - row_begin;
+                const float* tile = slots;
+                if (resident) {
+                    for (int c = lane; c < n; c += 32) mbar_wait(&full[c], (uint32_t)it & 1u);  // every copy, seen by this warp
+                    __syncwarp();
+                } else {
+                    L = vb < n_res ? n - n_res + vb : n + (vb - n_res);
+                    q = L < n ? L : L - n;
+                    const int rr = row_begin + q * R;
+                    nr = min(R, row_end - rr);
+                    if (use_tma) {
+                        const int s = L % S;
+                        mbar_wait(&full[s], load_parity(L));
+                        tile = slots + (size_t)s * p.slot_floats;
+                    } else {
+                        float* mt = slots + (size_t)warp * p.slot_floats;
+                        manual_fill(mt, rr, nr);
+                        tile = mt;
+                    }
+                }
+                const int n_items = nr * W4;
+                const float4* c4p = reinterpret_cast<const float4*>(tile);
+                const int i_step = resident ? SNW * 32 * FU : 32 * FU;
+                for (int item0 = resident ? warp * (32 * FU) : 0; item0 < n_items; item0 += i_step) {
+                    float4 q4[FU];
+                    float m = -INF;
+#pragma unroll
+                    for (int u = 0; u < FU; ++u) {
+                        const int i = item0 + u * 32 + lane;
+                        q4[u] = i < n_items ? c4p[i] : make_float4(-INF, -INF, -INF, -INF);
+                        m = fmaxf(m, fmaxf(fmaxf(q4[u].x, q4[u].y), fmaxf(q4[u].z, q4[u].w)));
+                    }
+                    // almost every block stops here: none of its 512 pixels reaches either threshold
+                    if (!__any_sync(FULL, m >= tau_min)) continue;
+                    uint32_t mask = 0u;  // bit u*4+j: pixel j of this lane's u-th float4 is a candidate
+#pragma unroll
+                    for (int u = 0; u < FU; ++u) {
+                        if (q4[u].x >= tau_min) mask |= 1u << (4 * u);
+                        if (q4[u].y >= tau_min) mask |= 2u << (4 * u);
+                        if (q4[u].z >= tau_min) mask |= 4u << (4 * u);
+                        if (q4[u].w >= tau_min) mask |= 8u << (4 * u);
+                    }
+                    const uint32_t cnt = (uint32_t)__popc(mask);
+                    uint32_t inc = cnt;
+#pragma unroll
+                    for (int off = 1; off < 32; off <<= 1) {
+                        const uint32_t o = __shfl_up_sync(FULL, inc, off);
+                        if (lane >= off) inc += o;
+                    }
+                    uint32_t base = 0u;
+                    if (lane == 31) base = atomicAdd(&s_nwl, inc);
+                    base = __shfl_sync(FULL, base, 31);
+                    uint32_t slot = base + inc - cnt;
+                    while (mask) {
+                        const int bit = __ffs(mask) - 1;
+                        mask &= mask - 1;
+                        const uint32_t code = ((uint32_t)q << 16) |
+                                              (uint32_t)((item0 + (bit >> 2) * 32 + lane) * 4 + (bit & 3));
+                        if (slot < (uint32_t)WL_CAP) {
+                            wl[slot] = code;
+                        } else {  // work list full (dense survivors): test and append right here, lane by lane
+                            float v;
+                            uint32_t gi;
+                            bool sraw, snms;
+                            cand_eval(code, v, gi, sraw, snms);
+                            if (sraw) {
+                                const uint32_t gs = atomicAdd(ctr_raw, 1u);
+                                if (gs < (uint32_t)CAND_CAP) cand_raw[gs] = make_comp(f2key(v), gi);
+                            }
+                            if (snms) {
+                                const uint32_t gs = atomicAdd(ctr_nms, 1u);
+                                if (gs < (uint32_t)CAND_CAP) cand_nms[gs] = make_comp(f2key(v), gi);
+                            }
+                        }
+                        ++slot;
+                    }
+                }
+                // this visit was the last use of the slot's contents: start the re-fetch that reuses it, if any
+                if (use_tma && !resident) {
+                    __syncwarp();
+                    if (lane == 0 && L + S < LPF) issue_load(L + S);
+                }
+            }
+            PROF(12);
+            __syncthreads();
+            PROF(13);
+            // B2: one candidate per thread; survivors go to the frame's lists with one atomic per warp and list
+            const uint32_t n_wl = min(s_nwl, (uint32_t)WL_CAP);
+            for (uint32_t c0 = 0; c0 < n_wl; c0 += ST) {
+                const uint32_t c = c0 + (uint32_t)tid;
+                float v = 0.0f;
+                uint32_t gi = 0u;
+                bool sraw = false, snms = false;
+                if (c < n_wl) cand_eval(wl[c], v, gi, sraw, snms);
+                const unsigned long long comp = make_comp(f2key(v), gi);
+#pragma unroll
+                for (int l = 0; l < 2; ++l) {
+                    const bool pr = l ? snms : sraw;
+                    const uint32_t bal = __ballot_sync(FULL, pr);
+                    if (!bal) continue;
+                    const int leader = __ffs(bal) - 1;
+                    uint32_t gb = 0u;
+                    if (lane == leader) gb = atomicAdd(l ? ctr_nms : ctr_raw, (uint32_t)__popc(bal));
+                    gb = __shfl_sync(FULL, gb, leader);
+                    const uint32_t gs = gb + (uint32_t)__popc(bal & lanemask_lt());
+                    if (pr && gs < (uint32_t)CAND_CAP) (l ? cand_nms : cand_raw)[gs] = comp;
+                }
+            }
+            PROF(14);
+            fence_async_smem();
+            __syncthreads();
+            // the slot area is free from here on.  Stage the radar depth plane for the association.
+            if (p.do_frustum && p.dep_off >= 0 && tid == 0) {
+                const uint32_t bytes = (uint32_t)(HW * 4);
+                mbar_expect_tx(&dep_bar, bytes);
+                tma_bulk_g2s(smem + p.dep_off, p.pc_dep + (size_t)b * 3 * HW, bytes, &dep_bar);
+            }
+        }
+        PROF(5);
+        cl_sync();  // survivor lists complete
+        PROF(6);
+
+        // ---- merge: job j on CTA j (both on the one CTA of a single-CTA cluster, one after the other) -------------
+        // select: sorted top-K of the job's survivor list -> peak pixels published to every CTA;
+        // gather: the K x (14 | 30) head values, spread over the whole cluster, delivered into the owner's shared memory;
+        // epilogue: frustum geometry / decode outputs from shared memory.
+        {
+            MergeSmem& msm = *reinterpret_cast<MergeSmem*>(smem);
+            int* xs_ind = reinterpret_cast<int*>(smem + merge_ind_off(K));  // [job][K], same offset in every CTA
+            const int rounds = cs == 1 ? p.n_jobs : 1;
+            for (int rd = 0; rd < rounds; ++rd) {
+                const int li_lo = cs == 1 ? rd : 0, li_hi = cs == 1 ? rd + 1 : p.n_jobs;
+                for (int li = li_lo; li < li_hi; ++li) {
+                    if ((uint32_t)(li & ((int)cs - 1)) != rank) continue;
+                    merge_select<ST>(p.mp, msm, b, li);
+                    if (p.mp.job[li].epilogue != EPI_TOPK) {
+                        const uint32_t dst = smem_u32(xs_ind + li * K);
+                        for (int k = tid; k < K; k += ST) {
+                            const uint32_t v = (uint32_t)msm.sind[k];
+                            for (uint32_t c = 0; c < cs; ++c) cl_st(cl_map(dst + 4u * k, c), v);
+                        }
+                    }
+                }
+                cl_sync();  // peak pixels of the jobs known everywhere
+                for (int li = li_lo; li < li_hi; ++li) {
+                    const MergeJob& jb = p.mp.job[li];
+                    const uint32_t owner = (uint32_t)(li & ((int)cs - 1));
+                    const uint32_t gath_remote = cl_map(smem_u32(smem + merge_gath_off()), owner);
+                    if (jb.epilogue == EPI_FRUSTUM)
+                        gather_share<ST, FS_N>(jb.gt, b, K, HW, xs_ind + li * K, gath_remote, (int)rank * ST + tid, (int)cs * ST);
+                    else if (jb.epilogue == EPI_DECODE)
+                        gather_share<ST, DS_N>(jb.gt, b, K, HW, xs_ind + li * K, gath_remote, (int)rank * ST + tid, (int)cs * ST);
+                }
+                cl_sync();  // gathered heads delivered
+                for (int li = li_lo; li < li_hi; ++li)
+                    if ((uint32_t)(li & ((int)cs - 1)) == rank) merge_epilogue<ST>(p.mp, msm, b, li);
+            }
+        }
+        PROF(7);
+        if (!p.do_frustum) continue;
+        cl_sync();  // frustum parameters of the K detections are in the workspace
+        PROF(8);
+
+        // ---- association: detection k on CTA k % CS, one warp per detection ---------------------------------------
+        // shared-memory layout of the tail (the merge scratch is dead): [sdet | sbest | srecs | owner map], the staged
+        // depth plane sits behind the merge scratch and is never overlapped
+        DetParam* sdet = reinterpret_cast<DetParam*>(smem);
+        unsigned long long* sbest = reinterpret_cast<unsigned long long*>(smem + (size_t)K * 32);
+        PaintRec* srecs = reinterpret_cast<PaintRec*>(smem + (size_t)K * 40);
+        {
+            const float* dep = p.pc_dep + (size_t)b * 3 * HW;
+            const float* dep0 = dep;
+            const int n_local = (K - (int)rank + (int)cs - 1) / (int)cs;
+            for (int t = tid; t < 2 * n_local; t += ST) {  // this CTA's frustum parameters: one L2 round trip
+                const size_t o = (size_t)b * K + rank + (size_t)(t >> 1) * cs;
+                reinterpret_cast<int4*>(sdet)[t] = __ldcg(reinterpret_cast<const int4*>(p.mp.det + o) + (t & 1));
+            }
+            if (p.dep_off >= 0) {
+                mbar_wait(&dep_bar, (uint32_t)it & 1u);
+                dep0 = reinterpret_cast<const float*>(smem + p.dep_off);
+            }
+            __syncthreads();
+            for (int kl = warp; kl < n_local; kl += SNW) {
+                const DetParam d = sdet[kl];
+                const unsigned long long best =
+                    warp_min_u64(roi_scan(dep0, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32));
+                if (lane == 0) sbest[kl] = best;
+            }
+            __syncthreads();
+            // paint records: the velocity reads of all matches go out together; every CTA of the cluster gets a copy
+            // of every record in its shared memory (st.shared::cluster), in detection order
+            for (int kl = tid; kl < n_local; kl += ST) {
+                const int k = (int)rank + kl * (int)cs;
+                const size_t o = (size_t)b * K + k;
+                const PaintRec r = assoc_finalize(sbest[kl], dep, H, W, sdet[kl], p.max_pc_dist, p.assoc ? p.assoc + o : nullptr);
+                const uint32_t* rw = reinterpret_cast<const uint32_t*>(&r);
+                const uint32_t dst = smem_u32(srecs + k);
+                for (uint32_t c = 0; c < cs; ++c) {
+                    const uint32_t ra = cl_map(dst, c);
+#pragma unroll
+                    for (int w = 0; w < 8; ++w) cl_st(ra + 4u * w, rw[w]);
+                }
+            }
+        }
+        PROF(9);
+        cl_sync();  // paint records complete
+        PROF(10);
+
+        // ---- paint: this CTA's band of rows of pc_hm ----------------------------------------------------------------
+        {
+            const int y0 = (int)((long long)H * rank / cs), y1 = (int)((long long)H * (rank + 1) / cs);
+            const size_t own_off = ((size_t)K * 72 + 15) & ~(size_t)15;
+            const int max_rows = max(1, (int)(((size_t)p.slot_area - own_off) / ((size_t)W * sizeof(int))));
+            paint_band<ST, true>(srecs, K, H, W, y0, y1, p.pc_hm + (size_t)b * 3 * HW, nullptr,
+                                 reinterpret_cast<int*>(smem + own_off), max_rows);
+        }
+        PROF(11);
+    }
+}
+
+// -----------------------------------------------------------------------------------------------------
+// host side: plan + launch
+// -----------------------------------------------------------------------------------------------------
+static size_t align_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct StagePlan {
+    int cs, cs_log2, R, S, slot_floats, hist_words, slot_area, dep_off, n_clusters;
+    size_t smem;
+};
+
+// geometry of one cluster size; false when it cannot run
+static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool stage_dep, StagePlan* pl) {
+    const long long CH = (long long)C * H;
+    if (cs > CH || HIST_BINS % (2 * cs) != 0) return false;
+    const int Wp = (W + 3) & ~3;
+    int cs_log2 = 0;
+    while ((1 << cs_log2) < cs) ++cs_log2;
+    const long long share = (CH + cs - 1) / cs;  // rows of the largest share
+    long long chunk_bytes = 8192;
+    if (const char* e = getenv("CFD3D_CHUNK_BYTES")) {
+        if (atoll(e) >= 256) chunk_bytes = atoll(e);
+    }
+    long long R = chunk_bytes / ((long long)Wp * 4);
+    if (R < 1) R = 1;
+    if (R > share) R = share;
+    // 16-bit histogram counters: a frame must not have more than 65535 lane groups
+    while (((share + R - 1) / R) * 32 * cs > 65535) ++R;
+    const size_t slot_bytes = align_up_sz((size_t)R * Wp * 4, 16);
+    const int hist_words = 2 * (HIST_BINS / cs) / 2;
+    const size_t fixed = (size_t)hist_words * 4 + (size_t)WL_CAP * sizeof(uint32_t);
+    if (fixed + slot_bytes > SMEM_DYN_CAP) return false;
+    const long long n = (share + R - 1) / R;
+    long long S = (long long)((SMEM_DYN_CAP - fixed) / slot_bytes);
+    if (S > MAX_SLOTS) S = MAX_SLOTS;
+    if (use_tma) {
+        if (S > n) S = n;
+    } else {
+        S = SNW;  // every warp stages its own chunk
+        if ((size_t)S * slot_bytes + fixed > SMEM_DYN_CAP) return false;
+    }
+    if (S < 1) return false;
+    const size_t merge_bytes = merge_smem_bytes(K);
+    size_t area = (size_t)S * slot_bytes;
+    if (area < merge_bytes) area = merge_bytes;
+    const size_t tail_bytes = align_up_sz((size_t)K * 72, 16) + (size_t)W * sizeof(int);  // det, best, records + >= 1 owner row
+    if (area < tail_bytes) area = tail_bytes;
+    int dep_off = -1;
+    if (stage_dep) {
+        const size_t dep_bytes = (size_t)H * W * 4;
+        if (dep_bytes < (1u << 20) && merge_bytes + dep_bytes + fixed <= SMEM_DYN_CAP) {
+            dep_off = (int)merge_bytes;
+            if (area < merge_bytes + dep_bytes) area = merge_bytes + dep_bytes;
+        }
+    }
+    area = align_up_sz(area, 128);
+    if (area + fixed > SMEM_DYN_CAP) return false;
+    pl->cs = cs;
+    pl->cs_log2 = cs_log2;
+    pl->R = (int)R;
+    pl->S = (int)S;
+    pl->slot_floats = (int)(slot_bytes / 4);
+    pl->hist_words = hist_words;
+    pl->slot_area = (int)area;
+    pl->dep_off = dep_off;
+    pl->smem = area + fixed;
+    return true;
+}
+
+static cudaError_t launch_cfg(const StagePlan& pl, int grid, cudaStream_t st, cudaLaunchConfig_t* cfg,
+                              cudaLaunchAttribute* attr) {
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)pl.cs;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg->gridDim = dim3((unsigned)grid);
+    cfg->blockDim = dim3(ST);
+    cfg->dynamicSmemBytes = pl.smem;
+    cfg->stream = st;
+    cfg->attrs = attr;
+    cfg->numAttrs = 1;
+    return cudaSuccess;
+}
+
+// co-resident clusters of this size with this much shared memory (cached per device)
+static int max_clusters(const StagePlan& pl) {
+    static std::mutex mu;
+    static std::map<std::tuple<int, int, size_t>, int> cache;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const auto key = std::make_tuple(dev, pl.cs, pl.smem);
+    {
+        std::lock_guard<std::mutex> g(mu);
+        auto f = cache.find(key);
+        if (f != cache.end()) return f->second;
+    }
+    int n = 0;
+    if (cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem) ==
+            cudaSuccess &&
+        (pl.cs <= 8 ||
+         cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess)) {
+        cudaLaunchConfig_t cfg;
+        cudaLaunchAttribute attr[1];
+        memset(&cfg, 0, sizeof(cfg));
+        launch_cfg(pl, pl.cs, nullptr, &cfg, attr);
+        if (cudaOccupancyMaxActiveClusters(&n, fusion_stage_kernel, &cfg) != cudaSuccess) n = 0;
+    }
+    cudaGetLastError();  // a refused cluster size is not an error of the call
+    std::lock_guard<std::mutex> g(mu);
+    cache[key] = n;
+    return n;
+}
+
+cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, int K, const Workspace& ws,
+                                const MergeJob* raw_job, const MergeJob* nms_job, const float* pc_dep,
+                                float max_pc_dist, float* pc_hm, int32_t* assoc, cudaStream_t st, int* launches) {
+    const bool do_frustum = raw_job && raw_job->epilogue == EPI_FRUSTUM && pc_dep && pc_hm;
+    const bool use_tma = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(heat) & 15u) == 0);
+    const bool stage_dep = do_frustum && (((size_t)H * W) % 4 == 0) && ((reinterpret_cast<uintptr_t>(pc_dep) & 15u) == 0);
+    // cluster size: fewest rounds over the batch, then the most CTAs per frame
+    StagePlan best;
+    long long best_rounds = -1;
+    int force_cs = 0;
+    if (const char* e = getenv("CFD3D_CLUSTER")) force_cs = atoi(e);
+    for (int cs = MAX_CS; cs >= 1; cs >>= 1) {
+        if (force_cs && cs != force_cs) continue;
+        StagePlan pl;
+        if (!plan_for_cs(cs, C, H, W, K, use_tma, stage_dep, &pl)) continue;
+        const int cap = max_clusters(pl);
+        if (cap < 1) continue;
+        pl.n_clusters = B < cap ? B : cap;
+        const long long rounds = ((long long)B + pl.n_clusters - 1) / pl.n_clusters;
+        if (best_rounds < 0 || rounds < best_rounds) {
+            best = pl;
+            best_rounds = rounds;
+        }
+    }
+    if (best_rounds < 0) return cudaErrorInvalidConfiguration;
+
+    StageParams p;
+    memset(&p, 0, sizeof(p));
+    p.heat = heat;
+    p.B = B;
+    p.C = C;
+    p.H = H;
+    p.W = W;
+    p.Wp = (W + 3) & ~3;
+    p.K = K;
+    p.R = best.R;
+    p.S = best.S;
+    p.slot_floats = best.slot_floats;
+    p.lists = (raw_job ? LIST_RAW : 0) | (nms_job ? LIST_NMS : 0);
+    p.use_tma = use_tma ? 1 : 0;
+    p.cs_log2 = best.cs_log2;
+    p.hist_words = best.hist_words;
+    p.slot_area = best.slot_area;
+    p.dep_off = best.dep_off;
+    p.ctr = ws.ctr;
+    p.cand = ws.cand;
+    p.mp.heat = heat;
+    p.mp.C = C;
+    p.mp.H = H;
+    p.mp.W = W;
+    p.mp.K = K;
+    p.mp.ctr = ws.ctr;
+    p.mp.cand = ws.cand;
+    p.mp.det = ws.det;
+    int n = 0;
+    if (raw_job) {
+        p.mp.list[n] = 0;
+        p.mp.job[n] = *raw_job;
+        ++n;
+    }
+    if (nms_job) {
+        p.mp.list[n] = 1;
+        p.mp.job[n] = *nms_job;
+        ++n;
+    }
+    if (n == 1) {
+        p.mp.list[1] = p.mp.list[0];
+        p.mp.job[1] = p.mp.job[0];
+    }
+    p.n_jobs = n;
+    p.do_frustum = do_frustum ? 1 : 0;
+    p.pc_dep = pc_dep;
+    p.max_pc_dist = max_pc_dist;
+    p.pc_hm = pc_hm;
+    p.assoc = assoc;
+    p.recs = ws.recs;
+    p.prof = getenv("CFD3D_PROF") ? 1 : 0;
+    p.mp.prof = p.prof;
+
+    cudaError_t e = cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)best.smem);
+    if (e != cudaSuccess) return e;
+    if (best.cs > 8) {
+        e = cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e != cudaSuccess) return e;
+    }
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    memset(&cfg, 0, sizeof(cfg));
+    launch_cfg(best, best.n_clusters * best.cs, st, &cfg, attr);
+    if (getenv("CFD3D_VERBOSE"))
+        fprintf(stderr, "[cfd3d] stage plan: B=%d cs=%d clusters=%d R=%d S=%d slot=%dB area=%d dep_off=%d smem=%zu tma=%d\n", B,
+                best.cs, best.n_clusters, best.R, best.S, best.slot_floats * 4, best.slot_area, best.dep_off, best.smem,
+                (int)use_tma);
+    e = cudaLaunchKernelEx(&cfg, fusion_stage_kernel, p);
+    if (e == cudaSuccess) ++*launches;
+    return e;
+}
+
+int debug_read_prof(long long* out, int n_cta) {
+    if (n_cta > 1024) n_cta = 1024;
+    return (int)cudaMemcpyFromSymbol(out, g_prof, sizeof(long long) * PROF_PTS * n_cta);
+}
+
+}  // namespace cf

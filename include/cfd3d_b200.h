@@ -158,7 +158,8 @@ enum {
     CF_KERNEL_ASSOC = 2,       /* per-ROI nearest-depth radar association */
     CF_KERNEL_PAINT = 3,       /* ordered pc_hm / pc_dep paint */
     CF_KERNEL_PILLAR_RECTS = 4, /* radar point -> pillar rectangle */
-    CF_KERNEL_PEAK_FILTER = 5   /* filter pass: re-read (L2) + survivors >= tau */
+    CF_KERNEL_PEAK_FILTER = 5,  /* filter pass: re-read (L2) + survivors >= tau */
+    CF_KERNEL_STAGE = 6         /* the fused stage kernel: one cluster per frame, all of the above in one launch */
 };
 CF_API int cf_set_kernel_events(int kernel_id, void* ev_start, void* ev_stop);
 

@@ -1,0 +1,49 @@
+"""Development aid: per-phase clock64 stamps of the fused stage kernel (CFD3D_PROF=1), cfg2 by default."""
+import ctypes as C
+import os
+import sys
+
+os.environ["CFD3D_PROF"] = "1"
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np
+import torch
+
+import bench
+from centerfusiondetect3d_b200 import _lib, ops, synthetic as syn
+
+wl = syn.WORKLOADS[sys.argv[1] if len(sys.argv) > 1 else "cfg2"]
+B = int(sys.argv[2]) if len(sys.argv) > 2 else min(wl.B, 32)
+dev = "cuda:0"
+host = bench.make_host_inputs(wl, B, seed=1234)
+keys = bench.STAGE_KEYS + ("calib", "pc_dep")
+d = {k: torch.from_numpy(np.ascontiguousarray(host[k])).to(dev) for k in keys}
+cfg = bench.Cfg(wl.K, wl.max_pc_dist)
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+L = _lib.lib()
+L.cf_debug_read_prof.argtypes = [C.c_void_p, C.c_int]
+names = ["start->sync0", "passA", "sync1", "tau", "passB+flush", "sync2", "merge", "sync3", "assoc", "sync4", "paint"]
+for rep in range(4):
+    _ = flush.view(torch.int32).sum()  # evict by READING: leaves clean lines, like the heads of a real pipeline
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    bench.run_stage(ops, wl, d, cfg)
+    e1.record()
+    torch.cuda.synchronize()
+    n_cta = 128
+    buf = np.zeros((n_cta, 32), dtype=np.int64)
+    L.cf_debug_read_prof(buf.ctypes.data, n_cta)
+    dt = np.diff(buf[:, :12], axis=1) / 1.965e3  # us at 1965 MHz
+    print("rep %d  call %.1f us   per-phase us over %d CTAs (min / mean / max); total mean %.1f" % (
+        rep, e0.elapsed_time(e1) * 1e3, n_cta, (buf[:, 11] - buf[:, 0]).mean() / 1.965e3))
+    for i, nm in enumerate(names):
+        print("   %-14s %7.2f %7.2f %7.2f" % (nm, dt[:, i].min(), dt[:, i].mean(), dt[:, i].max()))
+    ex = buf[:, [0, 15, 1]], buf[:, [4, 12, 13, 14, 5]]
+    mg = np.diff(buf[:, 16:22], axis=1) / 1.965e3
+    for r in (0, 1):
+        print("   merge rank %d: load %.2f  rank %.2f  gather %.2f  epilogue %.2f  sync %.2f" % ((r,) + tuple(mg[r::4].mean(axis=0))))
+    print("   passB: loop %.2f  sync %.2f  atomics+sync %.2f  copy %.2f" % tuple((np.diff(ex[1], axis=1) / 1.965e3).mean(axis=0)))
+    print("   passB loop per CTA (warp 0):", " ".join("%.0f" % x for x in (buf[:, 12] - buf[:, 4]) / 1.965e3))
+    for r in range(4):
+        print("   rank %d mean:" % r, " ".join("%6.2f" % x for x in dt[r::4].mean(axis=0)))
