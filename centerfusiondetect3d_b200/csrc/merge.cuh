@@ -1,10 +1,13 @@
 // merge.cuh -- per-frame merge of the peak-decode survivors: exact sorted top-K under the total order
-// (score desc, class asc, index asc) + the topk / frustum / decode epilogue.  Device code, executed by ONE CTA of
-// T threads per (frame, list) inside the fused stage kernel (stage.cu).
+// (score desc, class asc, index asc) + the topk / frustum / decode epilogue.  Device code of the fused stage kernel
+// (stage.cu), spread over the CTAs of a frame's cluster:
 //
-// Latency shape: the head values of the K peaks are gathered FIRST, all at once (every thread issues its loads
-// back to back into registers, then parks them in shared memory: one DRAM round trip for the whole job), the
-// epilogues then compute from shared memory and only store.
+//   select    the CTAs split the ranking of a job's survivor list between them (rank by counting); every ranked
+//             element is delivered to every CTA's shared memory (xs_comp[job][rank], st.shared::cluster);
+//   tail      detection k belongs to CTA k % CS from here on: that CTA gathers the head values of ITS detections (all
+//             loads of both jobs issued back to back: one DRAM round trip; one SM sustains only a few hundred
+//             outstanding scattered loads, so the cluster shares them), runs the frustum geometry / decode epilogue
+//             from shared memory and keeps the frustum parameters local for the association.
 //
 // Replaces (reference, src/lib/): model/utils.py:6-38 topk (second level), :41-72 transposeAndGetFeature; the
 // gathers + box / alpha / threshold block of utils/pointcloud.py:347-380; model/decode.py:47-172.
@@ -68,21 +71,130 @@ struct FrameSrc {
     }
 };
 
-// frustum geometry of the K detections from the gathered heads: 4 lanes per detection, the three atan2 and then
-// sin / cos evaluated side by side (fp64, rounded once: the parity contract of geometry.cuh)
-// reference src/lib/utils/pointcloud.py:348-380
+// shared memory of the selection
+struct MergeSmem {
+    SelScratch sc;
+    unsigned long long win[MERGE_WIN];
+};
+
+// more survivors than the rank window (dense ties), or a list flagged overflowed: exact block-level selection of the
+// K best into win[] from the list or, failing that, from the frame itself.  Slow, exact, rare -> never inlined.
 template <int T>
-__device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const MergeJob& jb, int b, const int* sind,
-                                                 const float* gath) {
-    const int K = p.K, W = p.W;
-    const int tid = threadIdx.x, j = tid & 3;
+__device__ __noinline__ void select_overflow(const MergeParams& p, MergeSmem& sm, int b, int list, uint32_t n,
+                                             const unsigned long long* cand) {
+    const int K = p.K, HWi = p.H * p.W;
+    if (n <= (uint32_t)CAND_CAP) {
+        ListSrc<T> src;
+        src.cand = cand;
+        src.n_in = (int)n;
+        src.n_round = (src.n_in + T - 1) / T * T;
+        block_select<T, 1>(src, K, sm.sc, [&](uint32_t slot, unsigned long long c) { sm.win[slot] = c; });
+    } else {
+        FrameSrc<T> src;
+        src.frame = p.heat + (size_t)b * p.C * HWi;
+        src.CH = p.C * p.H;
+        src.H = p.H;
+        src.W = p.W;
+        src.n_round = (p.C * HWi + T - 1) / T * T;
+        src.nms = list == 1;
+        block_select<T, 1>(src, K, sm.sc, [&](uint32_t slot, unsigned long long c) { sm.win[slot] = c; });
+    }
+    __syncthreads();
+}
+
+// part `part` of `parts` of the ranking of job li: emit(rank, composite) for this part's elements of the K best.
+// Composites are distinct, so ranks are a permutation and the parts' outputs are disjoint.
+template <int T, class Emit>
+__device__ __forceinline__ void merge_select_part(const MergeParams& p, MergeSmem& sm, int b, int li, int part,
+                                                  int parts, Emit&& emit) {
+    const int tid = threadIdx.x;
+    const int list = p.list[li];
+    const int K = p.K;
+    CF_MERGE_PROF(0);
+    const uint32_t n = __ldcg(p.ctr + ((size_t)b * 2 + list) * CTR_STRIDE);  // survivors appended (>= K by construction)
+    const unsigned long long* cand = p.cand + ((size_t)b * 2 + list) * CAND_CAP;
+    int nw;  // entries of win[] to rank
+    const bool listed = n <= (uint32_t)MERGE_WIN;
+    if (listed) {
+        for (int t = tid; t < (int)n; t += T) sm.win[t] = __ldcg(cand + t);
+        nw = (int)n;
+        __syncthreads();
+    } else {
+        select_overflow<T>(p, sm, b, list, n, cand);  // rare, out of line: keeps the common path's code small
+        nw = K;
+    }
+    CF_MERGE_PROF(1);
+    // rank by counting; four independent partial counts per thread keep the shared-memory broadcasts in flight.
+    // The parts split the list by position (the list is the same in every CTA); after select_overflow the order of
+    // win[] differs from CTA to CTA, so there the parts split by pixel identity instead.
+    for (int t = listed ? tid * parts + part : tid; t < nw; t += listed ? T * parts : T) {
+        const unsigned long long me = sm.win[t];
+        if (!listed && (int)(comp_gidx(me) % (uint32_t)parts) != part) continue;
+        int r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+        int jx = 0;
+        for (; jx + 4 <= nw; jx += 4) {
+            r0 += (sm.win[jx] > me) ? 1 : 0;
+            r1 += (sm.win[jx + 1] > me) ? 1 : 0;
+            r2 += (sm.win[jx + 2] > me) ? 1 : 0;
+            r3 += (sm.win[jx + 3] > me) ? 1 : 0;
+        }
+        for (; jx < nw; ++jx) r0 += (sm.win[jx] > me) ? 1 : 0;
+        const int rank = (r0 + r1) + (r2 + r3);
+        if (rank < K) emit(rank, me);
+    }
+    __syncthreads();  // win[] is reused by the next job of this CTA
+    CF_MERGE_PROF(2);
+}
+
+// detections kl0 .. kl0+nb of this CTA (detection k = first + kl * stride): head values of job N-channel table gt into
+// gath[(kl - kl0) * GATH_STRIDE + slot].  comps = the job's sorted composites xs_comp[job].
+template <int T, int N>
+__device__ __forceinline__ void gather_local(const GatherTab& gt, int b, size_t HW, const unsigned long long* comps,
+                                             int first, int stride, int kl0, int nb, float* gath) {
+    const int total = nb * N;
+    constexpr int U = 4;
+    for (int t0 = threadIdx.x; t0 < total; t0 += T * U) {
+        float v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int t = t0 + u * T;
+            v[u] = 0.0f;
+            if (t < total) {
+                const int kl = t / N, s = t - kl * N;
+                const float* base = gt.base[s];
+                const uint32_t ind = comp_gidx(comps[first + (kl0 + kl) * stride]) % (uint32_t)HW;
+                if (base) v[u] = __ldg(base + ((size_t)b * gt.nch[s] + gt.ch[s]) * HW + ind);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int t = t0 + u * T;
+            if (t < total) {
+                const int kl = t / N, s = t - kl * N;
+                gath[kl * GATH_STRIDE + s] = v[u];
+            }
+        }
+    }
+}
+
+// frustum geometry of this CTA's detections kl0 .. kl0+nb from the gathered heads: 4 lanes per detection, the three
+// atan2 and then sin / cos evaluated side by side (fp64, rounded once: the parity contract of geometry.cuh).  The
+// frustum parameters stay in shared memory (sdet[kl]) for the association.
+// reference src/lib/utils/pointcloud.py:348-380
+// Executed by the thread group [0, T) given as (tid, T): whole warps.
+__device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const MergeJob& jb, int b,
+                                                 const unsigned long long* comps, int first, int stride, int kl0, int nb,
+                                                 const float* gath, DetParam* sdet, int tid, int T) {
+    const int K = p.K, W = p.W, HWi = p.H * p.W;
+    const int j = tid & 3;
     const float* calib = jb.fh.calib + 12 * (size_t)b;
     const float cal0 = __ldg(calib + 0), cal2 = __ldg(calib + 2);
-    for (int k0 = 0; k0 < K; k0 += T / 4) {
-        const int k = k0 + (tid >> 2);
-        const bool live = k < K;
-        const float* g = gath + (live ? k : 0) * GATH_STRIDE;
-        const int ind = live ? sind[k] : 0;
+    for (int q0 = 0; q0 < nb; q0 += T / 4) {
+        const int q = q0 + (tid >> 2);
+        const bool live = q < nb;
+        const int kl = kl0 + (live ? q : 0), k = first + kl * stride;
+        const float* g = gath + (live ? q : 0) * GATH_STRIDE;
+        const int ind = (int)(comp_gidx(comps[k]) % (uint32_t)HWi);
         const int y = ind / W, x = ind - y * W;
         const float xf = __fadd_rn((float)x, 0.5f), yf = __fadd_rn((float)y, 0.5f);
         float w = g[FS_WH], h = g[FS_WH + 1];
@@ -104,37 +216,46 @@ __device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const Mer
         const float at1 = __shfl_sync(FULL, at, l0), at2 = __shfl_sync(FULL, at, l0 + 1),
                     ray = __shfl_sync(FULL, at, l0 + 2);
         const float yaw = yaw_wrap(alpha_blend(r[1], r[5], at1, at2), ray);  // :372, :230-235
-        const float cs = j == 0 ? (float)cos((double)yaw) : (j == 1 ? (float)sin((double)yaw) : 0.0f);
-        const float c = __shfl_sync(FULL, cs, l0), s = __shfl_sync(FULL, cs, l0 + 1);
+        const float cs_ = j == 0 ? (float)cos((double)yaw) : (j == 1 ? (float)sin((double)yaw) : 0.0f);
+        const float c = __shfl_sync(FULL, cs_, l0), s = __shfl_sync(FULL, cs_, l0 + 1);
         if (live && j == 0) {
             d.depth = g[FS_DEPTH];
             d.thr = thr_from_cs(c, s, g[FS_DIM + 1], g[FS_DIM + 2]);  // :380
             d.ind = ind;
             d.pad_ = 0;
+            sdet[kl] = d;
             const size_t o = (size_t)b * K + k;
-            p.det[o] = d;
             if (jb.fo.thr) jb.fo.thr[o] = d.thr;
             if (jb.fo.inds) jb.fo.inds[o] = ind;
         }
     }
 }
 
+// score of a sorted composite: the key decodes to the heat value; the nms'd list carries suppressed pixels as key 0
+// (value +-0 * heat, i.e. the signed zero the reference's heat * keep produces)
+__device__ __forceinline__ float comp_score(const MergeParams& p, int b, unsigned long long c, int cls, int ind) {
+    const uint32_t key = comp_key(c);
+    float score = key2f(key);
+    if (key == KEY_ZERO) score = __fmul_rn(__ldg(p.heat + ((size_t)b * p.C + cls) * (p.H * p.W) + ind), 0.0f);
+    return score;
+}
+
 // reference src/lib/model/decode.py:38-41, :80-85, :132-165
-template <int T>
 __device__ __forceinline__ void epilogue_decode(const MergeParams& p, const MergeJob& jb, int b,
-                                                const unsigned long long* sorted, const int* sind, const float* gath) {
+                                                const unsigned long long* comps, int first, int stride, int kl0, int nb,
+                                                const float* gath, int tid, int T) {
     const int K = p.K, HWi = p.H * p.W;
     const cf_decode_heads_t& hd = jb.dec.heads;
     const cf_decode_out_t& o = jb.dec.out;
-    for (int k = threadIdx.x; k < K; k += T) {
-        const unsigned long long c = sorted[k];
-        const uint32_t gi = comp_gidx(c), key = comp_key(c);
+    for (int q = tid; q < nb; q += T) {
+        const int k = first + (kl0 + q) * stride;
+        const unsigned long long c = comps[k];
+        const uint32_t gi = comp_gidx(c);
         const int cls = (int)(gi / (uint32_t)HWi);
-        const int ind = sind[k];
+        const int ind = (int)(gi - (uint32_t)cls * (uint32_t)HWi);
         const int y = ind / p.W, x = ind - y * p.W;
-        const float* g = gath + k * GATH_STRIDE;
-        float score = key2f(key);
-        if (key == KEY_ZERO) score = __fmul_rn(__ldg(p.heat + ((size_t)b * p.C + cls) * HWi + ind), 0.0f);
+        const float* g = gath + q * GATH_STRIDE;
+        float score = comp_score(p, b, c, cls, ind);
         const size_t ok = (size_t)b * K + k;
         if (hd.uncertainty) score = __fmul_rn(score, expf(-expf(g[DS_UNC])));
         o.scores[ok] = score;
@@ -178,177 +299,71 @@ __device__ __forceinline__ void epilogue_decode(const MergeParams& p, const Merg
     }
 }
 
-// plain channel copies of the decode heads out of the gather buffer: out[b,k,ch] = gath[k][slot0 + ch]
-template <int T>
-__device__ __forceinline__ void copy_head(const float* head, float* out, int nch, int slot0, int b, int K,
-                                          const float* gath) {
+// plain channel copies of the decode heads out of the gather buffer: out[b,k,ch] = gath[q][slot0 + ch]
+__device__ __forceinline__ void copy_head(const float* head, float* out, int nch, int slot0, int b, int K, int first,
+                                          int stride, int kl0, int nb, const float* gath, int tid, int T) {
     if (!head) return;
-    for (int t = threadIdx.x; t < K * nch; t += T) {
-        const int k = t / nch, ch = t - k * nch;
-        out[((size_t)b * K + k) * nch + ch] = gath[k * GATH_STRIDE + slot0 + ch];
+    for (int t = tid; t < nb * nch; t += T) {
+        const int q = t / nch, ch = t - q * nch;
+        const int k = first + (kl0 + q) * stride;
+        out[((size_t)b * K + k) * nch + ch] = gath[q * GATH_STRIDE + slot0 + ch];
     }
 }
 
-// shared memory of merge_frame: this struct followed by the gather buffer (K * GATH_STRIDE floats)
-struct MergeSmem {
-    SelScratch sc;
-    unsigned long long win[MERGE_WIN];
-    unsigned long long sorted[CF_MAX_K];
-    int sind[CF_MAX_K];
-};
-// [MergeSmem | gather buffer K*GATH_STRIDE floats | peak indices of both jobs 2*K ints]
-__host__ __device__ inline size_t merge_gath_off() { return ((sizeof(MergeSmem) + 127) / 128) * 128; }
-__host__ __device__ inline size_t merge_ind_off(int K) {
-    return merge_gath_off() + (((size_t)K * GATH_STRIDE * sizeof(float) + 127) / 128) * 128;
-}
-__host__ __device__ inline size_t merge_smem_bytes(int K) {
-    return merge_ind_off(K) + (((size_t)2 * K * sizeof(int) + 127) / 128) * 128;
-}
-
-// more survivors than the rank window (dense ties), or a list flagged overflowed: exact block-level selection of the
-// K best into win[] from the list or, failing that, from the frame itself.  Slow, exact, rare -> never inlined.
+// the tail of the jobs for this CTA's detections (k = first + kl * stride, kl < n_local), in batches of GB detections:
+// gathers of all jobs, then their epilogues.  gath holds n_jobs * GB * GATH_STRIDE floats.
 template <int T>
-__device__ __noinline__ void select_overflow(const MergeParams& p, MergeSmem& sm, int b, int list, uint32_t n,
-                                             const unsigned long long* cand) {
+__device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int b, int first, int stride, int n_local,
+                                           const unsigned long long* xs_comp, float* gath, int GB, DetParam* sdet) {
     const int K = p.K, HWi = p.H * p.W;
-    if (n <= (uint32_t)CAND_CAP) {
-        ListSrc<T> src;
-        src.cand = cand;
-        src.n_in = (int)n;
-        src.n_round = (src.n_in + T - 1) / T * T;
-        block_select<T, 1>(src, K, sm.sc, [&](uint32_t slot, unsigned long long c) { sm.win[slot] = c; });
-    } else {
-        FrameSrc<T> src;
-        src.frame = p.heat + (size_t)b * p.C * HWi;
-        src.CH = p.C * p.H;
-        src.H = p.H;
-        src.W = p.W;
-        src.n_round = (p.C * HWi + T - 1) / T * T;
-        src.nms = list == 1;
-        block_select<T, 1>(src, K, sm.sc, [&](uint32_t slot, unsigned long long c) { sm.win[slot] = c; });
-    }
-    __syncthreads();
-}
-
-// step 1 of a job: the K best survivors, sorted, into sm.sorted[] / sm.sind[] (flat pixel of each peak)
-template <int T>
-__device__ __forceinline__ void merge_select(const MergeParams& p, MergeSmem& sm, int b, int li) {
-    const int tid = threadIdx.x;
-    const int list = p.list[li];
-    const int K = p.K;
-    const int HWi = p.H * p.W;
-    CF_MERGE_PROF(0);
-    const uint32_t n = __ldcg(p.ctr + ((size_t)b * 2 + list) * CTR_STRIDE);  // survivors appended (>= K by construction)
-    const unsigned long long* cand = p.cand + ((size_t)b * 2 + list) * CAND_CAP;
-
-    int nw;  // entries of win[] to rank
-    if (n <= (uint32_t)MERGE_WIN) {
-        for (int t = tid; t < (int)n; t += T) sm.win[t] = __ldcg(cand + t);
-        nw = (int)n;
+    for (int kl0 = 0; kl0 < n_local; kl0 += GB) {
+        const int nb = min(GB, n_local - kl0);
+        for (int li = 0; li < n_jobs; ++li) {
+            const MergeJob& jb = p.job[li];
+            float* g = gath + (size_t)li * GB * GATH_STRIDE;
+            if (jb.epilogue == EPI_FRUSTUM)
+                gather_local<T, FS_N>(jb.gt, b, (size_t)HWi, xs_comp + li * K, first, stride, kl0, nb, g);
+            else if (jb.epilogue == EPI_DECODE)
+                gather_local<T, DS_N>(jb.gt, b, (size_t)HWi, xs_comp + li * K, first, stride, kl0, nb, g);
+        }
         __syncthreads();
-    } else {
-        select_overflow<T>(p, sm, b, list, n, cand);  // rare, out of line: keeps the common path's code small
-        nw = K;
-    }
-
-    CF_MERGE_PROF(1);
-    // rank by counting (composites are distinct: ranks are a permutation); the K best land in sorted[].  Four
-    // independent partial counts per thread keep the shared-memory broadcasts in flight.
-    for (int t = tid; t < nw; t += T) {
-        const unsigned long long me = sm.win[t];
-        int r0 = 0, r1 = 0, r2 = 0, r3 = 0;
-        int jx = 0;
-        for (; jx + 4 <= nw; jx += 4) {
-            r0 += (sm.win[jx] > me) ? 1 : 0;
-            r1 += (sm.win[jx + 1] > me) ? 1 : 0;
-            r2 += (sm.win[jx + 2] > me) ? 1 : 0;
-            r3 += (sm.win[jx + 3] > me) ? 1 : 0;
-        }
-        for (; jx < nw; ++jx) r0 += (sm.win[jx] > me) ? 1 : 0;
-        const int rank = (r0 + r1) + (r2 + r3);
-        if (rank < K) {
-            sm.sorted[rank] = me;
-            const uint32_t g = comp_gidx(me);
-            sm.sind[rank] = (int)(g % (uint32_t)HWi);
-        }
-    }
-    __syncthreads();
-    CF_MERGE_PROF(2);
-}
-
-// this CTA's share (pairs t = first, first + stride, ...) of the head gathers of one job: values go straight into the
-// gather buffer of the CTA that owns the job (st.shared::cluster; `gath_remote` = its shared::cluster address).
-// One SM sustains only a few hundred outstanding scattered loads, so the K * N loads of a job are spread over the
-// whole cluster.
-template <int T, int N>
-__device__ __forceinline__ void gather_share(const GatherTab& gt, int b, int K, size_t HW, const int* inds,
-                                             uint32_t gath_remote, int first, int stride) {
-    const int total = K * N;
-    constexpr int U = 4;
-    for (int t0 = first; t0 < total; t0 += stride * U) {
-        float v[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int t = t0 + u * stride;
-            v[u] = 0.0f;
-            if (t < total) {
-                const int k = t / N, s = t - k * N;
-                const float* base = gt.base[s];
-                if (base) v[u] = __ldg(base + ((size_t)b * gt.nch[s] + gt.ch[s]) * HW + inds[k]);
+        CF_MERGE_PROF(3);
+        // the epilogues of the two jobs run side by side, each on its own half of the CTA's warps
+        const int half = n_jobs == 2 ? T / 2 : T;
+        const int li = n_jobs == 2 ? (int)threadIdx.x / half : 0;
+        const int gt = (int)threadIdx.x - li * half;
+        {
+            const MergeJob& jb = p.job[li];
+            const unsigned long long* comps = xs_comp + li * K;
+            const float* g = gath + (size_t)li * GB * GATH_STRIDE;
+            if (jb.epilogue == EPI_TOPK) {
+                for (int q = gt; q < nb; q += half) {
+                    const int k = first + (kl0 + q) * stride;
+                    const unsigned long long c = comps[k];
+                    const uint32_t gi = comp_gidx(c);
+                    const int cls = (int)(gi / (uint32_t)HWi);
+                    const int ind = (int)(gi - (uint32_t)cls * (uint32_t)HWi);
+                    const int y = ind / p.W, x = ind - y * p.W;
+                    const size_t o = (size_t)b * K + k;
+                    if (jb.topk.scores) jb.topk.scores[o] = comp_score(p, b, c, cls, ind);
+                    if (jb.topk.inds) jb.topk.inds[o] = ind;
+                    if (jb.topk.classes) jb.topk.classes[o] = cls;
+                    if (jb.topk.ys) jb.topk.ys[o] = y;
+                    if (jb.topk.xs) jb.topk.xs[o] = x;
+                }
+            } else if (jb.epilogue == EPI_FRUSTUM) {
+                epilogue_frustum(p, jb, b, comps, first, stride, kl0, nb, g, sdet, gt, half);
+            } else if (jb.epilogue == EPI_DECODE) {
+                epilogue_decode(p, jb, b, comps, first, stride, kl0, nb, g, gt, half);
+                copy_head(jb.dec.heads.rot, jb.dec.out.rot, 8, DS_ROT, b, K, first, stride, kl0, nb, g, gt, half);
+                copy_head(jb.dec.heads.dim, jb.dec.out.dim, 3, DS_DIM, b, K, first, stride, kl0, nb, g, gt, half);
+                copy_head(jb.dec.heads.nuscenes_att, jb.dec.out.nuscenes_att, 8, DS_ATT, b, K, first, stride, kl0, nb, g, gt, half);
+                copy_head(jb.dec.heads.velocity, jb.dec.out.velocity, 3, DS_VEL, b, K, first, stride, kl0, nb, g, gt, half);
             }
         }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int t = t0 + u * stride;
-            if (t < total) {
-                const int k = t / N, s = t - k * N;
-                asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(gath_remote + 4u * (uint32_t)(k * GATH_STRIDE + s)),
-                             "f"(v[u])
-                             : "memory");
-            }
-        }
+        __syncthreads();
+        CF_MERGE_PROF(4);
     }
-}
-
-// step 3 of a job: epilogue from the gathered heads
-template <int T>
-__device__ __forceinline__ void merge_epilogue(const MergeParams& p, MergeSmem& sm, int b, int li) {
-    const int tid = threadIdx.x;
-    const MergeJob& jb = p.job[li];
-    const int K = p.K;
-    const int HWi = p.H * p.W;
-    const float* gath = reinterpret_cast<const float*>(reinterpret_cast<unsigned char*>(&sm) + merge_gath_off());
-    CF_MERGE_PROF(3);
-    if (jb.epilogue == EPI_TOPK) {
-        for (int k = tid; k < K; k += T) {
-            const unsigned long long c = sm.sorted[k];
-            const uint32_t g = comp_gidx(c), key = comp_key(c);
-            const int cls = (int)(g / (uint32_t)HWi);
-            const int ind = sm.sind[k];
-            const int y = ind / p.W, x = ind - y * p.W;
-            float score = key2f(key);
-            if (key == KEY_ZERO) score = __fmul_rn(__ldg(p.heat + ((size_t)b * p.C + cls) * HWi + ind), 0.0f);
-            const size_t o = (size_t)b * K + k;
-            if (jb.topk.scores) jb.topk.scores[o] = score;
-            if (jb.topk.inds) jb.topk.inds[o] = ind;
-            if (jb.topk.classes) jb.topk.classes[o] = cls;
-            if (jb.topk.ys) jb.topk.ys[o] = y;
-            if (jb.topk.xs) jb.topk.xs[o] = x;
-        }
-    } else if (jb.epilogue == EPI_FRUSTUM || jb.epilogue == EPI_DECODE) {
-        if (jb.epilogue == EPI_FRUSTUM) {
-            epilogue_frustum<T>(p, jb, b, sm.sind, gath);
-        } else {
-            epilogue_decode<T>(p, jb, b, sm.sorted, sm.sind, gath);
-            copy_head<T>(jb.dec.heads.rot, jb.dec.out.rot, 8, DS_ROT, b, K, gath);
-            copy_head<T>(jb.dec.heads.dim, jb.dec.out.dim, 3, DS_DIM, b, K, gath);
-            copy_head<T>(jb.dec.heads.nuscenes_att, jb.dec.out.nuscenes_att, 8, DS_ATT, b, K, gath);
-            copy_head<T>(jb.dec.heads.velocity, jb.dec.out.velocity, 3, DS_VEL, b, K, gath);
-        }
-    }
-    CF_MERGE_PROF(4);
-    __syncthreads();  // sm is reused by the next job of this CTA
-    CF_MERGE_PROF(5);
 }
 
 }  // namespace cf

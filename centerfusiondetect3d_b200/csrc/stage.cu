@@ -122,6 +122,11 @@ struct StageParams {
     int hist_words;    // 32-bit words of this CTA's part of the histogram (both lists)
     int slot_area;     // bytes of the slot area (also hosts the merge scratch, the depth plane and the owner map)
     int dep_off;       // byte offset of the staged depth plane inside the slot area, -1: read it from global memory
+    // byte offsets inside the slot area once the heat-map is done with it: [paint records K | sorted composites 2K |
+    // selection scratch | gather buffers | frustum parameters | matches | depth plane]; the owner map of the paint
+    // takes everything behind the records
+    int off_comp, off_msm, off_gath, off_det, off_best, off_own;
+    int GB;            // detections per gather batch
     uint32_t* ctr;
     unsigned long long* cand;
     MergeParams mp;
@@ -227,10 +232,12 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ uint64_t full[MAX_SLOTS];
     __shared__ uint64_t dep_bar;
+    __shared__ volatile uint32_t s_issued[MAX_SLOTS];  // ring mode: bulk copies started into each slot so far
     __shared__ uint32_t s_scan[2 * (SNW + 1)];
     __shared__ uint32_t s_tops[2][MAX_CS];
     __shared__ uint32_t s_mytop[2];
     __shared__ uint32_t s_nwl;  // entries of the pass-B work list
+    __shared__ uint32_t s_cnt[2], s_base[2];  // pass B2: survivors of this CTA per list, their base in the frame's list
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t rank = cl_rank(), cs = cl_size();
@@ -255,6 +262,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     const int LPF = n + n_ref;                         // bulk copies per frame
     const bool resident = use_tma && n_ref == 0;
 
+    if (tid < MAX_SLOTS) s_issued[tid] = 0u;
     if (tid == 0) {
         for (int s = 0; s < S; ++s) mbar_init(&full[s], 1);
         mbar_init(&dep_bar, 1);
@@ -270,6 +278,12 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         unsigned long long* cand_raw = p.cand + (size_t)b * 2 * CAND_CAP;
         unsigned long long* cand_nms = cand_raw + CAND_CAP;
 
+        // sequence number (1-based, over the whole launch) of bulk copy L of this frame on its slot
+        auto load_seq = [&](int L) -> uint32_t {
+            const int s = L % S;
+            const int per_frame = (LPF - 1 - s) / S + 1;
+            return (uint32_t)(it * per_frame + L / S) + 1u;
+        };
         auto issue_load = [&](int L) {  // one thread: bulk copy L of this frame (L >= n: pass-B re-fetch)
             const int q = L < n ? L : L - n;
             const int s = L % S;
@@ -277,11 +291,23 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             const uint32_t bytes = (uint32_t)nr * (uint32_t)W * 4u;
             mbar_expect_tx(&full[s], bytes);
             tma_bulk_g2s(slots + (size_t)s * p.slot_floats, frame + (size_t)rr * W, bytes, &full[s]);
+            if (!resident) {
+                __threadfence_block();
+                s_issued[s] = load_seq(L);
+            }
         };
-        auto load_parity = [&](int L) -> uint32_t {  // phase parity of bulk copy L on its slot's barrier
+        // Wait for bulk copy L.  A parity wait is only meaningful once the copy has been STARTED (a barrier that is
+        // still two phases behind reports the awaited parity as complete), and in ring mode the warp that starts it
+        // is whichever one frees the slot: wait for the start first, then for the bytes.
+        auto wait_load = [&](int L) {
             const int s = L % S;
-            const int per_frame = (LPF - 1 - s) / S + 1;
-            return (uint32_t)(it * per_frame + L / S) & 1u;
+            const uint32_t seq = load_seq(L);
+            if (!resident) {
+                for (uint32_t spins = 0; s_issued[s] < seq; ++spins)
+                    if (spins > (1u << 26)) __trap();
+                __threadfence_block();
+            }
+            mbar_wait(&full[s], (seq - 1u) & 1u);
         };
         // consuming warp stages a chunk itself (inputs the TMA cannot take): padded row stride, -inf padding
         auto manual_fill = [&](float* tile, int rr, int nr) {
@@ -329,9 +355,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 const int rr = row_begin + q * R, nr = min(R, row_end - rr);
                 float* tile;
                 if (use_tma) {
-                    const int s = q % S;
-                    mbar_wait(&full[s], load_parity(q));
-                    tile = slots + (size_t)s * p.slot_floats;
+                    wait_load(q);
+                    tile = slots + (size_t)(q % S) * p.slot_floats;
                 } else {
                     tile = slots + (size_t)warp * p.slot_floats;
                     manual_fill(tile, rr, nr);
@@ -373,9 +398,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     // group whose maximum is suppressed contributes nothing (weaker bound, still a bound)
                     const bool have = x >= 0;
                     if (resident) {  // rows above / below may sit in the neighbouring chunks: wait for their copies
-                        if (__any_sync(FULL, have && r == 0 && q > 0)) mbar_wait(&full[(q - 1) % S], load_parity(q - 1));
-                        if (__any_sync(FULL, have && r == nr - 1 && q < n - 1))
-                            mbar_wait(&full[(q + 1) % S], load_parity(q + 1));
+                        if (__any_sync(FULL, have && r == 0 && q > 0)) wait_load(q - 1);
+                        if (__any_sync(FULL, have && r == nr - 1 && q < n - 1)) wait_load(q + 1);
                     }
                     if (have) {
                         const int g = rr + r;   // frame-matrix row
@@ -503,9 +527,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     const int rr = row_begin + q * R;
                     nr = min(R, row_end - rr);
                     if (use_tma) {
-                        const int s = L % S;
-                        mbar_wait(&full[s], load_parity(L));
-                        tile = slots + (size_t)s * p.slot_floats;
+                        wait_load(L);
+                        tile = slots + (size_t)(L % S) * p.slot_floats;
                     } else {
                         float* mt = slots + (size_t)warp * p.slot_floats;
                         manual_fill(mt, rr, nr);
@@ -534,24 +557,25 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                         if (q4[u].z >= tau_min) mask |= 4u << (4 * u);
                         if (q4[u].w >= tau_min) mask |= 8u << (4 * u);
                     }
-                    const uint32_t cnt = (uint32_t)__popc(mask);
-                    uint32_t inc = cnt;
-#pragma unroll
-                    for (int off = 1; off < 32; off <<= 1) {
-                        const uint32_t o = __shfl_up_sync(FULL, inc, off);
-                        if (lane >= off) inc += o;
-                    }
-                    uint32_t base = 0u;
-                    if (lane == 31) base = atomicAdd(&s_nwl, inc);
-                    base = __shfl_sync(FULL, base, 31);
-                    uint32_t slot = base + inc - cnt;
-                    while (mask) {
+                    // park the candidates: one reservation per block, then one ballot per (float4, pixel) position,
+                    // so that a blob's pixels, which cluster in a few lanes, are written side by side
+                    const uint32_t total = __reduce_add_sync(FULL, (uint32_t)__popc(mask));
+                    uint32_t slot = 0u;
+                    if (lane == 0) slot = atomicAdd(&s_nwl, total);
+                    slot = __shfl_sync(FULL, slot, 0);
+                    for (;;) {  // every lane that still holds candidates parks one per round (typically 1-2 rounds)
+                        const bool mine = mask != 0u;
+                        const uint32_t bal = __ballot_sync(FULL, mine);
+                        if (!bal) break;
+                        const uint32_t my = slot + (uint32_t)__popc(bal & lanemask_lt());
+                        slot += (uint32_t)__popc(bal);
+                        if (!mine) continue;
                         const int bit = __ffs(mask) - 1;
                         mask &= mask - 1;
                         const uint32_t code = ((uint32_t)q << 16) |
                                               (uint32_t)((item0 + (bit >> 2) * 32 + lane) * 4 + (bit & 3));
-                        if (slot < (uint32_t)WL_CAP) {
-                            wl[slot] = code;
+                        if (my < (uint32_t)WL_CAP) {
+                            wl[my] = code;
                         } else {  // work list full (dense survivors): test and append right here, lane by lane
                             float v;
                             uint32_t gi;
@@ -566,7 +590,6 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                                 if (gs < (uint32_t)CAND_CAP) cand_nms[gs] = make_comp(f2key(v), gi);
                             }
                         }
-                        ++slot;
                     }
                 }
                 // this visit was the last use of the slot's contents: start the re-fetch that reuses it, if any
@@ -578,27 +601,29 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             PROF(12);
             __syncthreads();
             PROF(13);
-            // B2: one candidate per thread; survivors go to the frame's lists with one atomic per warp and list
+            // B2: one candidate per thread.  Survivors are counted per CTA (shared-memory atomics), the frame's lists
+            // see ONE reservation per (CTA, list): same-address global atomics serialise at a few per microsecond.
             const uint32_t n_wl = min(s_nwl, (uint32_t)WL_CAP);
             for (uint32_t c0 = 0; c0 < n_wl; c0 += ST) {
                 const uint32_t c = c0 + (uint32_t)tid;
                 float v = 0.0f;
                 uint32_t gi = 0u;
                 bool sraw = false, snms = false;
+                if (tid < 2) s_cnt[tid] = 0u;
+                __syncthreads();
                 if (c < n_wl) cand_eval(wl[c], v, gi, sraw, snms);
                 const unsigned long long comp = make_comp(f2key(v), gi);
-#pragma unroll
-                for (int l = 0; l < 2; ++l) {
-                    const bool pr = l ? snms : sraw;
-                    const uint32_t bal = __ballot_sync(FULL, pr);
-                    if (!bal) continue;
-                    const int leader = __ffs(bal) - 1;
-                    uint32_t gb = 0u;
-                    if (lane == leader) gb = atomicAdd(l ? ctr_nms : ctr_raw, (uint32_t)__popc(bal));
-                    gb = __shfl_sync(FULL, gb, leader);
-                    const uint32_t gs = gb + (uint32_t)__popc(bal & lanemask_lt());
-                    if (pr && gs < (uint32_t)CAND_CAP) (l ? cand_nms : cand_raw)[gs] = comp;
-                }
+                const uint32_t bal0 = __ballot_sync(FULL, sraw), bal1 = __ballot_sync(FULL, snms);
+                uint32_t lb0 = 0u, lb1 = 0u;
+                if (bal0 && lane == 0) lb0 = atomicAdd(&s_cnt[0], (uint32_t)__popc(bal0));
+                if (bal1 && lane == 0) lb1 = atomicAdd(&s_cnt[1], (uint32_t)__popc(bal1));
+                lb0 = __shfl_sync(FULL, lb0, 0) + (uint32_t)__popc(bal0 & lanemask_lt());
+                lb1 = __shfl_sync(FULL, lb1, 0) + (uint32_t)__popc(bal1 & lanemask_lt());
+                __syncthreads();
+                if (tid < 2 && s_cnt[tid]) s_base[tid] = atomicAdd(tid ? ctr_nms : ctr_raw, s_cnt[tid]);
+                __syncthreads();
+                if (sraw && s_base[0] + lb0 < (uint32_t)CAND_CAP) cand_raw[s_base[0] + lb0] = comp;
+                if (snms && s_base[1] + lb1 < (uint32_t)CAND_CAP) cand_nms[s_base[1] + lb1] = comp;
             }
             PROF(14);
             fence_async_smem();
@@ -614,66 +639,48 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         cl_sync();  // survivor lists complete
         PROF(6);
 
-        // ---- merge: job j on CTA j (both on the one CTA of a single-CTA cluster, one after the other) -------------
-        // select: sorted top-K of the job's survivor list -> peak pixels published to every CTA;
-        // gather: the K x (14 | 30) head values, spread over the whole cluster, delivered into the owner's shared memory;
-        // epilogue: frustum geometry / decode outputs from shared memory.
+        // ---- select: the CTAs split the ranking of the jobs' survivor lists; sorted composites land everywhere -------
+        unsigned long long* xs_comp = reinterpret_cast<unsigned long long*>(smem + p.off_comp);  // [job][K]
         {
-            MergeSmem& msm = *reinterpret_cast<MergeSmem*>(smem);
-            int* xs_ind = reinterpret_cast<int*>(smem + merge_ind_off(K));  // [job][K], same offset in every CTA
-            const int rounds = cs == 1 ? p.n_jobs : 1;
-            for (int rd = 0; rd < rounds; ++rd) {
-                const int li_lo = cs == 1 ? rd : 0, li_hi = cs == 1 ? rd + 1 : p.n_jobs;
-                for (int li = li_lo; li < li_hi; ++li) {
-                    if ((uint32_t)(li & ((int)cs - 1)) != rank) continue;
-                    merge_select<ST>(p.mp, msm, b, li);
-                    if (p.mp.job[li].epilogue != EPI_TOPK) {
-                        const uint32_t dst = smem_u32(xs_ind + li * K);
-                        for (int k = tid; k < K; k += ST) {
-                            const uint32_t v = (uint32_t)msm.sind[k];
-                            for (uint32_t c = 0; c < cs; ++c) cl_st(cl_map(dst + 4u * k, c), v);
-                        }
+            MergeSmem& msm = *reinterpret_cast<MergeSmem*>(smem + p.off_msm);
+            const int nj = p.n_jobs;
+            const bool split = (int)cs >= nj;  // else (single-CTA cluster, two jobs): one after the other
+            const int n_sel = split ? 1 : nj;
+            for (int jj = 0; jj < n_sel; ++jj) {
+                const int li = split ? (int)rank % nj : jj;
+                const int part = split ? (int)rank / nj : 0, parts = split ? (int)cs / nj : 1;
+                const uint32_t dst = smem_u32(xs_comp + li * K);
+                merge_select_part<ST>(p.mp, msm, b, li, part, parts, [&](int r, unsigned long long c) {
+                    for (uint32_t c2 = 0; c2 < cs; ++c2) {
+                        const uint32_t ra = cl_map(dst + 8u * (uint32_t)r, c2);
+                        cl_st(ra, (uint32_t)c);
+                        cl_st(ra + 4u, (uint32_t)(c >> 32));
                     }
-                }
-                cl_sync();  // peak pixels of the jobs known everywhere
-                for (int li = li_lo; li < li_hi; ++li) {
-                    const MergeJob& jb = p.mp.job[li];
-                    const uint32_t owner = (uint32_t)(li & ((int)cs - 1));
-                    const uint32_t gath_remote = cl_map(smem_u32(smem + merge_gath_off()), owner);
-                    if (jb.epilogue == EPI_FRUSTUM)
-                        gather_share<ST, FS_N>(jb.gt, b, K, HW, xs_ind + li * K, gath_remote, (int)rank * ST + tid, (int)cs * ST);
-                    else if (jb.epilogue == EPI_DECODE)
-                        gather_share<ST, DS_N>(jb.gt, b, K, HW, xs_ind + li * K, gath_remote, (int)rank * ST + tid, (int)cs * ST);
-                }
-                cl_sync();  // gathered heads delivered
-                for (int li = li_lo; li < li_hi; ++li)
-                    if ((uint32_t)(li & ((int)cs - 1)) == rank) merge_epilogue<ST>(p.mp, msm, b, li);
+                });
             }
         }
         PROF(7);
-        if (!p.do_frustum) continue;
-        cl_sync();  // frustum parameters of the K detections are in the workspace
+        cl_sync();  // sorted top-K of every job known to every CTA
         PROF(8);
 
-        // ---- association: detection k on CTA k % CS, one warp per detection ---------------------------------------
-        // shared-memory layout of the tail (the merge scratch is dead): [sdet | sbest | srecs | owner map], the staged
-        // depth plane sits behind the merge scratch and is never overlapped
-        DetParam* sdet = reinterpret_cast<DetParam*>(smem);
-        unsigned long long* sbest = reinterpret_cast<unsigned long long*>(smem + (size_t)K * 32);
-        PaintRec* srecs = reinterpret_cast<PaintRec*>(smem + (size_t)K * 40);
+        // ---- tail: detection k belongs to CTA k % CS: gathers, frustum geometry / decode outputs ----------------------
+        const int n_local = (K - (int)rank + (int)cs - 1) / (int)cs;
+        DetParam* sdet = reinterpret_cast<DetParam*>(smem + p.off_det);
+        merge_tail<ST>(p.mp, p.n_jobs, b, (int)rank, (int)cs, n_local, xs_comp, reinterpret_cast<float*>(smem + p.off_gath),
+                       p.GB, sdet);
+        PROF(24);
+        if (!p.do_frustum) continue;
+
+        // ---- association: one warp per detection, ROI scan of the staged depth plane ---------------------------------
+        PaintRec* srecs = reinterpret_cast<PaintRec*>(smem);  // all K records, in detection order, in every CTA
         {
+            unsigned long long* sbest = reinterpret_cast<unsigned long long*>(smem + p.off_best);
             const float* dep = p.pc_dep + (size_t)b * 3 * HW;
             const float* dep0 = dep;
-            const int n_local = (K - (int)rank + (int)cs - 1) / (int)cs;
-            for (int t = tid; t < 2 * n_local; t += ST) {  // this CTA's frustum parameters: one L2 round trip
-                const size_t o = (size_t)b * K + rank + (size_t)(t >> 1) * cs;
-                reinterpret_cast<int4*>(sdet)[t] = __ldcg(reinterpret_cast<const int4*>(p.mp.det + o) + (t & 1));
-            }
             if (p.dep_off >= 0) {
                 mbar_wait(&dep_bar, (uint32_t)it & 1u);
                 dep0 = reinterpret_cast<const float*>(smem + p.dep_off);
             }
-            __syncthreads();
             for (int kl = warp; kl < n_local; kl += SNW) {
                 const DetParam d = sdet[kl];
                 const unsigned long long best =
@@ -703,7 +710,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         // ---- paint: this CTA's band of rows of pc_hm ----------------------------------------------------------------
         {
             const int y0 = (int)((long long)H * rank / cs), y1 = (int)((long long)H * (rank + 1) / cs);
-            const size_t own_off = ((size_t)K * 72 + 15) & ~(size_t)15;
+            const size_t own_off = (size_t)p.off_own;
             const int max_rows = max(1, (int)(((size_t)p.slot_area - own_off) / ((size_t)W * sizeof(int))));
             paint_band<ST, true>(srecs, K, H, W, y0, y1, p.pc_hm + (size_t)b * 3 * HW, nullptr,
                                  reinterpret_cast<int*>(smem + own_off), max_rows);
@@ -719,6 +726,7 @@ static size_t align_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct StagePlan {
     int cs, cs_log2, R, S, slot_floats, hist_words, slot_area, dep_off, n_clusters;
+    int off_comp, off_msm, off_gath, off_det, off_best, off_own, GB;
     size_t smem;
 };
 
@@ -753,17 +761,25 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
         if ((size_t)S * slot_bytes + fixed > SMEM_DYN_CAP) return false;
     }
     if (S < 1) return false;
-    const size_t merge_bytes = merge_smem_bytes(K);
+    // layout of the slot area once the heat-map is done with it (StageParams)
+    const int n_local_max = (K + cs - 1) / cs;
+    const int GB = n_local_max < 256 ? n_local_max : 256;
+    const size_t off_comp = align_up_sz((size_t)K * sizeof(PaintRec), 128);
+    const size_t off_msm = align_up_sz(off_comp + 2 * (size_t)K * 8, 128);
+    const size_t off_gath = align_up_sz(off_msm + sizeof(MergeSmem), 128);
+    const size_t off_det = align_up_sz(off_gath + 2 * (size_t)GB * GATH_STRIDE * 4, 128);
+    const size_t off_best = align_up_sz(off_det + (size_t)n_local_max * sizeof(DetParam), 128);
+    const size_t tail_end = align_up_sz(off_best + (size_t)n_local_max * 8, 128);
+    const size_t off_own = align_up_sz((size_t)K * sizeof(PaintRec), 16);
     size_t area = (size_t)S * slot_bytes;
-    if (area < merge_bytes) area = merge_bytes;
-    const size_t tail_bytes = align_up_sz((size_t)K * 72, 16) + (size_t)W * sizeof(int);  // det, best, records + >= 1 owner row
-    if (area < tail_bytes) area = tail_bytes;
+    if (area < tail_end) area = tail_end;
+    if (area < off_own + (size_t)W * sizeof(int)) area = off_own + (size_t)W * sizeof(int);  // >= 1 row of owner map
     int dep_off = -1;
     if (stage_dep) {
         const size_t dep_bytes = (size_t)H * W * 4;
-        if (dep_bytes < (1u << 20) && merge_bytes + dep_bytes + fixed <= SMEM_DYN_CAP) {
-            dep_off = (int)merge_bytes;
-            if (area < merge_bytes + dep_bytes) area = merge_bytes + dep_bytes;
+        if (dep_bytes < (1u << 20) && tail_end + dep_bytes + fixed <= SMEM_DYN_CAP) {
+            dep_off = (int)tail_end;
+            if (area < tail_end + dep_bytes) area = tail_end + dep_bytes;
         }
     }
     area = align_up_sz(area, 128);
@@ -776,6 +792,13 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
     pl->hist_words = hist_words;
     pl->slot_area = (int)area;
     pl->dep_off = dep_off;
+    pl->off_comp = (int)off_comp;
+    pl->off_msm = (int)off_msm;
+    pl->off_gath = (int)off_gath;
+    pl->off_det = (int)off_det;
+    pl->off_best = (int)off_best;
+    pl->off_own = (int)off_own;
+    pl->GB = GB;
     pl->smem = area + fixed;
     return true;
 }
@@ -839,7 +862,10 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
         if (force_cs && cs != force_cs) continue;
         StagePlan pl;
         if (!plan_for_cs(cs, C, H, W, K, use_tma, stage_dep, &pl)) continue;
-        const int cap = max_clusters(pl);
+        int cap = max_clusters(pl);
+        if (const char* e = getenv("CFD3D_MAX_CLUSTERS")) {  // tests: force several frames per cluster
+            if (atoi(e) >= 1 && atoi(e) < cap) cap = atoi(e);
+        }
         if (cap < 1) continue;
         pl.n_clusters = B < cap ? B : cap;
         const long long rounds = ((long long)B + pl.n_clusters - 1) / pl.n_clusters;
@@ -868,6 +894,13 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     p.hist_words = best.hist_words;
     p.slot_area = best.slot_area;
     p.dep_off = best.dep_off;
+    p.off_comp = best.off_comp;
+    p.off_msm = best.off_msm;
+    p.off_gath = best.off_gath;
+    p.off_det = best.off_det;
+    p.off_best = best.off_best;
+    p.off_own = best.off_own;
+    p.GB = best.GB;
     p.ctr = ws.ctr;
     p.cand = ws.cand;
     p.mp.heat = heat;

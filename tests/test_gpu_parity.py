@@ -182,6 +182,20 @@ def test_oracle_stage(ops, oracle, cfg_name, B):
     _check_stage(ops, oracle, wl, inp, B)
 
 
+@pytest.mark.parametrize("cs", [1, 2, 4, 8, 16])
+@pytest.mark.parametrize("cfg_name,B", [("cfg1", 3), ("cfg5", 3)])
+def test_oracle_stage_forced_plans(ops, oracle, monkeypatch, cfg_name, B, cs):
+    """Every execution plan of the fused stage kernel gives the oracle's result: cluster sizes 1..16 (heat-map share
+    resident in shared memory, or streamed through the slot ring and re-fetched by the filter pass) and clusters that
+    process several frames one after the other.  The host picks the plan per call; the two environment variables
+    (development aids of stage.cu) pin it."""
+    monkeypatch.setenv("CFD3D_CLUSTER", str(cs))
+    monkeypatch.setenv("CFD3D_MAX_CLUSTERS", "2")
+    wl = syn.WORKLOADS[cfg_name]
+    inp = make_case(wl, B)
+    _check_stage(ops, oracle, wl, inp, B)
+
+
 def test_oracle_dense_radar_with_pillars(ops, oracle):
     """cfg4: 2000 points/frame, pillar expansion on the GPU feeding the association."""
     wl = syn.WORKLOADS["cfg4"]

@@ -21,8 +21,7 @@ cfg = bench.Cfg(wl.K, wl.max_pc_dist)
 bench.run_stage(ops, wl, d, cfg)
 torch.cuda.synchronize()
 ws, _ = ops._stage_ws(torch.device(dev), B, wl.C, wl.H, wl.W, wl.K)
-hist_bytes = (B * 2 * 4096 * 4 + 255) // 256 * 256
-ctr = ws[hist_bytes:hist_bytes + B * 2 * 4 * 4].view(torch.int32).cpu().numpy().reshape(B, 2, 4)
-print("mode", "legacy" if os.environ.get("CFD3D_LEGACY") else "fused")
+ctr = ws[0:B * 2 * 4 * 4].view(torch.int32).cpu().numpy().reshape(B, 2, 4)
+print("cluster", os.environ.get("CFD3D_CLUSTER"), "chunk", os.environ.get("CFD3D_CHUNK_BYTES"))
 print("raw survivors per frame:", ctr[:, 0, 0])
 print("nms survivors per frame:", ctr[:, 1, 0])

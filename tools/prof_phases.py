@@ -23,7 +23,8 @@ cfg = bench.Cfg(wl.K, wl.max_pc_dist)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 L = _lib.lib()
 L.cf_debug_read_prof.argtypes = [C.c_void_p, C.c_int]
-names = ["start->sync0", "passA", "sync1", "tau", "passB+flush", "sync2", "merge", "sync3", "assoc", "sync4", "paint"]
+names = ["start->sync0", "passA", "sync1", "tau", "passB", "sync2", "select", "sync3", "tail", "assoc", "sync4", "paint"]
+order = [0, 1, 2, 3, 4, 5, 6, 7, 8, 24, 9, 10, 11]
 for rep in range(4):
     _ = flush.view(torch.int32).sum()  # evict by READING: leaves clean lines, like the heads of a real pipeline
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -34,15 +35,16 @@ for rep in range(4):
     n_cta = 128
     buf = np.zeros((n_cta, 32), dtype=np.int64)
     L.cf_debug_read_prof(buf.ctypes.data, n_cta)
-    dt = np.diff(buf[:, :12], axis=1) / 1.965e3  # us at 1965 MHz
+    dt = np.diff(buf[:, order], axis=1) / 1.965e3  # us at 1965 MHz
     print("rep %d  call %.1f us   per-phase us over %d CTAs (min / mean / max); total mean %.1f" % (
         rep, e0.elapsed_time(e1) * 1e3, n_cta, (buf[:, 11] - buf[:, 0]).mean() / 1.965e3))
     for i, nm in enumerate(names):
         print("   %-14s %7.2f %7.2f %7.2f" % (nm, dt[:, i].min(), dt[:, i].mean(), dt[:, i].max()))
     ex = buf[:, [0, 15, 1]], buf[:, [4, 12, 13, 14, 5]]
-    mg = np.diff(buf[:, 16:22], axis=1) / 1.965e3
-    for r in (0, 1):
-        print("   merge rank %d: load %.2f  rank %.2f  gather %.2f  epilogue %.2f  sync %.2f" % ((r,) + tuple(mg[r::4].mean(axis=0))))
+    mg = np.diff(buf[:, 16:19], axis=1) / 1.965e3
+    tl = np.diff(buf[:, [8, 19, 20]], axis=1) / 1.965e3
+    for r in range(4):
+        print("   rank %d: select load %.2f  rank %.2f | tail gather %.2f  epilogue %.2f" % ((r,) + tuple(mg[r::4].mean(axis=0)) + tuple(tl[r::4].mean(axis=0))))
     print("   passB: loop %.2f  sync %.2f  atomics+sync %.2f  copy %.2f" % tuple((np.diff(ex[1], axis=1) / 1.965e3).mean(axis=0)))
     print("   passB loop per CTA (warp 0):", " ".join("%.0f" % x for x in (buf[:, 12] - buf[:, 4]) / 1.965e3))
     for r in range(4):
