@@ -23,6 +23,8 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
 // flat pixel): depths that pass are positive, so the bit pattern orders like the value and the minimum key is
 // the first minimum in row-major ROI order.  Lanes run over columns, rows are unrolled: independent loads, no
 // division.
+// U = row loads in flight per thread: 8 hides shared-memory latency, global (L2) reads want more.
+template <int U = 8>
 __device__ __forceinline__ unsigned long long roi_scan(const float* dep, int H, int W, float x1, float y1,
                                                        float x2, float y2, float depth, float thr, int t, int NT) {
     int ya, yb, xa, xb;
@@ -39,7 +41,6 @@ __device__ __forceinline__ unsigned long long roi_scan(const float* dep, int H, 
     const int rows_par = NT / cols;         // rows processed side by side
     const int ty = t / cols, tx = t - ty * cols;
     if (ty >= rows_par) return best;
-    constexpr int U = 8;  // loads in flight per thread
     for (int xx = xa + tx; xx < xb; xx += cols) {
         for (int y0 = ya + ty; y0 < yb; y0 += U * rows_par) {
             float v[U];

@@ -683,8 +683,9 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             }
             for (int kl = warp; kl < n_local; kl += SNW) {
                 const DetParam d = sdet[kl];
-                const unsigned long long best =
-                    warp_min_u64(roi_scan(dep0, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32));
+                const unsigned long long best = warp_min_u64(
+                    p.dep_off >= 0 ? roi_scan<8>(dep0, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32)
+                                   : roi_scan<24>(dep0, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32));
                 if (lane == 0) sbest[kl] = best;
             }
             __syncthreads();
@@ -866,6 +867,7 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
         if (const char* e = getenv("CFD3D_MAX_CLUSTERS")) {  // tests: force several frames per cluster
             if (atoi(e) >= 1 && atoi(e) < cap) cap = atoi(e);
         }
+        if (getenv("CFD3D_VERBOSE")) fprintf(stderr, "[cfd3d]   cs=%d: %d co-resident clusters (smem %zu)\n", cs, cap, pl.smem);
         if (cap < 1) continue;
         pl.n_clusters = B < cap ? B : cap;
         const long long rounds = ((long long)B + pl.n_clusters - 1) / pl.n_clusters;

@@ -15,6 +15,7 @@ from centerfusiondetect3d_b200 import _lib, ops, synthetic as syn
 
 wl = syn.WORKLOADS[sys.argv[1] if len(sys.argv) > 1 else "cfg2"]
 B = int(sys.argv[2]) if len(sys.argv) > 2 else min(wl.B, 32)
+CS = int(sys.argv[3]) if len(sys.argv) > 3 else 4
 dev = "cuda:0"
 host = bench.make_host_inputs(wl, B, seed=1234)
 keys = bench.STAGE_KEYS + ("calib", "pc_dep")
@@ -32,7 +33,7 @@ for rep in range(4):
     bench.run_stage(ops, wl, d, cfg)
     e1.record()
     torch.cuda.synchronize()
-    n_cta = 128
+    n_cta = min(B, 148 // CS) * CS
     buf = np.zeros((n_cta, 32), dtype=np.int64)
     L.cf_debug_read_prof(buf.ctypes.data, n_cta)
     dt = np.diff(buf[:, order], axis=1) / 1.965e3  # us at 1965 MHz
@@ -43,9 +44,9 @@ for rep in range(4):
     ex = buf[:, [0, 15, 1]], buf[:, [4, 12, 13, 14, 5]]
     mg = np.diff(buf[:, 16:19], axis=1) / 1.965e3
     tl = np.diff(buf[:, [8, 19, 20]], axis=1) / 1.965e3
-    for r in range(4):
-        print("   rank %d: select load %.2f  rank %.2f | tail gather %.2f  epilogue %.2f" % ((r,) + tuple(mg[r::4].mean(axis=0)) + tuple(tl[r::4].mean(axis=0))))
+    for r in range(min(CS, 4)):
+        print("   rank %d: select load %.2f  rank %.2f | tail gather %.2f  epilogue %.2f" % ((r,) + tuple(mg[r::CS].mean(axis=0)) + tuple(tl[r::CS].mean(axis=0))))
     print("   passB: loop %.2f  sync %.2f  atomics+sync %.2f  copy %.2f" % tuple((np.diff(ex[1], axis=1) / 1.965e3).mean(axis=0)))
     print("   passB loop per CTA (warp 0):", " ".join("%.0f" % x for x in (buf[:, 12] - buf[:, 4]) / 1.965e3))
-    for r in range(4):
-        print("   rank %d mean:" % r, " ".join("%6.2f" % x for x in dt[r::4].mean(axis=0)))
+    for r in range(min(CS, 4)):
+        print("   rank %d mean:" % r, " ".join("%6.2f" % x for x in dt[r::CS].mean(axis=0)))
