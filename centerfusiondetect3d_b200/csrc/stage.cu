@@ -18,15 +18,17 @@
 //   -- cluster barrier --
 //      tau      every CTA scans the distributed histogram top-down (ld.shared::cluster): tau = lower edge of the
 //               bin holding the K-th largest group maximum.
-//   B  filter   second look, from shared memory: pixels >= tau (and, nms'd list, surviving the 3x3 test) are staged
-//               per CTA and appended to the frame's survivor list (typically 1.1-3 x K entries).
+//   B  filter   second look, from shared memory: B1 scans (one vote per 512 pixels) and parks the candidate pixels in
+//               a CTA-wide work list; B2 tests them side by side, one per thread (threshold, 3x3 suppression) and
+//               appends the survivors to the frame's lists (typically 1.1-3 x K entries; one reservation per CTA).
 //   -- cluster barrier --
-//   C  merge    CTA 0: exact sorted top-K of the raw list + NCHW gathers + frustum geometry; CTA 1: the same for
-//               the nms'd list + the fusionDecode epilogue (merge.cuh).  Meanwhile every CTA stages the frame's
-//               radar depth plane pc_dep[b,0] in the shared memory the heat-map no longer needs (one bulk copy).
+//      select   the CTAs split the rank-by-counting of the two survivor lists; every ranked composite is delivered to
+//               every CTA (st.shared::cluster).  Meanwhile the frame's radar depth plane pc_dep[b,0] lands in the
+//               shared memory the heat-map no longer needs (one bulk copy).
 //   -- cluster barrier --
-//   D  assoc    one warp per detection over the whole cluster: ROI scan of the staged depth plane, warp-shuffle
-//               lexicographic (depth, pixel) minimum (assoc.cuh).
+//      tail     detection k belongs to CTA k % CS: head gathers, frustum geometry / decode epilogue (merge.cuh);
+//   D  assoc    one warp per detection: ROI scan of the staged depth plane, warp-shuffle lexicographic (depth, pixel)
+//               minimum (assoc.cuh); the K paint records are broadcast to every CTA.
 //   -- cluster barrier --
 //   E  paint    each CTA paints its band of rows of pc_hm: owner map in shared memory, every pixel written once.
 //
