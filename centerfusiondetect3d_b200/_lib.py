@@ -27,6 +27,16 @@ class DecodeOut(C.Structure):
                                    "nuscenes_att", "velocity", "inds")]
 
 
+class PostIn(C.Structure):
+    """cf_post_in_t"""
+    _fields_ = [(n, _vp) for n in ("class_ids", "centers", "bboxes", "depth", "rot", "dim", "amodal", "velocity")]
+
+
+class PostOut(C.Structure):
+    """cf_post_out_t"""
+    _fields_ = [(n, _vp) for n in ("centers", "bboxes", "alpha", "locations", "yaws", "bboxes3d")]
+
+
 # every symbol include/cfd3d_b200.h declares: name -> (restype, argtypes)
 _I, _F, _D, _Z, _L = C.c_int, C.c_float, C.c_double, C.c_size_t, C.c_int64
 SYMBOLS = {
@@ -47,6 +57,9 @@ SYMBOLS = {
                               _vp]),
     "cf_fusion_stage": (_I, [_vp] * 7 + [_I] * 5 + [_F] + [_vp] * 4 + [C.POINTER(DecodeHeads), _I, _I, _I,
                                                                        C.POINTER(DecodeOut), _vp, _Z, _vp]),
+    "cf_fusion_stage_strided": (_I, [_vp] * 7 + [_I] * 5 + [_F] + [_vp, _L] + [_vp] * 3 + [C.POINTER(DecodeHeads), _I, _I, _I,
+                                                                                        C.POINTER(DecodeOut), _vp, _Z, _vp]),
+    "cf_post_process": (_I, [C.POINTER(PostIn), _I, _I, _I, _I, C.POINTER(C.c_float), _vp, _I, C.POINTER(PostOut), _vp]),
     "cf_radar_pillars": (_I, [_vp, _vp, _I, _I, _vp, _vp, _vp, _I, _I, _I, _I, C.POINTER(_D), _D, _D, _vp, _vp, _vp,
                               _Z, _vp]),
 }

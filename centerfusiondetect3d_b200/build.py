@@ -15,7 +15,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcfd3d_b200.so")
-SOURCES = ["api.cu", "peak_ops.cu", "frustum.cu", "stage.cu"]
+SOURCES = ["api.cu", "peak_ops.cu", "frustum.cu", "stage.cu", "post.cu"]
 HEADERS = ["common.cuh", "select.cuh", "geometry.cuh", "kernels.cuh", "merge.cuh", "assoc.cuh", "paint.cuh", os.path.join("..", "..", "include", "cfd3d_b200.h")]
 
 NVCC_FLAGS = [

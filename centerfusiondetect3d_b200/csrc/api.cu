@@ -79,7 +79,7 @@ static int run_peak_passes(const float* heat, int B, int C, int H, int W, int K,
     if (raw_job) finish_job(raw_job);
     if (nms_job) finish_job(nms_job);
     CF_KERNEL(CF_KERNEL_STAGE, st,
-              launch_fusion_stage(heat, B, C, H, W, K, w, raw_job, nms_job, nullptr, 0.0f, nullptr, nullptr, st, n),
+              launch_fusion_stage(heat, B, C, H, W, K, w, raw_job, nms_job, nullptr, 0.0f, nullptr, 0, nullptr, st, n),
               "fusion_stage");
     return 0;
 }
@@ -242,6 +242,17 @@ int cf_fusion_stage(const float* heat, const float* wh, const float* depth, cons
                     float* pc_hm, int32_t* assoc, float* thr, int64_t* inds, const cf_decode_heads_t* dec_heads,
                     int out_h, int out_w, int norm2d, const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes,
                     void* stream) {
+    return cf_fusion_stage_strided(heat, wh, depth, dim, rot, pc_dep, calib, B, C, H, W, K, max_pc_dist, pc_hm,
+                                   3ll * H * W, assoc, thr, inds, dec_heads, out_h, out_w, norm2d, dec_out, ws, ws_bytes,
+                                   stream);
+}
+
+int cf_fusion_stage_strided(const float* heat, const float* wh, const float* depth, const float* dim, const float* rot,
+                            const float* pc_dep, const float* calib, int B, int C, int H, int W, int K,
+                            float max_pc_dist, float* pc_hm, int64_t pc_hm_batch_stride, int32_t* assoc, float* thr,
+                            int64_t* inds, const cf_decode_heads_t* dec_heads, int out_h, int out_w, int norm2d,
+                            const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes, void* stream) {
+    if (pc_hm_batch_stride < 3ll * H * W) return fail(CF_E_SHAPE, "cf_fusion_stage: pc_hm batch stride < 3*H*W");
     g_launches = 0;
     if (B == 0) return 0;
     if (int rc = check_frustum_args(heat, wh, depth, dim, rot, pc_dep, calib, pc_hm)) return rc;
@@ -277,8 +288,27 @@ int cf_fusion_stage(const float* heat, const float* wh, const float* depth, cons
     if (with_decode) finish_job(&dj);
     CF_KERNEL(CF_KERNEL_STAGE, st,
               launch_fusion_stage(heat, B, C, H, W, K, w, &fj, with_decode ? &dj : nullptr, pc_dep, max_pc_dist, pc_hm,
-                                  assoc, st, &n),
+                                  (long long)pc_hm_batch_stride, assoc, st, &n),
               "fusion_stage");
+    g_launches = n;
+    return 0;
+}
+
+int cf_post_process(const cf_post_in_t* in, int B, int K, int out_h, int out_w, const float* trans_host,
+                    const float* calib, int is_gt, const cf_post_out_t* out, void* stream) {
+    g_launches = 0;
+    if (!in || !out || !trans_host) return fail(CF_E_NULL, "cf_post_process: in/out/trans is NULL");
+    if (B < 0 || K < 0 || out_h < 1 || out_w < 1) return fail(CF_E_SHAPE, "cf_post_process: bad shape");
+    if (B == 0 || K == 0) return 0;
+    if (!in->class_ids || !in->centers || !out->centers) return fail(CF_E_NULL, "cf_post_process: class_ids/centers NULL");
+    const bool has3d = in->rot && in->depth && in->dim;
+    if ((in->bboxes && !out->bboxes) || (in->rot && !out->alpha) ||
+        (has3d && (!out->locations || !out->yaws || !out->bboxes3d || !calib)))
+        return fail(CF_E_NULL, "cf_post_process: an input is present but its output pointer is NULL");
+    int n = 0;
+    CF_KERNEL(CF_KERNEL_POST, (cudaStream_t)stream,
+              launch_post_process(*in, B, K, out_h, out_w, trans_host, calib, is_gt, *out, (cudaStream_t)stream, &n),
+              "post_process");
     g_launches = n;
     return 0;
 }

@@ -102,7 +102,11 @@ struct MergeParams {
 // job and pc_dep / pc_hm are given) in ONE launch, one thread-block cluster per frame
 cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, int K, const Workspace& ws,
                                 const MergeJob* raw_job, const MergeJob* nms_job, const float* pc_dep,
-                                float max_pc_dist, float* pc_hm, int32_t* assoc, cudaStream_t st, int* launches);
+                                float max_pc_dist, float* pc_hm, long long pc_hm_stride, int32_t* assoc, cudaStream_t st,
+                                int* launches);
+cudaError_t launch_post_process(const cf_post_in_t& in, int B, int K, int out_h, int out_w, const float* trans_host,
+                                const float* calib, int is_gt, const cf_post_out_t& out, cudaStream_t st,
+                                int* launches);
 int debug_read_prof(long long* out, int n_cta);
 cudaError_t launch_paint(const PaintRec* recs, int n_per_frame, int rec_stride, const int32_t* counts, int B, int H,
                          int W, float* out, int32_t* owner, cudaStream_t st, int* launches);

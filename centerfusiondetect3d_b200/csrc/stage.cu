@@ -137,6 +137,7 @@ struct StageParams {
     const float* pc_dep;
     float max_pc_dist;
     float* pc_hm;
+    long long pc_hm_stride;  // floats between the pc_hm of consecutive frames (3*H*W, or 67*H*W inside the combiner input)
     int32_t* assoc;
     PaintRec* recs;
 };
@@ -715,7 +716,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             const int y0 = (int)((long long)H * rank / cs), y1 = (int)((long long)H * (rank + 1) / cs);
             const size_t own_off = (size_t)p.off_own;
             const int max_rows = max(1, (int)(((size_t)p.slot_area - own_off) / ((size_t)W * sizeof(int))));
-            paint_band<ST, true>(srecs, K, H, W, y0, y1, p.pc_hm + (size_t)b * 3 * HW, nullptr,
+            paint_band<ST, true>(srecs, K, H, W, y0, y1, p.pc_hm + (size_t)b * (size_t)p.pc_hm_stride, nullptr,
                                  reinterpret_cast<int*>(smem + own_off), max_rows);
         }
         PROF(11);
@@ -852,7 +853,8 @@ static int max_clusters(const StagePlan& pl) {
 
 cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, int K, const Workspace& ws,
                                 const MergeJob* raw_job, const MergeJob* nms_job, const float* pc_dep,
-                                float max_pc_dist, float* pc_hm, int32_t* assoc, cudaStream_t st, int* launches) {
+                                float max_pc_dist, float* pc_hm, long long pc_hm_stride, int32_t* assoc, cudaStream_t st,
+                                int* launches) {
     const bool do_frustum = raw_job && raw_job->epilogue == EPI_FRUSTUM && pc_dep && pc_hm;
     const bool use_tma = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(heat) & 15u) == 0);
     const bool stage_dep = do_frustum && (((size_t)H * W) % 4 == 0) && ((reinterpret_cast<uintptr_t>(pc_dep) & 15u) == 0);
@@ -935,6 +937,7 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     p.pc_dep = pc_dep;
     p.max_pc_dist = max_pc_dist;
     p.pc_hm = pc_hm;
+    p.pc_hm_stride = pc_hm_stride > 0 ? pc_hm_stride : 3ll * H * W;
     p.assoc = assoc;
     p.recs = ws.recs;
     p.prof = getenv("CFD3D_PROF") ? 1 : 0;

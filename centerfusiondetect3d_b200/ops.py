@@ -17,15 +17,16 @@ from __future__ import annotations
 
 import ctypes as C
 
+import numpy as np
 import torch
 
 from . import _lib
-from ._lib import DecodeHeads, DecodeOut
+from ._lib import DecodeHeads, DecodeOut, PostIn, PostOut
 
 __all__ = [
     "nms", "topk", "getFeature", "transposeAndGetFeature", "get_alpha", "getDistanceThresh",
     "getPcFrustumHeatmap", "cvtPcDepthToHeatmap", "fusionDecode", "radar_to_pc_dep", "fusion_stage",
-    "frustum_association", "last_launch_count",
+    "frustum_association", "last_launch_count", "postProcess", "inverse_output_affine",
     "_nms", "_topk", "_gather_feat", "_tranpose_and_gather_feat", "generate_pc_hm", "get_pc_hm",
     "pc_dep_to_hm_torch", "fusion_decode", "get_dist_thresh",
 ]
@@ -325,12 +326,16 @@ def fusionDecode(outputs, outputSize=(112, 200), K=100, norm2d=False) -> dict:
 
 
 def fusion_stage(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config, outputSize=None, norm2d=False,
-                 decode_output: dict | None = None):
+                 decode_output: dict | None = None, sec_feats: torch.Tensor | None = None):
     """getPcFrustumHeatmap + fusionDecode with ONE pass over the heat-map (cf_fusion_stage).
 
     `output` holds the first-stage heads (heatmap, widthHeight, depth, dimension, rotation); `decode_output` the dict
     fusionDecode would receive (defaults to `output`, which then typically also carries reg, depth2, rotation2, ...).
-    Returns (pc_hm, ret) exactly as the two reference calls would."""
+    Returns (pc_hm, ret) exactly as the two reference calls would.
+
+    `sec_feats` (row f3): a pre-allocated contiguous (B, C_img + 3, H, W) fp32 buffer, the input of the secondary heads
+    (ConcateCombiner, fusionModules.py:18-35: cat([imgFeatures, pc_hm], 1)).  pc_hm is then painted straight into its
+    last three channels and the returned pc_hm is that view: no torch.cat copy of the image features."""
     K, max_pc_dist = _cfg_k_dist(config)
     heat = _map(_head(output, "heatmap"), "heatmap")
     B, Cc, H, W = heat.shape
@@ -351,14 +356,90 @@ def fusion_stage(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config
         dec["rotation"] = dec.pop("rotation2")
     if outputSize is None:
         outputSize = (H, W)
-    pc_hm = torch.empty_like(pcd)
+    if sec_feats is None:
+        pc_hm = torch.empty_like(pcd)
+        stride = 3 * H * W
+    else:
+        if not (sec_feats.is_cuda and sec_feats.dtype == torch.float32 and sec_feats.is_contiguous() and
+                sec_feats.dim() == 4 and sec_feats.shape[0] == B and sec_feats.shape[1] >= 3 and
+                tuple(sec_feats.shape[2:]) == (H, W)):
+            raise ValueError("sec_feats must be a contiguous fp32 CUDA tensor (B, C_img + 3, H, W)")
+        pc_hm = sec_feats[:, sec_feats.shape[1] - 3:]
+        stride = sec_feats.shape[1] * H * W
     ws, wsn = _stage_ws(heat.device, B, Cc, H, W, K)
-    _lib.check(_lib.lib().cf_fusion_stage(heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
-                                          rot.data_ptr(), pcd.data_ptr(), cal.data_ptr(), B, Cc, H, W, K,
-                                          max_pc_dist, pc_hm.data_ptr(), None, None, None, C.byref(heads),
-                                          int(outputSize[0]), int(outputSize[1]), int(bool(norm2d)), C.byref(out),
-                                          ws.data_ptr(), wsn, _stream(heat)))
+    _lib.check(_lib.lib().cf_fusion_stage_strided(heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
+                                                  rot.data_ptr(), pcd.data_ptr(), cal.data_ptr(), B, Cc, H, W, K,
+                                                  max_pc_dist, pc_hm.data_ptr(), stride, None, None, None,
+                                                  C.byref(heads), int(outputSize[0]), int(outputSize[1]),
+                                                  int(bool(norm2d)), C.byref(out), ws.data_ptr(), wsn, _stream(heat)))
     return pc_hm, ret
+
+
+# ------------------------------------------------------------------------------------------------------
+# f1  postProcess                                     src/lib/utils/postProcess.py:13-85
+# ------------------------------------------------------------------------------------------------------
+def inverse_output_affine(center, scale, width: int, height: int) -> np.ndarray:
+    """getAffineTransform(center, scale, 0, (width, height), inverse=True) (utils/image.py:43-83) as a 2x3 fp32
+    matrix: the map from output-map pixels back to image pixels.  With no rotation the three point pairs the
+    reference hands to cv2.getAffineTransform describe a pure scale + shift, solved here in float64 like cv2 does."""
+    c = np.asarray(center, dtype=np.float32).astype(np.float64)
+    sc = np.asarray(scale, dtype=np.float32).reshape(-1).astype(np.float64)
+    src_w = float(sc[0])
+    src = np.zeros((3, 2)); dst = np.zeros((3, 2))
+    src[0] = c
+    src[1] = c + np.array([0.0, src_w * -0.5])
+    dst[0] = [width * 0.5, height * 0.5]
+    dst[1] = dst[0] + np.array([0.0, width * -0.5])
+    for pts in (src, dst):  # get3rdPoint: b + (a - b) rotated by 90 degrees
+        d = pts[0] - pts[1]
+        pts[2] = pts[1] + np.array([-d[1], d[0]])
+    A = np.hstack([dst.astype(np.float32).astype(np.float64), np.ones((3, 1))])  # inverse: dst -> src
+    M = np.linalg.solve(A, src.astype(np.float32).astype(np.float64)).T
+    return np.ascontiguousarray(M, dtype=np.float32)
+
+
+def postProcess(y: dict, center, scale, height, width, calibs, isGt=False) -> dict:
+    """postProcess.py:13-85 -- drop-in for the calls at detector.py:341 and progressBar.py:104,196.  Mutates and
+    returns `y` like the reference: classIds and velocity are updated in place, rotation is replaced by alpha."""
+    scores = _map(y["scores"], "scores", ndim=2)
+    B, K = scores.shape
+    dev = scores.device
+    trans = inverse_output_affine(center, scale, int(width), int(height))
+    cls = y["classIds"]
+    if not (isinstance(cls, torch.Tensor) and cls.is_cuda and cls.dtype == torch.float32 and cls.is_contiguous()):
+        raise ValueError("classIds must be a contiguous fp32 CUDA tensor (updated in place)")
+    cen = _map(y["centers"], "centers", ndim=3)
+    opt = lambda k, nd: (_map(y[k], k, ndim=nd) if k in y else None)  # noqa: E731
+    bb, rot, dim, amo = opt("bboxes", 3), opt("rotation", 3), opt("dimension", 3), opt("amodal_offset", 3)
+    dep = _map(y["depth"], "depth", ndim=None).reshape(B, K) if "depth" in y else None
+    vel = y.get("velocity")
+    if vel is not None and not (vel.is_cuda and vel.dtype == torch.float32 and vel.is_contiguous()):
+        raise ValueError("velocity must be a contiguous fp32 CUDA tensor (updated in place)")
+    has3d = rot is not None and dep is not None and dim is not None
+    cal = _map(calibs, "calibs", ndim=None).reshape(-1, 3, 4) if has3d else None
+    if cal is not None and cal.shape[0] != B:
+        cal = cal.expand(B, 3, 4).contiguous()
+    new = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)  # noqa: E731
+    o_cen = new(B, K, 2)
+    o_bb = new(B, K, 4) if bb is not None else None
+    o_alpha = new(B, K) if rot is not None else None
+    o_loc, o_yaw, o_b3 = (new(B, K, 3), new(B, K), new(B, K, 8, 3)) if has3d else (None, None, None)
+    pin = PostIn(_ptr(cls), _ptr(cen), _ptr(bb), _ptr(dep), _ptr(rot), _ptr(dim), _ptr(amo), _ptr(vel))
+    pout = PostOut(_ptr(o_cen), _ptr(o_bb), _ptr(o_alpha), _ptr(o_loc), _ptr(o_yaw), _ptr(o_b3))
+    tarr = (C.c_float * 6)(*[float(v) for v in trans.reshape(-1)])
+    _lib.check(_lib.lib().cf_post_process(C.byref(pin), B, K, int(height), int(width), tarr, _ptr(cal),
+                                          int(bool(isGt)), C.byref(pout), _stream(scores)))
+    y["centers"] = o_cen
+    if bb is not None:
+        y["bboxes"] = o_bb
+    if dep is not None:
+        y["depth"] = dep
+    if rot is not None:
+        y.pop("rotation")
+        y["alpha"] = o_alpha
+    if has3d:
+        y["locations"], y["yaws"], y["bboxes3d"] = o_loc, o_yaw, o_b3
+    return y
 
 
 # ------------------------------------------------------------------------------------------------------

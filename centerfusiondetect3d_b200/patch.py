@@ -23,12 +23,13 @@ _TARGETS = {
     "utils.pointcloud": ("getPcFrustumHeatmap", "cvtPcDepthToHeatmap", "getDistanceThresh", "get_alpha"),
     "model.utils": ("nms", "topk", "getFeature", "transposeAndGetFeature"),
     "model.decode": ("fusionDecode",),
+    "utils.postProcess": ("postProcess",),
 }
 # modules that imported the names with `from ... import ...`
 _BY_NAME = ("model", "detector", "model.progressBar", "model.decode", "utils.pointcloud", "model.losses",
             "lib.detector", "lib.model", "lib.model.progressBar")
 _NAMES = ("nms", "topk", "getFeature", "transposeAndGetFeature", "fusionDecode", "getPcFrustumHeatmap",
-          "cvtPcDepthToHeatmap")
+          "cvtPcDepthToHeatmap", "postProcess")
 
 
 def apply(modules=None, torch_branch_only: bool = True):

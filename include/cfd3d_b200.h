@@ -130,6 +130,48 @@ CF_API int cf_fusion_stage(const float* heat, const float* wh, const float* dept
                            const cf_decode_heads_t* dec_heads, int out_h, int out_w, int norm2d,
                            const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- f3  the same, painting straight into the secondary heads' input -------------------------------------------
+ * ConcateCombiner.forward (src/lib/model/fusionModules.py:18-35) concatenates the 64-channel image features with the
+ * 3-channel pc_hm (torch.cat: a copy of the 64 channels).  With pc_hm = &sec_feats[0][64][0][0] and
+ * pc_hm_batch_stride = 67*H*W the stage writes channels 64..66 of a pre-allocated (B,67,H,W) buffer in place, so a
+ * backbone that emits its features into channels 0..63 of that buffer needs no concatenation at all.  The stride is
+ * in floats and must be >= 3*H*W; the three channel planes of a frame stay contiguous. */
+CF_API int cf_fusion_stage_strided(const float* heat, const float* wh, const float* depth, const float* dim,
+                                   const float* rot, const float* pc_dep, const float* calib, int B, int C, int H, int W,
+                                   int K, float max_pc_dist, float* pc_hm, int64_t pc_hm_batch_stride, int32_t* assoc,
+                                   float* thr, int64_t* inds, const cf_decode_heads_t* dec_heads, int out_h, int out_w,
+                                   int norm2d, const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- f1  postProcess(y, center, scale, height, width, calibs, isGt)   src/lib/utils/postProcess.py:13-85 ----
+ * Decoded detections (the cf_fusion_decode outputs) -> image-space boxes, camera-frame locations, yaw, velocity
+ * re-oriented along the box and the 8 corners of the 3-D box (utils/ddd.py:8-23, :122-199).  One detection per
+ * thread.  Inputs: NULL = key absent in the reference's dict.  class_ids and velocity are updated IN PLACE like the
+ * reference does; everything else goes to `out`.  trans_host: the 2x3 fp32 inverse output affine
+ * getAffineTransform(center, scale, 0, (width, height), inverse=True) (utils/image.py:43-83) on the HOST;
+ * calib (B,3,4) on the device. */
+typedef struct {
+    float* class_ids;      /* (B,K)   required, in/out: += 1 */
+    const float* centers;  /* (B,K,2) required: normalised [x/W, y/H] */
+    const float* bboxes;   /* (B,K,4) or NULL */
+    const float* depth;    /* (B,K)   or NULL */
+    const float* rot;      /* (B,K,8) or NULL */
+    const float* dim;      /* (B,K,3) or NULL */
+    const float* amodal;   /* (B,K,2) or NULL */
+    float* velocity;       /* (B,K,3) or NULL, in/out */
+} cf_post_in_t;
+
+typedef struct {
+    float* centers;   /* (B,K,2)   required */
+    float* bboxes;    /* (B,K,4)   iff in.bboxes */
+    float* alpha;     /* (B,K)     iff in.rot */
+    float* locations; /* (B,K,3)   iff in.rot && in.depth && in.dim */
+    float* yaws;      /* (B,K)     same */
+    float* bboxes3d;  /* (B,K,8,3) same */
+} cf_post_out_t;
+
+CF_API int cf_post_process(const cf_post_in_t* in, int B, int K, int out_h, int out_w, const float* trans_host,
+                           const float* calib, int is_gt, const cf_post_out_t* out, void* stream);
+
 /* ---- a5 + a6  radar pillar expansion -> pc_dep -----------------------------------------------------------
  * loadRadarPointCloud filters      src/lib/dataset/datasets/nuscenes.py:172-205
  * map_pointcloud_to_image          src/lib/utils/pointcloud.py:17-49
@@ -159,6 +201,7 @@ enum {
     CF_KERNEL_PAINT = 3,       /* ordered pc_hm / pc_dep paint */
     CF_KERNEL_PILLAR_RECTS = 4, /* radar point -> pillar rectangle */
     CF_KERNEL_PEAK_FILTER = 5,  /* filter pass: re-read (L2) + survivors >= tau */
+    CF_KERNEL_POST = 7,         /* postProcess */
     CF_KERNEL_STAGE = 6         /* the fused stage kernel: one cluster per frame, all of the above in one launch */
 };
 CF_API int cf_set_kernel_events(int kernel_id, void* ev_start, void* ev_stop);

@@ -204,3 +204,36 @@ def radar_pillars(points, counts, cam, calib, A, img_wh, out_hw, pillar_dims=(1.
                             C.c_double(float(max_dist)), C.c_double(float(z_offset)), _p(pc_dep, _f32p),
                             _p(owner, _i32p))
     return pc_dep, owner
+
+
+def post_process(y: dict, trans, out_hw, calib, is_gt=False):
+    """postProcess (utils/postProcess.py:13-85) on NumPy copies of a decode dict; returns a new dict with the
+    reference's keys.  `trans` = the 2x3 fp32 inverse output affine (getAffineTransform(..., inverse=True))."""
+    B, K = y["scores"].shape
+    opt = lambda k: (_f32(y[k]).copy() if k in y else None)  # noqa: E731
+    cls, cen = _f32(y["classIds"]).copy(), _f32(y["centers"])
+    bb, dep, rot, dim, amo, vel = (opt(k) for k in ("bboxes", "depth", "rotation", "dimension", "amodal_offset", "velocity"))
+    has3d = rot is not None and dep is not None and dim is not None
+    o_cen = np.empty((B, K, 2), np.float32)
+    o_bb = np.empty((B, K, 4), np.float32) if bb is not None else None
+    o_alpha = np.empty((B, K), np.float32) if rot is not None else None
+    o_loc = np.empty((B, K, 3), np.float32) if has3d else None
+    o_yaw = np.empty((B, K), np.float32) if has3d else None
+    o_b3 = np.empty((B, K, 8, 3), np.float32) if has3d else None
+    pp = lambda a: (_p(a, _f32p) if a is not None else None)  # noqa: E731
+    lib().cfo_post_process(pp(cls), pp(cen), pp(bb), pp(dep), pp(rot), pp(dim), pp(amo), pp(vel), B, K,
+                           int(out_hw[0]), int(out_hw[1]), pp(_f32(trans)), pp(_f32(calib).reshape(-1, 3, 4)),
+                           int(bool(is_gt)), pp(o_cen), pp(o_bb), pp(o_alpha), pp(o_loc), pp(o_yaw), pp(o_b3))
+    out = {k: v for k, v in y.items() if k != "rotation"}
+    out["classIds"], out["centers"] = cls, o_cen
+    if bb is not None:
+        out["bboxes"] = o_bb
+    if dep is not None:
+        out["depth"] = dep.reshape(B, K)
+    if rot is not None:
+        out["alpha"] = o_alpha
+    if vel is not None:
+        out["velocity"] = vel
+    if has3d:
+        out["locations"], out["yaws"], out["bboxes3d"] = o_loc, o_yaw, o_b3
+    return out

@@ -533,3 +533,106 @@ CFO_API void cfo_radar_pillars(const double* points, const int32_t* counts, int 
         }
     }
 }
+
+/* ------------------------------------------------------------------------------------------
+ * f1  postProcess               utils/postProcess.py:13-85
+ *     affineTransform           utils/image.py:86-109   (2x3 fp32 matrix, points (x, y, 1))
+ *     cvtImgToCamCoord          utils/ddd.py:176-199 with project2DTo3D :146-172, alpha2rot_y :122-142
+ *     get3dBox / get3DCorners   utils/ddd.py:8-23, utils/pointcloud.py:239-296
+ * One detection per iteration; any input pointer except class_ids / centers may be NULL (= key absent in
+ * the reference's dict).  class_ids and velocity are updated in place like the reference does.
+ * Arithmetic: fp32, one rounding per written operation, sums left to right (the reference's torch.mm /
+ * einsum leave the order to the BLAS: parity with the reference is a tolerance, SURVEY.md "Hard parts").
+ * ------------------------------------------------------------------------------------------ */
+static inline void affine_pt(const float* t, float x, float y, float* ox, float* oy) {
+    float a = t[0] * x, b = t[1] * y;
+    float s = a + b;
+    *ox = s + t[2];
+    a = t[3] * x;
+    b = t[4] * y;
+    s = a + b;
+    *oy = s + t[5];
+}
+
+CFO_API void cfo_post_process(float* class_ids, const float* centers_in, const float* bboxes_in, const float* depth,
+                              const float* rot, const float* dim, const float* amodal, float* velocity, int B, int K,
+                              int out_h, int out_w, const float* trans /*2x3*/, const float* calib /*B,3,4*/, int is_gt,
+                              float* centers, float* bboxes, float* alpha_out, float* locations, float* yaws,
+                              float* bboxes3d) {
+    const int has3d = rot && depth && dim;
+    for (long i = 0; i < (long)B * K; ++i) {
+        const float* cal = calib + 12 * (i / K);
+        class_ids[i] += 1.0f;                                            /* :34 */
+        float cx = centers_in[2 * i] * (float)out_w, cy = centers_in[2 * i + 1] * (float)out_h; /* :35-37 */
+        float bb[4] = {0, 0, 0, 0};
+        if (bboxes_in) {                                                 /* :39-42 */
+            affine_pt(trans, bboxes_in[4 * i], bboxes_in[4 * i + 1], &bb[0], &bb[1]);
+            affine_pt(trans, bboxes_in[4 * i + 2], bboxes_in[4 * i + 3], &bb[2], &bb[3]);
+            for (int j = 0; j < 4; ++j) bboxes[4 * i + j] = bb[j];
+        }
+        float alpha = 0.0f;
+        if (rot) {                                                       /* :47-48 */
+            alpha = cfo_get_alpha(rot + 8 * i);
+            alpha_out[i] = alpha;
+        }
+        if (has3d) {
+            if (!is_gt && amodal) {                                      /* :54-59 */
+                float ax = cx + amodal[2 * i], ay = cy + amodal[2 * i + 1];
+                affine_pt(trans, ax, ay, &cx, &cy);
+            } else if (!is_gt && bboxes_in) {                            /* :62-64 */
+                float sx = bb[0] + bb[2], sy = bb[1] + bb[3];
+                cx = sx / 2.0f;
+                cy = sy / 2.0f;
+            }
+            /* project2DTo3D, ddd.py:160-166 */
+            const float d = depth[i];
+            float z = d - cal[11];
+            float x = cx * d;
+            x = x - cal[3];
+            float t = cal[2] * z;
+            x = x - t;
+            x = x / cal[0];
+            float y = cy * d;
+            y = y - cal[7];
+            t = cal[6] * z;
+            y = y - t;
+            y = y / cal[5];
+            float hh = dim[3 * i] / 2.0f;                                /* ddd.py:197 */
+            y = y + hh;
+            float yaw = alpha + f32_atan2(cx - cal[2], cal[0]);          /* ddd.py:137-141 */
+            if (yaw > PI_F) yaw -= 2.0f * PI_F;
+            if (yaw < -PI_F) yaw += 2.0f * PI_F;
+            locations[3 * i] = x;
+            locations[3 * i + 1] = y;
+            locations[3 * i + 2] = z;
+            yaws[i] = yaw;
+            const float c = (float)cos((double)yaw), s = (float)sin((double)yaw);
+            if (!is_gt && velocity) {                                    /* :71-76 */
+                float v0 = velocity[3 * i], v2 = velocity[3 * i + 2];
+                float q0 = v0 * v0, q2 = v2 * v2;
+                float V = sqrtf(q0 + q2);
+                velocity[3 * i] = c * V;
+                velocity[3 * i + 2] = (-s) * V;
+            }
+            /* get3DCorners + location, zeroed when any dimension <= 0  (:78-81) */
+            const float h = dim[3 * i], w = dim[3 * i + 1], l = dim[3 * i + 2];
+            const int dead = h <= 0.0f || w <= 0.0f || l <= 0.0f;
+            for (int k = 0; k < 8; ++k) {
+                float xc = ((k & 2) ? -0.5f : 0.5f) * l;
+                float yc = (k & 4) ? h * -1.0f : 0.0f;
+                float zc = (((k + 1) & 2) ? -0.5f : 0.5f) * w;
+                float a = c * xc, b2 = s * zc;
+                float X = a + b2;
+                a = (-s) * xc;
+                b2 = c * zc;
+                float Z = a + b2;
+                float* o = bboxes3d + (24 * i + 3 * k);
+                o[0] = dead ? 0.0f : X + x;
+                o[1] = dead ? 0.0f : yc + y;
+                o[2] = dead ? 0.0f : Z + z;
+            }
+        }
+        centers[2 * i] = cx;
+        centers[2 * i + 1] = cy;
+    }
+}

@@ -180,9 +180,37 @@ def gen_frustum_and_decode():
     save("frustum_decode", **arrs)
 
 
+def gen_post_process():
+    """postProcess (utils/postProcess.py:13-85) on the decode outputs stored in frustum_decode.npz: every branch of
+    the centre choice (amodal offset / 2-D box centre / isGt) and a detection with a non-positive dimension."""
+    g = np.load(os.path.join(HERE, "frustum_decode.npz"))
+    H, W = g["in_heatmap"].shape[2:]
+    center, scale = np.array([800.0, 450.0], dtype=np.float32), 1600.0
+    calib = g["in_calib"]
+    arrs = dict(in_center=center, in_scale=np.float32(scale), in_H=np.int64(H), in_W=np.int64(W), in_calib=calib,
+                in_trans=ns.getAffineTransform(center, scale, 0, (W, H), inverse=True).astype(np.float32))
+    variants = {"amodal": ("full", (), False), "bboxcenter": ("full", ("amodal_offset",), False),
+                "gt": ("full", (), True), "no3d": ("full", ("rotation", "velocity"), False)}
+    for vname, (dec, drop, is_gt) in variants.items():
+        y = {k[len("out_dec_%s_" % dec):]: g[k].copy() for k in g.files if k.startswith("out_dec_%s_" % dec)}
+        for k in drop:
+            y.pop(k)
+        if "dimension" in y:
+            y["dimension"][0, 3, 1] = -0.25  # any(dim <= 0) -> the 3-D box is zeroed
+            y["dimension"][1, 5, 0] = 0.0
+        for k, v in y.items():
+            arrs["in_%s_%s" % (vname, k)] = v.copy()
+        arrs["in_%s_isgt" % vname] = np.bool_(is_gt)
+        out = ns.postProcess({k: t(v).clone() for k, v in y.items()}, center, scale, H, W, t(calib), isGt=is_gt)
+        for k, v in out.items():
+            arrs["out_%s_%s" % (vname, k)] = v.numpy()
+    save("post_process", **arrs)
+
+
 if __name__ == "__main__":
     gen_topk_nms()
     gen_alpha_thr()
     gen_pillars()
     gen_pc2hm_quirks()
     gen_frustum_and_decode()
+    gen_post_process()

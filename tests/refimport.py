@@ -170,13 +170,14 @@ def load_reference():
     ddd = _load("utils.ddd", "utils/ddd.py")
     gd = _load("dataset.generic_dataset", "dataset/generic_dataset.py")
     nus = _load("dataset.datasets.nuscenes", "dataset/datasets/nuscenes.py")
+    pp = _load("utils.postProcess", "utils/postProcess.py")
     ns = types.SimpleNamespace(
         model_utils=mu, pointcloud=pc, decode=dec, image=img, ddd=ddd, generic_dataset=gd, nuscenes=nus,
         nms=mu.nms, topk=mu.topk, transposeAndGetFeature=mu.transposeAndGetFeature,
         getPcFrustumHeatmap=pc.getPcFrustumHeatmap, cvtPcDepthToHeatmap=pc.cvtPcDepthToHeatmap,
         getDistanceThresh=pc.getDistanceThresh, get_alpha=pc.get_alpha,
         map_pointcloud_to_image=pc.map_pointcloud_to_image, fusionDecode=dec.fusionDecode,
-        getAffineTransform=img.getAffineTransform,
+        getAffineTransform=img.getAffineTransform, postProcess=pp.postProcess,
     )
     _loaded["ns"] = ns
     return ns

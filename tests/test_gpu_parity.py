@@ -196,6 +196,62 @@ def test_oracle_stage_forced_plans(ops, oracle, monkeypatch, cfg_name, B, cs):
     _check_stage(ops, oracle, wl, inp, B)
 
 
+def test_paint_into_combiner_input(ops, oracle):
+    """f3: pc_hm painted straight into channels 64..66 of the (B,67,H,W) secondary-head input equals the stand-alone
+    pc_hm, and the 64 image-feature channels are left untouched (ConcateCombiner, fusionModules.py:18-35)."""
+    wl = syn.WORKLOADS["cfg2"]
+    B = 5
+    inp = make_case(wl, B)
+    cfg = type("Cfg", (), {"MODEL": type("M", (), {"K": wl.K})(), "DATASET": type("D", (), {"MAX_PC_DIST": wl.max_pc_dist})()})()
+    pc_hm, ret = ops.fusion_stage(to_cuda(inp, DEC_KEYS, DEV), cu(inp["pc_dep"]), cu(inp["calib"]), cfg)
+    sec = torch.full((B, 67, wl.H, wl.W), 7.0, dtype=torch.float32, device=DEV)
+    pc_hm2, ret2 = ops.fusion_stage(to_cuda(inp, DEC_KEYS, DEV), cu(inp["pc_dep"]), cu(inp["calib"]), cfg, sec_feats=sec)
+    assert pc_hm2.data_ptr() == sec[:, 64:].data_ptr()
+    eq(npy(sec[:, 64:]), npy(pc_hm), "pc_hm inside the combiner input")
+    assert bool((sec[:, :64] == 7.0).all())
+    for k in ret:
+        eq(npy(ret2[k]), npy(ret[k]), k)
+    hm_o = oracle.frustum_pc_hm(inp["heatmap"], inp["widthHeight"], inp["depth"], inp["dimension"], inp["rotation"],
+                                inp["pc_dep"], inp["calib"], wl.K, wl.max_pc_dist)[0]
+    eq(npy(sec[:, 64:]), hm_o, "pc_hm vs oracle")
+
+
+def test_post_process(ops, oracle):
+    """f1 postProcess: the kernel against the oracle (bit-exact apart from the fp64-rounded trigonometry, 1e-6) and
+    against the reference's own outputs (golden fixture, 1e-5 relative: north_star's bar for decoded boxes)."""
+    from test_oracle_golden import POST_VARIANTS, post_case
+    g = load_golden("post_process")
+    H, W = int(g["in_H"]), int(g["in_W"])
+    trans = ops.inverse_output_affine(g["in_center"], float(g["in_scale"]), W, H)
+    eq(trans, g["in_trans"], "inverse output affine")
+    for v in POST_VARIANTS:
+        y, is_gt, ref = post_case(g, v)
+        out_o = oracle.post_process(y, g["in_trans"], (H, W), g["in_calib"], is_gt)
+        yd = {k: cu(a) for k, a in y.items()}
+        cls_t, vel_t = yd["classIds"], yd.get("velocity")
+        out = ops.postProcess(yd, g["in_center"], float(g["in_scale"]), H, W, cu(g["in_calib"]), isGt=is_gt)
+        assert out is yd and out["classIds"] is cls_t and (vel_t is None or out["velocity"] is vel_t)  # in place
+        assert set(out) == set(ref), (v, set(out) ^ set(ref))
+        for k, r in ref.items():
+            a = npy(out[k])
+            assert a.shape == r.shape and a.dtype == r.dtype, (v, k, a.shape, r.shape)
+            np.testing.assert_allclose(a, r, rtol=1e-5, atol=1e-5, err_msg="vs reference %s %s" % (v, k))
+            if k in ("alpha", "yaws", "velocity", "bboxes3d", "locations"):
+                np.testing.assert_allclose(a, out_o[k], rtol=1e-6, atol=1e-6, err_msg="vs oracle %s %s" % (v, k))
+            else:
+                eq(a, out_o[k], "vs oracle %s %s" % (v, k))
+    # full-size property: B=32, K=100 through fusionDecode -> postProcess; boxes of dead dimensions are zero,
+    # everything finite, yaw wrapped into [-pi, pi]
+    wl = syn.WORKLOADS["cfg2"]
+    inp = make_case(wl, 4)
+    ret = ops.fusionDecode([to_cuda(inp, DEC_KEYS, DEV)], (wl.H, wl.W), wl.K)
+    out = ops.postProcess(ret, (800.0, 450.0), 1600.0, wl.H, wl.W, cu(inp["calib"]))
+    assert out["bboxes3d"].shape == (4, wl.K, 8, 3) and bool(torch.isfinite(out["bboxes3d"]).all())
+    assert float(out["yaws"].abs().max()) <= np.pi + 1e-6
+    dead = (out["dimension"] <= 0).any(dim=2)
+    assert not bool(out["bboxes3d"][dead].any())
+
+
 def test_oracle_dense_radar_with_pillars(ops, oracle):
     """cfg4: 2000 points/frame, pillar expansion on the GPU feeding the association."""
     wl = syn.WORKLOADS["cfg4"]

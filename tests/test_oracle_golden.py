@@ -108,3 +108,30 @@ def test_fusion_decode_variants(oracle):
                 np.testing.assert_allclose(ret[k], refv, rtol=1e-6)  # expf differs by an ulp
             else:
                 assert np.array_equal(ret[k].view(np.uint32), refv.view(np.uint32)), (vname, k)
+
+
+POST_VARIANTS = ("amodal", "bboxcenter", "gt", "no3d")
+
+
+def post_case(g, v):
+    y = {k[len("in_%s_" % v):]: g[k] for k in g if k.startswith("in_%s_" % v) and not k.endswith("_isgt")}
+    ref = {k[len("out_%s_" % v):]: g[k] for k in g if k.startswith("out_%s_" % v)}
+    return y, bool(g["in_%s_isgt" % v]), ref
+
+
+def test_post_process_variants(oracle):
+    """f1: postProcess (utils/postProcess.py:13-85) against outputs of the reference itself.  Tolerance, not bits: the
+    reference leaves the summation order of its 2x3 / 3x3 products to the BLAS and uses SLEEF fp32 trigonometry;
+    1e-5 relative is the bar north_star states for decoded boxes (observed: 1.2e-6)."""
+    g = load_golden("post_process")
+    H, W = int(g["in_H"]), int(g["in_W"])
+    for v in POST_VARIANTS:
+        y, is_gt, ref = post_case(g, v)
+        out = oracle.post_process(y, g["in_trans"], (H, W), g["in_calib"], is_gt)
+        assert set(out) == set(ref), (v, set(out) ^ set(ref))
+        for k, r in ref.items():
+            assert out[k].shape == r.shape and out[k].dtype == r.dtype, (v, k)
+            np.testing.assert_allclose(out[k], r, rtol=1e-5, atol=1e-5, err_msg="%s %s" % (v, k))
+    # a detection with a non-positive dimension has its 3-D box zeroed (postProcess.py:81)
+    _, _, ref = post_case(g, "amodal")
+    assert not ref["bboxes3d"][0, 3].any() and not ref["bboxes3d"][1, 5].any()
