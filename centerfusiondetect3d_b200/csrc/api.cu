@@ -294,6 +294,39 @@ int cf_fusion_stage_strided(const float* heat, const float* wh, const float* dep
     return 0;
 }
 
+int cf_radar_sort(const double* points, const int32_t* counts, int B, int Nmax, double* sorted, int32_t* order,
+                  void* stream) {
+    g_launches = 0;
+    if (!counts || !sorted || (Nmax > 0 && !points)) return fail(CF_E_NULL, "cf_radar_sort: NULL pointer");
+    if (B < 0 || Nmax < 0 || Nmax > 25600) return fail(CF_E_SHAPE, "cf_radar_sort: bad shape (Nmax <= 25600)");
+    if (points == sorted) return fail(CF_E_NULL, "cf_radar_sort: sorted must not alias points");
+    int n = 0;
+    CF_CUDA(launch_radar_sort(points, counts, B, Nmax, sorted, order, (cudaStream_t)stream, &n), "radar_sort");
+    g_launches = n;
+    return 0;
+}
+
+int cf_frustum_boxes(const float* pc_dep, const float* bboxes, const float* depth, const float* thr,
+                     const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, float* pc_hm, int32_t* assoc,
+                     void* ws, size_t ws_bytes, void* stream) {
+    g_launches = 0;
+    if (!pc_dep || !pc_hm || (N > 0 && (!bboxes || !depth || !thr))) return fail(CF_E_NULL, "cf_frustum_boxes: NULL pointer");
+    if (B < 0 || N < 0 || H < 1 || W < 1 || H > 32767 || W > 32767) return fail(CF_E_SHAPE, "cf_frustum_boxes: bad shape");
+    const size_t need = (size_t)B * N * sizeof(PaintRec);
+    if (need) {
+        if (int rc = check_ws(ws, ws_bytes, need)) return rc;
+    }
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    int n = 0;
+    CF_KERNEL(CF_KERNEL_ASSOC, st,
+              launch_box_assoc(pc_dep, bboxes, depth, thr, counts, B, N, H, W, max_pc_dist, (PaintRec*)ws, assoc, st, &n),
+              "box_assoc");
+    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint((const PaintRec*)ws, N, N, counts, B, H, W, pc_hm, nullptr, st, &n), "paint");
+    g_launches = n;
+    return 0;
+}
+
 int cf_post_process(const cf_post_in_t* in, int B, int K, int out_h, int out_w, const float* trans_host,
                     const float* calib, int is_gt, const cf_post_out_t* out, void* stream) {
     g_launches = 0;

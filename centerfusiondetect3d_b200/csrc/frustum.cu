@@ -57,6 +57,51 @@ cudaError_t launch_paint(const PaintRec* recs, int n_per_frame, int rec_stride, 
 }
 
 // -----------------------------------------------------------------------------------------------------
+// f4: frustum association of GIVEN boxes (training targets): the per-annotation loop of
+// dataset/generic_dataset.py:673-687, cvtPcDepthToHeatmap per box in list order.  One warp per box, then the
+// ordered paint (later boxes overwrite earlier ones, like the reference's sequential slice writes).
+// -----------------------------------------------------------------------------------------------------
+constexpr int BW = 8;  // warps (boxes) per CTA
+
+__global__ void __launch_bounds__(BW * 32) box_assoc_kernel(const float* __restrict__ pc_dep, const float* __restrict__ bboxes,
+                                                            const float* __restrict__ depth, const float* __restrict__ thr,
+                                                            const int32_t* __restrict__ counts, int N, int H, int W,
+                                                            float max_pc_dist, PaintRec* __restrict__ recs,
+                                                            int32_t* __restrict__ assoc) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n = blockIdx.x * BW + warp, b = blockIdx.y;
+    if (n >= N) return;
+    const size_t o = (size_t)b * N + n;
+    const float* dep = pc_dep + (size_t)b * 3 * H * W;
+    unsigned long long best = ~0ull;
+    DetParam d;
+    d.x1 = d.y1 = d.x2 = d.y2 = d.depth = d.thr = 0.0f;
+    d.ind = d.pad_ = 0;
+    const bool live = !counts || n < counts[b];
+    if (live) {
+        d.x1 = __ldg(bboxes + 4 * o);
+        d.y1 = __ldg(bboxes + 4 * o + 1);
+        d.x2 = __ldg(bboxes + 4 * o + 2);
+        d.y2 = __ldg(bboxes + 4 * o + 3);
+        d.depth = __ldg(depth + o);
+        d.thr = __ldg(thr + o);
+        best = warp_min_u64(roi_scan<16>(dep, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32));
+    }
+    if (lane == 0) recs[o] = assoc_finalize(best, dep, H, W, d, max_pc_dist, assoc ? assoc + o : nullptr);
+}
+
+cudaError_t launch_box_assoc(const float* pc_dep, const float* bboxes, const float* depth, const float* thr,
+                             const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, PaintRec* recs,
+                             int32_t* assoc, cudaStream_t st, int* launches) {
+    if (B == 0 || N == 0) return cudaSuccess;
+    box_assoc_kernel<<<dim3((N + BW - 1) / BW, B), BW * 32, 0, st>>>(pc_dep, bboxes, depth, thr, counts, N, H, W,
+                                                                      max_pc_dist, recs, assoc);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) ++*launches;
+    return e;
+}
+
+// -----------------------------------------------------------------------------------------------------
 // cvtPcDepthToHeatmap, one detection, in place                      reference pointcloud.py:397-481
 // -----------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) pc2hm_single_kernel(float* __restrict__ pc_hm, const float* __restrict__ pc_dep,
@@ -142,6 +187,59 @@ cudaError_t launch_dist_thresh(const float* calib, const float* center, const fl
                                int K, float* thr, cudaStream_t st, int* launches) {
     if (B * K == 0) return cudaSuccess;
     dist_thresh_kernel<<<(B * K + 127) / 128, 128, 0, st>>>(calib, center, dim, alpha, B, K, thr);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) ++*launches;
+    return e;
+}
+
+// -----------------------------------------------------------------------------------------------------
+// f2: stable depth sort of a frame's radar points on the device (ascending Z, ties by source index).
+// The reference sorts on the host with np.argsort (dataset/datasets/nuscenes.py:195-197, detector.py:281), whose
+// default kind is not stable; the pillar paint is last-writer-wins, so the order is part of the result.  Here the
+// order is fixed: (Z, source index) ascending == np.argsort(kind="stable").  One CTA per frame, rank by counting
+// with the depths in shared memory (N <= a few thousand points).
+// -----------------------------------------------------------------------------------------------------
+constexpr int RS_T = 1024;
+
+__global__ void __launch_bounds__(RS_T) radar_sort_kernel(const double* __restrict__ points, const int32_t* __restrict__ counts,
+                                                          int Nmax, double* __restrict__ out, int32_t* __restrict__ order) {
+    extern __shared__ double sz[];
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int n = min(Nmax, max(0, counts[b]));
+    const double* fp = points + (size_t)b * Nmax * 5;
+    double* fo = out + (size_t)b * Nmax * 5;
+    for (int i = tid; i < n; i += RS_T) sz[i] = fp[(size_t)i * 5 + 2];
+    __syncthreads();
+    for (int i = tid; i < Nmax; i += RS_T) {
+        int rank = i;  // padding rows keep their place
+        if (i < n) {
+            const double zi = sz[i];
+            int r0 = 0, r1 = 0;
+            int j = 0;
+            for (; j + 2 <= n; j += 2) {
+                const double a = sz[j], c = sz[j + 1];
+                r0 += (a < zi || (a == zi && j < i)) ? 1 : 0;
+                r1 += (c < zi || (c == zi && j + 1 < i)) ? 1 : 0;
+            }
+            if (j < n) r0 += (sz[j] < zi || (sz[j] == zi && j < i)) ? 1 : 0;
+            rank = r0 + r1;
+        }
+#pragma unroll
+        for (int c = 0; c < 5; ++c) fo[(size_t)rank * 5 + c] = fp[(size_t)i * 5 + c];
+        if (order) order[(size_t)b * Nmax + rank] = i;
+    }
+}
+
+cudaError_t launch_radar_sort(const double* points, const int32_t* counts, int B, int Nmax, double* out, int32_t* order,
+                              cudaStream_t st, int* launches) {
+    if (B == 0 || Nmax == 0) return cudaSuccess;
+    const size_t smem = (size_t)Nmax * sizeof(double);
+    if (smem > 200 * 1024) return cudaErrorInvalidValue;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(radar_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    radar_sort_kernel<<<B, RS_T, smem, st>>>(points, counts, Nmax, out, order);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) ++*launches;
     return e;

@@ -107,6 +107,11 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
 cudaError_t launch_post_process(const cf_post_in_t& in, int B, int K, int out_h, int out_w, const float* trans_host,
                                 const float* calib, int is_gt, const cf_post_out_t& out, cudaStream_t st,
                                 int* launches);
+cudaError_t launch_box_assoc(const float* pc_dep, const float* bboxes, const float* depth, const float* thr,
+                             const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, PaintRec* recs,
+                             int32_t* assoc, cudaStream_t st, int* launches);
+cudaError_t launch_radar_sort(const double* points, const int32_t* counts, int B, int Nmax, double* out, int32_t* order,
+                              cudaStream_t st, int* launches);
 int debug_read_prof(long long* out, int n_cta);
 cudaError_t launch_paint(const PaintRec* recs, int n_per_frame, int rec_stride, const int32_t* counts, int B, int H,
                          int W, float* out, int32_t* owner, cudaStream_t st, int* launches);

@@ -26,7 +26,7 @@ from ._lib import DecodeHeads, DecodeOut, PostIn, PostOut
 __all__ = [
     "nms", "topk", "getFeature", "transposeAndGetFeature", "get_alpha", "getDistanceThresh",
     "getPcFrustumHeatmap", "cvtPcDepthToHeatmap", "fusionDecode", "radar_to_pc_dep", "fusion_stage",
-    "frustum_association", "last_launch_count", "postProcess", "inverse_output_affine",
+    "frustum_association", "last_launch_count", "postProcess", "inverse_output_affine", "frustum_targets", "radar_sort",
     "_nms", "_topk", "_gather_feat", "_tranpose_and_gather_feat", "generate_pc_hm", "get_pc_hm",
     "pc_dep_to_hm_torch", "fusion_decode", "get_dist_thresh",
 ]
@@ -254,6 +254,30 @@ def cvtPcDepthToHeatmap(pc_hm, pc_dep, depth, bbox, distanceThreshold, max_pc_di
                                                  t.data_ptr(), float(max_pc_dist), None, _stream(hm)))
 
 
+def frustum_targets(pc_dep: torch.Tensor, bboxes: torch.Tensor, depth: torch.Tensor, distanceThreshold: torch.Tensor,
+                    counts: torch.Tensor | None = None, max_pc_dist: float = 60.0, return_assoc: bool = False):
+    """Row f4 -- the training-target form of the frustum association (dataset/generic_dataset.py:673-687): for every
+    frame, cvtPcDepthToHeatmap of annotation 0, 1, ... in list order on a zero pc_hm.  pc_dep (B,3,H,W); bboxes (B,N,4)
+    in output-map pixels; depth, distanceThreshold (B,N); counts (B) int32 annotations per frame (None = N).
+    Returns pc_hm (B,3,H,W) [, assoc (B,N) int32]."""
+    pcd = _map(pc_dep, "pc_dep")
+    B, _, H, W = pcd.shape
+    bb = _map(bboxes, "bboxes", ndim=3)
+    N = bb.shape[1]
+    if bb.shape != (B, N, 4):
+        raise ValueError("bboxes must be (B,N,4)")
+    dp = _map(depth, "depth", ndim=None).reshape(B, N)
+    th = _map(distanceThreshold, "distanceThreshold", ndim=None).reshape(B, N)
+    cn = _map(counts, "counts", ndim=1, dtype=torch.int32) if counts is not None else None
+    pc_hm = torch.empty_like(pcd)
+    assoc = torch.empty((B, N), dtype=torch.int32, device=pcd.device) if return_assoc else None
+    ws = _workspace(pcd.device, B * N * 32 + 256)
+    _lib.check(_lib.lib().cf_frustum_boxes(pcd.data_ptr(), bb.data_ptr(), dp.data_ptr(), th.data_ptr(), _ptr(cn), B, N, H, W,
+                                           float(max_pc_dist), pc_hm.data_ptr(), _ptr(assoc), ws.data_ptr(), ws.numel(),
+                                           _stream(pcd)))
+    return (pc_hm, assoc) if return_assoc else pc_hm
+
+
 # ------------------------------------------------------------------------------------------------------
 # a9  fusionDecode                                                          src/lib/model/decode.py:10-174
 # ------------------------------------------------------------------------------------------------------
@@ -445,16 +469,32 @@ def postProcess(y: dict, center, scale, height, width, calibs, isGt=False) -> di
 # ------------------------------------------------------------------------------------------------------
 # a5 + a6  radar pillar expansion -> pc_dep          src/lib/dataset/generic_dataset.py:738-942 (processPointCloud)
 # ------------------------------------------------------------------------------------------------------
+def radar_sort(points: torch.Tensor, counts: torch.Tensor, return_order: bool = False):
+    """Row f2 -- stable ascending depth sort of every frame's first counts[b] points on the device
+    (== points[b][np.argsort(points[b,:n,2], kind="stable")]; nuscenes.py:195-197 / detector.py:281 sort on the host)."""
+    pts = _map(points, "points", ndim=3, dtype=torch.float64)
+    B, Nmax, _ = pts.shape
+    cnt = _map(counts, "counts", ndim=1, dtype=torch.int32)
+    out = torch.empty_like(pts)
+    order = torch.empty((B, Nmax), dtype=torch.int32, device=pts.device) if return_order else None
+    _lib.check(_lib.lib().cf_radar_sort(_ptr(pts) if Nmax else None, cnt.data_ptr(), B, Nmax, out.data_ptr(), _ptr(order),
+                                        _stream(pts)))
+    return (out, order) if return_order else out
+
+
 def radar_to_pc_dep(points: torch.Tensor, counts: torch.Tensor, cam: torch.Tensor, calib: torch.Tensor,
                     A_out: torch.Tensor, out_hw, img_wh=(1600, 900), pillar_dims=(1.5, 0.2, 0.2), max_dist=60.0,
-                    z_offset=0.0, return_owner=False):
-    """points (B,Nmax,5) f64 [X,Y,Z,vx,vz] camera frame, each frame sorted ascending by Z; counts (B,) i32;
+                    z_offset=0.0, return_owner=False, sort_points=False):
+    """points (B,Nmax,5) f64 [X,Y,Z,vx,vz] camera frame, each frame sorted ascending by Z (or sort_points=True: sorted
+    on the device first, row f2; owner indices then refer to the SORTED order); counts (B,) i32;
     cam (B,3,3) f64; calib (B,3,4) f64; A_out (B,2,3) f64 -> pc_dep (B,3,H,W) f32 [, owner (B,H,W) i32]."""
     pts = _map(points, "points", ndim=3, dtype=torch.float64)
     B, Nmax, five = pts.shape
     if five != 5:
         raise ValueError("points must be (B,Nmax,5) [X,Y,Z,vx,vz]")
     cnt = _map(counts, "counts", ndim=1, dtype=torch.int32)
+    if sort_points and Nmax:
+        pts = radar_sort(pts, cnt)
     cam = _map(cam, "cam", ndim=None, dtype=torch.float64).view(B, 3, 3)
     cal = _map(calib, "calib", ndim=None, dtype=torch.float64).view(B, 3, 4)
     A = _map(A_out, "A_out", ndim=None, dtype=torch.float64).view(B, 2, 3)

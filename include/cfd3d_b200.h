@@ -142,6 +142,25 @@ CF_API int cf_fusion_stage_strided(const float* heat, const float* wh, const flo
                                    float* thr, int64_t* inds, const cf_decode_heads_t* dec_heads, int out_h, int out_w,
                                    int norm2d, const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- f2  stable depth sort of the radar points on the device --------------------------------------------------
+ * The host-side np.argsort(depth) of src/lib/dataset/datasets/nuscenes.py:195-197 / src/lib/detector.py:281 (default
+ * kind: not stable, so the reference's order among equal depths is unspecified) with the order fixed to
+ * (Z ascending, source index ascending) == np.argsort(kind="stable").  points (B,Nmax,5) fp64 as in cf_radar_pillars,
+ * counts (B) i32; sorted (B,Nmax,5) fp64 must not alias points; rows beyond counts[b] are copied in place.
+ * order (B,Nmax) i32 optional: source index of every sorted row.  Nmax <= 25600. */
+CF_API int cf_radar_sort(const double* points, const int32_t* counts, int B, int Nmax, double* sorted, int32_t* order,
+                         void* stream);
+
+/* ---- f4  frustum association of given boxes (training targets) ---------------------------------------------------
+ * The per-annotation loop of src/lib/dataset/generic_dataset.py:673-687: cvtPcDepthToHeatmap
+ * (src/lib/utils/pointcloud.py:397-481) for box 0, 1, ... of every frame in list order, later boxes overwriting earlier
+ * ones.  bboxes (B,N,4) [x1,y1,x2,y2] in output-map pixels, depth (B,N), thr (B,N) distance thresholds
+ * (cf_dist_thresh), counts (B) i32 boxes per frame or NULL (= N).  Writes pc_hm (B,3,H,W) completely; assoc (B,N) i32
+ * optional (flat matched pixel or -1).  Workspace: B*N*32 bytes, 256-byte aligned. */
+CF_API int cf_frustum_boxes(const float* pc_dep, const float* bboxes, const float* depth, const float* thr,
+                            const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, float* pc_hm,
+                            int32_t* assoc, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- f1  postProcess(y, center, scale, height, width, calibs, isGt)   src/lib/utils/postProcess.py:13-85 ----
  * Decoded detections (the cf_fusion_decode outputs) -> image-space boxes, camera-frame locations, yaw, velocity
  * re-oriented along the box and the 8 corners of the 3-D box (utils/ddd.py:8-23, :122-199).  One detection per

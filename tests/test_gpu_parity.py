@@ -216,6 +216,65 @@ def test_paint_into_combiner_input(ops, oracle):
     eq(npy(sec[:, 64:]), hm_o, "pc_hm vs oracle")
 
 
+def test_radar_sort_on_device(ops, oracle):
+    """f2: the device sort is np.argsort(kind="stable") on depth (ties keep source order, padding rows stay), and the
+    pillar expansion of device-sorted points equals the one of host-sorted points."""
+    wl = syn.WORKLOADS["cfg4"]
+    B = 3
+    inp = make_case(wl, B)
+    pts, cnt = inp["radar_points"].copy(), inp["radar_counts"].copy()
+    rng = np.random.default_rng(3)
+    shuf = pts.copy()
+    for b in range(B):
+        n = int(cnt[b])
+        shuf[b, :n] = pts[b, rng.permutation(n)]
+        shuf[b, 5:25, 2] = shuf[b, 4, 2]  # a run of equal depths: ties must keep their source order
+    cnt[1] = max(0, cnt[1] - 17)  # ragged
+    want = shuf.copy()
+    order_w = np.tile(np.arange(shuf.shape[1], dtype=np.int32), (B, 1))
+    for b in range(B):
+        n = int(cnt[b])
+        o = np.argsort(shuf[b, :n, 2], kind="stable")
+        want[b, :n] = shuf[b, :n][o]
+        order_w[b, :n] = o
+    got, order = ops.radar_sort(cu(shuf), cu(cnt), return_order=True)
+    eq(npy(got), want, "sorted points")
+    eq(npy(order), order_w, "order")
+    args = (cu(inp["cam"]), cu(inp["calib64"]), cu(inp["A_out"]), (wl.H, wl.W), (wl.img_w, wl.img_h), wl.pillar_dims,
+            wl.max_pc_dist)
+    a = ops.radar_to_pc_dep(cu(want), cu(cnt), *args)
+    b_ = ops.radar_to_pc_dep(cu(shuf), cu(cnt), *args, sort_points=True)
+    eq(npy(a), npy(b_), "pc_dep of device-sorted points")
+    pc_o, _ = oracle.radar_pillars(want, cnt, inp["cam"], inp["calib64"], inp["A_out"], (wl.img_w, wl.img_h), (wl.H, wl.W),
+                                   wl.pillar_dims, wl.max_pc_dist, want_owner=False)
+    eq(npy(b_), pc_o, "pc_dep vs oracle")
+
+
+def test_frustum_targets(ops, oracle):
+    """f4: association of given (ground-truth style) boxes in list order == the oracle's cvtPcDepthToHeatmap loop
+    (pinned on the reference by the quirk fixtures), ragged counts included."""
+    wl = syn.WORKLOADS["cfg2"]
+    B, N = 3, 37
+    inp = make_case(wl, B)
+    rng = np.random.default_rng(7)
+    cx, cy = rng.uniform(-5, wl.W + 5, (B, N)), rng.uniform(-5, wl.H + 5, (B, N))
+    w, h = rng.uniform(0, 60, (B, N)), rng.uniform(0, 40, (B, N))
+    bb = np.stack([cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2], -1).astype(np.float32)
+    depth = rng.uniform(1, 70, (B, N)).astype(np.float32)
+    thr = rng.uniform(0.3, 6.0, (B, N)).astype(np.float32)
+    counts = np.array([N, 0, 11], dtype=np.int32)
+    hm_o = np.zeros_like(inp["pc_dep"])
+    assoc_o = np.full((B, N), -1, np.int32)
+    for b in range(B):
+        for n in range(counts[b]):
+            assoc_o[b, n] = oracle.pc_dep_to_hm(hm_o[b], inp["pc_dep"][b], depth[b, n], bb[b, n], thr[b, n], wl.max_pc_dist)
+    hm, assoc = ops.frustum_targets(cu(inp["pc_dep"]), cu(bb), cu(depth), cu(thr), cu(counts), wl.max_pc_dist,
+                                    return_assoc=True)
+    eq(npy(assoc), assoc_o, "assoc")
+    eq(npy(hm), hm_o, "pc_hm")
+    assert (assoc_o >= 0).sum() >= 5
+
+
 def test_post_process(ops, oracle):
     """f1 postProcess: the kernel against the oracle (bit-exact apart from the fp64-rounded trigonometry, 1e-6) and
     against the reference's own outputs (golden fixture, 1e-5 relative: north_star's bar for decoded boxes)."""
