@@ -26,29 +26,44 @@ __device__ __forceinline__ void paint_band(const PaintRec* __restrict__ fr, int 
         const int npx = (ye - ys) * W;
         for (int i = tid; i < npx; i += T) sown[i] = -1;
         __syncthreads();
-        for (int base = warp * 32; base < n; base += T) {
-            const int k = base + lane;
-            int ra = 0, rb = 0, ca = 0, cb = 0;
-            if (k < n) {
-                const short4 q = SHARED ? *reinterpret_cast<const short4*>(fr + k)
-                                        : __ldg(reinterpret_cast<const short4*>(fr + k));
-                ra = q.x;
-                rb = q.y;
-                ca = q.z;
-                cb = q.w;
-            }
-            const bool hit = rb > ra && cb > ca && ra < ye && rb > ys;
-            uint32_t m = __ballot_sync(FULL, hit);
-            while (m) {
-                const int bit = __ffs(m) - 1;
-                m &= m - 1;
-                const int qa = max(__shfl_sync(FULL, ra, bit), ys), qb = min(__shfl_sync(FULL, rb, bit), ye);
-                const int xa = __shfl_sync(FULL, ca, bit), xb = __shfl_sync(FULL, cb, bit);
-                const int w = xb - xa;
+        if (SHARED) {
+            // records in shared memory: record k on warp k % (T/32), so that all warps paint (a broadcast read each)
+            for (int k = warp; k < n; k += T / 32) {
+                const short4 q = *reinterpret_cast<const short4*>(fr + k);
+                if (!(q.y > q.x && q.w > q.z && q.x < ye && q.y > ys)) continue;
+                const int qa = max((int)q.x, ys), qb = min((int)q.y, ye);
+                const int xa = q.z, w = q.w - q.z;
                 const int cnt = (qb - qa) * w;
                 for (int t = lane; t < cnt; t += 32) {
                     const int ry = t / w;
-                    atomicMax(&sown[(qa - ys + ry) * W + xa + (t - ry * w)], base + bit);
+                    atomicMax(&sown[(qa - ys + ry) * W + xa + (t - ry * w)], k);
+                }
+            }
+        } else {
+            // records in global memory: 32 coalesced loads per warp, then the hits one after the other
+            for (int base = warp * 32; base < n; base += T) {
+                const int k = base + lane;
+                int ra = 0, rb = 0, ca = 0, cb = 0;
+                if (k < n) {
+                    const short4 q = __ldg(reinterpret_cast<const short4*>(fr + k));
+                    ra = q.x;
+                    rb = q.y;
+                    ca = q.z;
+                    cb = q.w;
+                }
+                const bool hit = rb > ra && cb > ca && ra < ye && rb > ys;
+                uint32_t m = __ballot_sync(FULL, hit);
+                while (m) {
+                    const int bit = __ffs(m) - 1;
+                    m &= m - 1;
+                    const int qa = max(__shfl_sync(FULL, ra, bit), ys), qb = min(__shfl_sync(FULL, rb, bit), ye);
+                    const int xa = __shfl_sync(FULL, ca, bit), xb = __shfl_sync(FULL, cb, bit);
+                    const int w = xb - xa;
+                    const int cnt = (qb - qa) * w;
+                    for (int t = lane; t < cnt; t += 32) {
+                        const int ry = t / w;
+                        atomicMax(&sown[(qa - ys + ry) * W + xa + (t - ry * w)], base + bit);
+                    }
                 }
             }
         }

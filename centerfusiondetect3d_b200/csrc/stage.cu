@@ -691,7 +691,9 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                                    : roi_scan<24>(dep0, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32));
                 if (lane == 0) sbest[kl] = best;
             }
+            PROF(25);
             __syncthreads();
+            PROF(26);
             // paint records: the velocity reads of all matches go out together; every CTA of the cluster gets a copy
             // of every record in its shared memory (st.shared::cluster), in detection order
             for (int kl = tid; kl < n_local; kl += ST) {
