@@ -124,23 +124,80 @@ __device__ __forceinline__ void merge_select_part(const MergeParams& p, MergeSme
         nw = K;
     }
     CF_MERGE_PROF(1);
-    // rank by counting; four independent partial counts per thread keep the shared-memory broadcasts in flight.
-    // The parts split the list by position (the list is the same in every CTA); after select_overflow the order of
-    // win[] differs from CTA to CTA, so there the parts split by pixel identity instead.
-    for (int t = listed ? tid * parts + part : tid; t < nw; t += listed ? T * parts : T) {
-        const unsigned long long me = sm.win[t];
-        if (!listed && (int)(comp_gidx(me) % (uint32_t)parts) != part) continue;
-        int r0 = 0, r1 = 0, r2 = 0, r3 = 0;
-        int jx = 0;
-        for (; jx + 4 <= nw; jx += 4) {
-            r0 += (sm.win[jx] > me) ? 1 : 0;
-            r1 += (sm.win[jx + 1] > me) ? 1 : 0;
-            r2 += (sm.win[jx + 2] > me) ? 1 : 0;
-            r3 += (sm.win[jx + 3] > me) ? 1 : 0;
+    // Rank = number of larger composites.  Counting over the whole list costs n^2 compares (microseconds at n ~ 500),
+    // so the list is first bucketed by key (256 linear buckets over [min key, max key], a counting sort in shared
+    // memory): rank = entries of the higher buckets + larger entries of the own bucket.  Every CTA of the job builds
+    // the same buckets; the CTAs split the final counting by pixel identity (the order inside win[] / a bucket may
+    // differ from CTA to CTA, the ranks cannot: composites are pairwise distinct).
+    static_assert(MERGE_WIN <= 2 * T && MERGE_WIN <= SEL_CAP / 2, "two entries per thread; sorted[] and start[] share surv[]");
+    unsigned long long* sorted = sm.sc.surv;
+    uint32_t* start = reinterpret_cast<uint32_t*>(sm.sc.surv + MERGE_WIN);
+    const int lane = tid & 31;
+    if (tid < 256) sm.sc.hist[tid] = 0u;
+    if (tid == 0) {
+        sm.sc.L = 0xffffffffu;
+        sm.sc.kmax = 0u;
+    }
+    unsigned long long me[2];
+    uint32_t kmn = 0xffffffffu, kmx = 0u;
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const int t = tid + u * T;
+        me[u] = t < nw ? sm.win[t] : 0ull;
+        if (t < nw) {
+            kmn = min(kmn, comp_key(me[u]));
+            kmx = max(kmx, comp_key(me[u]));
         }
-        for (; jx < nw; ++jx) r0 += (sm.win[jx] > me) ? 1 : 0;
-        const int rank = (r0 + r1) + (r2 + r3);
-        if (rank < K) emit(rank, me);
+    }
+    kmn = __reduce_min_sync(FULL, kmn);
+    kmx = __reduce_max_sync(FULL, kmx);
+    __syncthreads();
+    if (lane == 0 && kmn <= kmx) {
+        atomicMin(&sm.sc.L, kmn);
+        atomicMax(&sm.sc.kmax, kmx);
+    }
+    __syncthreads();
+    const uint32_t kmin = sm.sc.L, range = sm.sc.kmax - kmin;
+    const int shift = range < 256u ? 0 : 24 - __clz(range);  // (range >> shift) < 256
+    uint32_t bk[2], pos[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        bk[u] = (comp_key(me[u]) - kmin) >> shift;
+        if (tid + u * T < nw) pos[u] = atomicAdd(&sm.sc.hist[bk[u]], 1u);
+    }
+    __syncthreads();
+    if (tid < 32) {  // start[b] = entries of the buckets above b
+        uint32_t h[8], sum = 0u;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            h[j] = sm.sc.hist[lane * 8 + j];
+            sum += h[j];
+        }
+        uint32_t suf = sum;  // inclusive suffix sum over lanes >= lane
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t o = __shfl_down_sync(FULL, suf, off);
+            if (lane + off < 32) suf += o;
+        }
+        uint32_t acc = suf - sum;
+#pragma unroll
+        for (int j = 7; j >= 0; --j) {
+            start[lane * 8 + j] = acc;
+            acc += h[j];
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+        if (tid + u * T < nw) sorted[start[bk[u]] + pos[u]] = me[u];
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        if (tid + u * T >= nw || (int)(comp_gidx(me[u]) % (uint32_t)parts) != part) continue;
+        const int s0 = (int)start[bk[u]], s1 = s0 + (int)sm.sc.hist[bk[u]];
+        int rank = s0;
+        for (int jx = s0; jx < s1; ++jx) rank += (sorted[jx] > me[u]) ? 1 : 0;
+        if (rank < K) emit(rank, me[u]);
     }
     __syncthreads();  // win[] is reused by the next job of this CTA
     CF_MERGE_PROF(2);
@@ -148,12 +205,13 @@ __device__ __forceinline__ void merge_select_part(const MergeParams& p, MergeSme
 
 // detections kl0 .. kl0+nb of this CTA (detection k = first + kl * stride): head values of job N-channel table gt into
 // gath[(kl - kl0) * GATH_STRIDE + slot].  comps = the job's sorted composites xs_comp[job].
-template <int T, int N>
+// Executed by the thread group [0, T) given as (tid, T).
+template <int N>
 __device__ __forceinline__ void gather_local(const GatherTab& gt, int b, size_t HW, const unsigned long long* comps,
-                                             int first, int stride, int kl0, int nb, float* gath) {
+                                             int first, int stride, int kl0, int nb, float* gath, int tid, int T) {
     const int total = nb * N;
     constexpr int U = 4;
-    for (int t0 = threadIdx.x; t0 < total; t0 += T * U) {
+    for (int t0 = tid; t0 < total; t0 += T * U) {
         float v[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -318,20 +376,21 @@ __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int
     const int K = p.K, HWi = p.H * p.W;
     for (int kl0 = 0; kl0 < n_local; kl0 += GB) {
         const int nb = min(GB, n_local - kl0);
-        for (int li = 0; li < n_jobs; ++li) {
-            const MergeJob& jb = p.job[li];
-            float* g = gath + (size_t)li * GB * GATH_STRIDE;
-            if (jb.epilogue == EPI_FRUSTUM)
-                gather_local<T, FS_N>(jb.gt, b, (size_t)HWi, xs_comp + li * K, first, stride, kl0, nb, g);
-            else if (jb.epilogue == EPI_DECODE)
-                gather_local<T, DS_N>(jb.gt, b, (size_t)HWi, xs_comp + li * K, first, stride, kl0, nb, g);
-        }
-        __syncthreads();
-        CF_MERGE_PROF(3);
-        // the epilogues of the two jobs run side by side, each on its own half of the CTA's warps
+        // the two jobs run side by side, each on its own half of the CTA's warps: first the gathers (one round of
+        // scattered loads in flight for both jobs at once), then the epilogues
         const int half = n_jobs == 2 ? T / 2 : T;
         const int li = n_jobs == 2 ? (int)threadIdx.x / half : 0;
         const int gt = (int)threadIdx.x - li * half;
+        {
+            const MergeJob& jb = p.job[li];
+            float* g = gath + (size_t)li * GB * GATH_STRIDE;
+            if (jb.epilogue == EPI_FRUSTUM)
+                gather_local<FS_N>(jb.gt, b, (size_t)HWi, xs_comp + li * K, first, stride, kl0, nb, g, gt, half);
+            else if (jb.epilogue == EPI_DECODE)
+                gather_local<DS_N>(jb.gt, b, (size_t)HWi, xs_comp + li * K, first, stride, kl0, nb, g, gt, half);
+        }
+        __syncthreads();
+        CF_MERGE_PROF(3);
         {
             const MergeJob& jb = p.job[li];
             const unsigned long long* comps = xs_comp + li * K;

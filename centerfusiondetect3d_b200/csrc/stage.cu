@@ -55,9 +55,10 @@ namespace cf {
 constexpr int ST = 512;          // threads per CTA
 constexpr int SNW = ST / 32;     // warps
 constexpr int WL_CAP = 640;      // pass-B work list: candidate pixels a CTA parks before it tests them side by side
+constexpr int FL_CAP = 256;      // pass-B flagged-group list (resident shares)
 constexpr int MAX_SLOTS = 64;
 constexpr int MAX_CS = 16;
-constexpr size_t SMEM_DYN_CAP = 227 * 1024 - 1536;  // leaves room for the kernel's static shared memory
+constexpr size_t SMEM_DYN_CAP = 227 * 1024 - 1792;  // leaves room for the kernel's static shared memory
 
 // ---- cluster primitives ------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t cl_rank() {
@@ -240,6 +241,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     __shared__ uint32_t s_tops[2][MAX_CS];
     __shared__ uint32_t s_mytop[2];
     __shared__ uint32_t s_nwl;  // entries of the pass-B work list
+    __shared__ uint32_t s_nfl;  // pass B, resident shares: flagged groups (a group = the 1/32 of a chunk one lane took in pass A)
+    __shared__ uint16_t s_fl[FL_CAP];
     __shared__ uint32_t s_cnt[2], s_base[2];  // pass B2: survivors of this CTA per list, their base in the frame's list
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -332,7 +335,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         for (int i = tid; i < p.hist_words; i += ST) hist[i] = 0u;
         if (tid < 2 * MAX_CS) (&s_tops[0][0])[tid] = 0u;
         if (tid < 2) s_mytop[tid] = 0u;
-        if (tid == 0) s_nwl = 0u;
+        if (tid == 0) s_nwl = s_nfl = 0u;
         fence_async_smem();  // the previous frame's merge scratch / owner map were generic writes to the slot area
         __syncthreads();
         // "this CTA runs and its histogram part is clear": arrive now, wait right before the first remote reduction
@@ -351,6 +354,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         PROF(1);
 
         // ---- pass A: group maxima -> distributed histogram ------------------------------------------------------
+        float gmax[4] = {-CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F, -CUDART_INF_F};  // this lane's groups (resident: n <= 64)
         {
             const float inv_w4 = 1.0f / (float)W4;
             uint32_t tkraw = 0u, tknms = 0u;
@@ -429,6 +433,13 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 if (want_nms) hist_add_cluster(hist_saddr, list_words, 1, knms, p.cs_log2);
                 tkraw = max(tkraw, kraw);
                 tknms = max(tknms, knms);
+                {
+                    const int ci = q / SNW;
+                    if (ci == 0) gmax[0] = best;
+                    else if (ci == 1) gmax[1] = best;
+                    else if (ci == 2) gmax[2] = best;
+                    else if (ci == 3) gmax[3] = best;
+                }
                 // a chunk that will not stay resident frees its slot: this warp starts the copy that reuses it
                 if (use_tma && q < n - n_res) {
                     __syncwarp();
@@ -515,9 +526,103 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 sraw = want_raw && v >= tau_raw;
                 snms = want_nms && v >= tau_nms && !(nb > v);
             };
-            // Visits: resident -> ONE visit, the whole share as one contiguous tile, 128-item blocks interleaved over
-            // the warps; ring / manual -> one visit per chunk per warp.
-            const int n_vis = resident ? 1 : n;
+            // park this lane's candidates (bit j of mask: pixel j of float4 item_of(bit)) in the work list from `slot` on;
+            // lanes that hold several park one per round, so that a blob's pixels are written side by side
+            uint16_t* wl16 = reinterpret_cast<uint16_t*>(wl);
+            const uint32_t wl_cap = resident ? 2u * WL_CAP : (uint32_t)WL_CAP;
+            auto park = [&](uint32_t mask, uint32_t slot, int q, auto&& item_of) {
+                for (;;) {
+                    const bool mine = mask != 0u;
+                    const uint32_t bal = __ballot_sync(FULL, mine);
+                    if (!bal) break;
+                    const uint32_t my = slot + (uint32_t)__popc(bal & lanemask_lt());
+                    slot += (uint32_t)__popc(bal);
+                    if (!mine) continue;
+                    const int bit = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    const uint32_t code = ((uint32_t)q << 16) | (uint32_t)(item_of(bit) * 4 + (bit & 3));
+                    if (my < wl_cap) {
+                        if (resident) wl16[my] = (uint16_t)code;  // q == 0: the pixel index alone, and it fits 16 bits
+                        else wl[my] = code;
+                    } else {  // work list full (dense survivors): test and append right here, lane by lane
+                        float v;
+                        uint32_t gi;
+                        bool sraw, snms;
+                        cand_eval(code, v, gi, sraw, snms);
+                        if (sraw) {
+                            const uint32_t gs = atomicAdd(ctr_raw, 1u);
+                            if (gs < (uint32_t)CAND_CAP) cand_raw[gs] = make_comp(f2key(v), gi);
+                        }
+                        if (snms) {
+                            const uint32_t gs = atomicAdd(ctr_nms, 1u);
+                            if (gs < (uint32_t)CAND_CAP) cand_nms[gs] = make_comp(f2key(v), gi);
+                        }
+                    }
+                }
+            };
+            // Resident share, fast path: pass A left every lane the maximum of each of its groups, so the groups that
+            // hold a candidate are known without touching the share again.  They go to a CTA-wide list, and half-warps
+            // rescan just those (a group = 1/32 of a chunk), whichever warp found them.
+            bool scanned = false;
+            if (resident) {
+                // (every chunk's copy was awaited by the warp that took the chunk in pass A; the CTA barrier below
+                // orders those observations before the reads of all the other warps)
+                PROF(30);
+#pragma unroll
+                for (int ci = 0; ci < 4; ++ci) {
+                    const int q = warp + ci * SNW;
+                    const bool flag = q < n && gmax[ci] >= tau_min;
+                    const uint32_t bal = __ballot_sync(FULL, flag);
+                    if (bal) {
+                        uint32_t base = 0u;
+                        if (lane == 0) base = atomicAdd(&s_nfl, (uint32_t)__popc(bal));
+                        base = __shfl_sync(FULL, base, 0) + (uint32_t)__popc(bal & lanemask_lt());
+                        if (flag && base < (uint32_t)FL_CAP) s_fl[base] = (uint16_t)((q << 5) | lane);
+                    }
+                }
+                PROF(31);
+                __syncthreads();
+                const int nfl = (int)s_nfl;
+                PROF(29);
+                scanned = nfl <= FL_CAP;  // else (dense frame): the block scan below
+                if (scanned) {
+                    // every half-warp takes up to FL_CAP/32 groups; a lane collects the candidate bits of all of them in
+                    // one register first (loads back to back), so that the reservation and the parking happen once
+                    const int hw = tid >> 4, hl = tid & 15;
+                    const int chunk_items = R * W4, t_max = (chunk_items + 31) >> 5;
+                    const float4* c4p = reinterpret_cast<const float4*>(slots);
+                    for (int t0 = 0; t0 < t_max; t0 += 16) {
+                        uint32_t mask = 0u;
+#pragma unroll
+                        for (int u = 0; u < FL_CAP / 32; ++u) {
+                            const int f = u * 32 + hw;
+                            if (f < nfl) {
+                                const int code = (int)s_fl[f];
+                                const int q = code >> 5, i = (code & 31) + 32 * (t0 + hl);
+                                if (i < min(R, row_end - (row_begin + q * R)) * W4) {
+                                    const float4 v = c4p[q * chunk_items + i];  // the slots of a resident share are contiguous
+                                    const uint32_t m4 = (v.x >= tau_min ? 1u : 0u) | (v.y >= tau_min ? 2u : 0u) |
+                                                        (v.z >= tau_min ? 4u : 0u) | (v.w >= tau_min ? 8u : 0u);
+                                    mask |= m4 << (4 * u);
+                                }
+                            }
+                        }
+                        PROF(21);
+                        const uint32_t total = __reduce_add_sync(FULL, (uint32_t)__popc(mask));
+                        if (!total) continue;
+                        uint32_t slot = 0u;
+                        if (lane == 0) slot = atomicAdd(&s_nwl, total);
+                        slot = __shfl_sync(FULL, slot, 0);
+                        park(mask, slot, 0, [&](int bit) {
+                            const int code = (int)s_fl[(bit >> 2) * 32 + hw];
+                            return (code >> 5) * chunk_items + (code & 31) + 32 * (t0 + hl);
+                        });
+                    }
+                }
+            }
+            // Block scan.  Visits: resident -> ONE visit, the whole share as one contiguous tile, 128-item blocks
+            // interleaved over the warps; ring / manual -> one visit per chunk per warp.
+            const int n_vis = scanned ? 0 : (resident ? 1 : n);
             for (int vb = resident ? 0 : warp; vb < n_vis; vb += SNW) {
                 int L = 0, q = 0, nr = row_end - row_begin;
                 const float* tile = slots;
@@ -566,34 +671,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     uint32_t slot = 0u;
                     if (lane == 0) slot = atomicAdd(&s_nwl, total);
                     slot = __shfl_sync(FULL, slot, 0);
-                    for (;;) {  // every lane that still holds candidates parks one per round (typically 1-2 rounds)
-                        const bool mine = mask != 0u;
-                        const uint32_t bal = __ballot_sync(FULL, mine);
-                        if (!bal) break;
-                        const uint32_t my = slot + (uint32_t)__popc(bal & lanemask_lt());
-                        slot += (uint32_t)__popc(bal);
-                        if (!mine) continue;
-                        const int bit = __ffs(mask) - 1;
-                        mask &= mask - 1;
-                        const uint32_t code = ((uint32_t)q << 16) |
-                                              (uint32_t)((item0 + (bit >> 2) * 32 + lane) * 4 + (bit & 3));
-                        if (my < (uint32_t)WL_CAP) {
-                            wl[my] = code;
-                        } else {  // work list full (dense survivors): test and append right here, lane by lane
-                            float v;
-                            uint32_t gi;
-                            bool sraw, snms;
-                            cand_eval(code, v, gi, sraw, snms);
-                            if (sraw) {
-                                const uint32_t gs = atomicAdd(ctr_raw, 1u);
-                                if (gs < (uint32_t)CAND_CAP) cand_raw[gs] = make_comp(f2key(v), gi);
-                            }
-                            if (snms) {
-                                const uint32_t gs = atomicAdd(ctr_nms, 1u);
-                                if (gs < (uint32_t)CAND_CAP) cand_nms[gs] = make_comp(f2key(v), gi);
-                            }
-                        }
-                    }
+                    park(mask, slot, q, [&](int bit) { return item0 + (bit >> 2) * 32 + lane; });
                 }
                 // this visit was the last use of the slot's contents: start the re-fetch that reuses it, if any
                 if (use_tma && !resident) {
@@ -606,7 +684,11 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             PROF(13);
             // B2: one candidate per thread.  Survivors are counted per CTA (shared-memory atomics), the frame's lists
             // see ONE reservation per (CTA, list): same-address global atomics serialise at a few per microsecond.
-            const uint32_t n_wl = min(s_nwl, (uint32_t)WL_CAP);
+            const uint32_t n_wl = min(s_nwl, wl_cap);
+            if (p.prof && tid == 0 && blockIdx.x < 1024) {
+                g_prof[blockIdx.x * PROF_PTS + 27] = (long long)s_nfl;
+                g_prof[blockIdx.x * PROF_PTS + 28] = (long long)s_nwl;
+            }
             for (uint32_t c0 = 0; c0 < n_wl; c0 += ST) {
                 const uint32_t c = c0 + (uint32_t)tid;
                 float v = 0.0f;
@@ -614,7 +696,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 bool sraw = false, snms = false;
                 if (tid < 2) s_cnt[tid] = 0u;
                 __syncthreads();
-                if (c < n_wl) cand_eval(wl[c], v, gi, sraw, snms);
+                if (c < n_wl) cand_eval(resident ? (uint32_t)wl16[c] : wl[c], v, gi, sraw, snms);
                 const unsigned long long comp = make_comp(f2key(v), gi);
                 const uint32_t bal0 = __ballot_sync(FULL, sraw), bal1 = __ballot_sync(FULL, snms);
                 uint32_t lb0 = 0u, lb1 = 0u;
@@ -649,9 +731,16 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             const int nj = p.n_jobs;
             const bool split = (int)cs >= nj;  // else (single-CTA cluster, two jobs): one after the other
             const int n_sel = split ? 1 : nj;
+            const int cut = (int)cs / 2;
             for (int jj = 0; jj < n_sel; ++jj) {
-                const int li = split ? (int)rank % nj : jj;
-                const int part = split ? (int)rank / nj : 0, parts = split ? (int)cs / nj : 1;
+                int li = jj, part = 0, parts = 1;
+                if (split && nj == 2) {
+                    li = (int)rank < cut ? 0 : 1;
+                    part = li ? (int)rank - cut : (int)rank;
+                    parts = li ? (int)cs - cut : cut;
+                } else if (split) {
+                    li = 0, part = (int)rank, parts = (int)cs;
+                }
                 const uint32_t dst = smem_u32(xs_comp + li * K);
                 merge_select_part<ST>(p.mp, msm, b, li, part, parts, [&](int r, unsigned long long c) {
                     for (uint32_t c2 = 0; c2 < cs; ++c2) {

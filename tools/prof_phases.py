@@ -50,5 +50,9 @@ for rep in range(4):
         print("   rank %d: select load %.2f  rank %.2f | tail gather %.2f  epilogue %.2f" % ((r,) + tuple(mg[r::CS].mean(axis=0)) + tuple(tl[r::CS].mean(axis=0))))
     print("   passB: loop %.2f  sync %.2f  atomics+sync %.2f  copy %.2f" % tuple((np.diff(ex[1], axis=1) / 1.965e3).mean(axis=0)))
     print("   passB loop per CTA (warp 0):", " ".join("%.0f" % x for x in (buf[:, 12] - buf[:, 4]) / 1.965e3))
+    print("   passB: barrier waits %.2f flags %.2f sync %.2f" % tuple((np.diff(buf[:, [4, 30, 31, 29]], axis=1) / 1.965e3).mean(axis=0)))
+    print("   passB: masks %.2f park %.2f" % tuple((np.diff(buf[:, [29, 21, 12]], axis=1) / 1.965e3).mean(axis=0)))
+    print("   passB flag+sync %.2f; flagged groups per CTA:" % ((buf[:, 29] - buf[:, 4]).mean() / 1.965e3), " ".join(str(x) for x in buf[:, 27]))
+    print("   candidates per CTA:", " ".join(str(x) for x in buf[:, 28]))
     for r in range(min(CS, 4)):
         print("   rank %d mean:" % r, " ".join("%6.2f" % x for x in dt[r::CS].mean(axis=0)))
