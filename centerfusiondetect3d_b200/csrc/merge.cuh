@@ -20,6 +20,7 @@
 
 #ifndef CF_MERGE_PROF
 #define CF_MERGE_PROF(i) do { } while (0)
+#define CF_MERGE_PROF_DEP(i, v) do { } while (0)
 #endif
 
 namespace cf {
@@ -235,6 +236,22 @@ __device__ __forceinline__ void gather_local(const GatherTab& gt, int b, size_t 
     }
 }
 
+// The trigonometry of one detection on its 4 lanes (whole warps call this together): lane 0 atan2(rot2, rot3), lane 1
+// atan2(rot6, rot7), lane 2 the ray angle, then cos / sin of the yaw on lanes 0 / 1; returns the distance threshold on
+// every lane of the quad.
+__device__ __forceinline__ float frustum_thr_quad(float ay, float ax, float rot1, float rot5, float dim_w, float dim_l,
+                                               int tid) {
+    const int j = tid & 3;
+    const float at = j < 3 ? f32_atan2(ay, ax) : 0.0f;
+    const int l0 = (tid & 31) & ~3;
+    const float at1 = __shfl_sync(FULL, at, l0), at2 = __shfl_sync(FULL, at, l0 + 1),
+                ray = __shfl_sync(FULL, at, l0 + 2);
+    const float yaw = yaw_wrap(alpha_blend(rot1, rot5, at1, at2), ray);
+    const float cs_ = j == 0 ? (float)cos((double)yaw) : (j == 1 ? (float)sin((double)yaw) : 0.0f);
+    const float c = __shfl_sync(FULL, cs_, l0), s = __shfl_sync(FULL, cs_, l0 + 1);
+    return thr_from_cs(c, s, dim_w, dim_l);
+}
+
 // frustum geometry of this CTA's detections kl0 .. kl0+nb from the gathered heads: 4 lanes per detection, the three
 // atan2 and then sin / cos evaluated side by side (fp64, rounded once: the parity contract of geometry.cuh).  The
 // frustum parameters stay in shared memory (sdet[kl]) for the association.
@@ -242,11 +259,12 @@ __device__ __forceinline__ void gather_local(const GatherTab& gt, int b, size_t 
 // Executed by the thread group [0, T) given as (tid, T): whole warps.
 __device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const MergeJob& jb, int b,
                                                  const unsigned long long* comps, int first, int stride, int kl0, int nb,
-                                                 const float* gath, DetParam* sdet, int tid, int T) {
+                                                 const float* gath, DetParam* sdet, const float* cal, int tid, int T) {
     const int K = p.K, W = p.W, HWi = p.H * p.W;
     const int j = tid & 3;
+    // cal = {calib[0,0], calib[0,2]} of the frame where the caller fetched them ahead of time (the row is cold in DRAM)
     const float* calib = jb.fh.calib + 12 * (size_t)b;
-    const float cal0 = __ldg(calib + 0), cal2 = __ldg(calib + 2);
+    const float cal0 = cal ? cal[0] : __ldg(calib + 0), cal2 = cal ? cal[1] : __ldg(calib + 2);
     for (int q0 = 0; q0 < nb; q0 += T / 4) {
         const int q = q0 + (tid >> 2);
         const bool live = q < nb;
@@ -269,16 +287,12 @@ __device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const Mer
         // lane 0: atan2(rot2, rot3), lane 1: atan2(rot6, rot7), lane 2: the ray angle
         const float ay = j == 0 ? r[2] : (j == 1 ? r[6] : __fsub_rn(cx, cal2));
         const float ax = j == 0 ? r[3] : (j == 1 ? r[7] : cal0);
-        const float at = j < 3 ? f32_atan2(ay, ax) : 0.0f;
-        const int l0 = (tid & 31) & ~3;
-        const float at1 = __shfl_sync(FULL, at, l0), at2 = __shfl_sync(FULL, at, l0 + 1),
-                    ray = __shfl_sync(FULL, at, l0 + 2);
-        const float yaw = yaw_wrap(alpha_blend(r[1], r[5], at1, at2), ray);  // :372, :230-235
-        const float cs_ = j == 0 ? (float)cos((double)yaw) : (j == 1 ? (float)sin((double)yaw) : 0.0f);
-        const float c = __shfl_sync(FULL, cs_, l0), s = __shfl_sync(FULL, cs_, l0 + 1);
+        CF_MERGE_PROF_DEP(5, __float_as_int(ay) ^ __float_as_int(ax));
+        const float thr = frustum_thr_quad(ay, ax, r[1], r[5], g[FS_DIM + 1], g[FS_DIM + 2], tid);  // :372, :230-235, :380
+        CF_MERGE_PROF(6);
         if (live && j == 0) {
             d.depth = g[FS_DEPTH];
-            d.thr = thr_from_cs(c, s, g[FS_DIM + 1], g[FS_DIM + 2]);  // :380
+            d.thr = thr;
             d.ind = ind;
             d.pad_ = 0;
             sdet[kl] = d;
@@ -372,7 +386,8 @@ __device__ __forceinline__ void copy_head(const float* head, float* out, int nch
 // gathers of all jobs, then their epilogues.  gath holds n_jobs * GB * GATH_STRIDE floats.
 template <int T>
 __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int b, int first, int stride, int n_local,
-                                           const unsigned long long* xs_comp, float* gath, int GB, DetParam* sdet) {
+                                           const unsigned long long* xs_comp, float* gath, int GB, DetParam* sdet,
+                                           const float* cal) {
     const int K = p.K, HWi = p.H * p.W;
     for (int kl0 = 0; kl0 < n_local; kl0 += GB) {
         const int nb = min(GB, n_local - kl0);
@@ -411,7 +426,7 @@ __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int
                     if (jb.topk.xs) jb.topk.xs[o] = x;
                 }
             } else if (jb.epilogue == EPI_FRUSTUM) {
-                epilogue_frustum(p, jb, b, comps, first, stride, kl0, nb, g, sdet, gt, half);
+                epilogue_frustum(p, jb, b, comps, first, stride, kl0, nb, g, sdet, cal, gt, half);
             } else if (jb.epilogue == EPI_DECODE) {
                 epilogue_decode(p, jb, b, comps, first, stride, kl0, nb, g, gt, half);
                 copy_head(jb.dec.heads.rot, jb.dec.out.rot, 8, DS_ROT, b, K, first, stride, kl0, nb, g, gt, half);
@@ -420,6 +435,7 @@ __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int
                 copy_head(jb.dec.heads.velocity, jb.dec.out.velocity, 3, DS_VEL, b, K, first, stride, kl0, nb, g, gt, half);
             }
         }
+        CF_MERGE_PROF(7);
         __syncthreads();
         CF_MERGE_PROF(4);
     }

@@ -55,6 +55,7 @@ namespace cf {
 constexpr int ST = 512;          // threads per CTA
 constexpr int SNW = ST / 32;     // warps
 constexpr int WL_CAP = 640;      // pass-B work list: candidate pixels a CTA parks before it tests them side by side
+constexpr int WL_CAP_RING = 4096;  // ... when the share streams through a ring of slots (shared memory to spare)
 constexpr int FL_CAP = 256;      // pass-B flagged-group list (resident shares)
 constexpr int MAX_SLOTS = 64;
 constexpr int MAX_CS = 16;
@@ -103,6 +104,14 @@ __device__ long long g_prof[1024 * PROF_PTS];
     do {                                                                                                  \
         if (p.prof && threadIdx.x == 0 && blockIdx.x < 1024) g_prof[blockIdx.x * PROF_PTS + 16 + (i)] = clock64(); \
     } while (0)
+#define CF_MERGE_PROF_DEP(i, val)                                                                          \
+    do {                                                                                                  \
+        if (p.prof && threadIdx.x == 0 && blockIdx.x < 1024) {                                            \
+            long long t_;                                                                                 \
+            asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"(val) : "memory");                      \
+            g_prof[blockIdx.x * PROF_PTS + 16 + (i)] = t_;                                                \
+        }                                                                                                 \
+    } while (0)
 #define PROF(i)                                                                              \
     do {                                                                                     \
         if (p.prof && tid == 0 && blockIdx.x < 1024) g_prof[blockIdx.x * PROF_PTS + (i)] = clock64(); \
@@ -128,8 +137,9 @@ struct StageParams {
     // byte offsets inside the slot area once the heat-map is done with it: [paint records K | sorted composites 2K |
     // selection scratch | gather buffers | frustum parameters | matches | depth plane]; the owner map of the paint
     // takes everything behind the records
-    int off_comp, off_msm, off_gath, off_det, off_best, off_own;
+    int off_comp, off_msm, off_gath, off_det, off_best, off_par, off_own;
     int GB;            // detections per gather batch
+    int wl_entries;    // words of the pass-B work list
     uint32_t* ctr;
     unsigned long long* cand;
     MergeParams mp;
@@ -241,6 +251,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     __shared__ uint32_t s_tops[2][MAX_CS];
     __shared__ uint32_t s_mytop[2];
     __shared__ uint32_t s_nwl;  // entries of the pass-B work list
+    __shared__ float s_cal[2];    // calib[0,0], calib[0,2] of the frame (fetched at frame start)
     __shared__ uint32_t s_nfl;  // pass B, resident shares: flagged groups (a group = the 1/32 of a chunk one lane took in pass A)
     __shared__ uint16_t s_fl[FL_CAP];
     __shared__ uint32_t s_cnt[2], s_base[2];  // pass B2: survivors of this CTA per list, their base in the frame's list
@@ -256,7 +267,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
 
     float* slots = reinterpret_cast<float*>(smem);
     uint32_t* hist = reinterpret_cast<uint32_t*>(smem + p.slot_area);
-    uint32_t* wl = hist + p.hist_words;  // pass-B work list, WL_CAP entries
+    uint32_t* wl = hist + p.hist_words;  // pass-B work list, p.wl_entries words
     const uint32_t hist_saddr = smem_u32(hist);
     const int list_words = p.hist_words >> 1;
 
@@ -268,6 +279,13 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     const int LPF = n + n_ref;                         // bulk copies per frame
     const bool resident = use_tma && n_ref == 0;
 
+    // The merge parameters (two jobs with their head tables) are indexed at run time (job of this half of the CTA, head
+    // channel of this thread).  Out of the kernel's parameter space such a read costs microseconds the first time, so
+    // every thread fetches one word of them now -- the latency passes during pass A -- and parks it in shared memory
+    // once the heat-map has left the slot area.
+    static_assert(sizeof(MergeParams) <= ST * 4 && sizeof(MergeParams) % 4 == 0, "one word per thread");
+    uint32_t par_word = 0u;
+    if (tid < (int)(sizeof(MergeParams) / 4)) par_word = reinterpret_cast<const uint32_t*>(&p.mp)[tid];
     if (tid < MAX_SLOTS) s_issued[tid] = 0u;
     if (tid == 0) {
         for (int s = 0; s < S; ++s) mbar_init(&full[s], 1);
@@ -343,6 +361,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         cl_arrive();
         if (use_tma && tid < (LPF < S ? LPF : S)) issue_load(tid);
         if (rank == 0 && tid < 2 * CTR_STRIDE) ctr_raw[tid] = 0u;  // ordered before any append by the next barrier
+        if (p.do_frustum && tid >= ST - 2)  // (the last warp: it stalls on this DRAM read before its first chunk)
+            s_cal[tid - (ST - 2)] = __ldg(p.mp.job[0].fh.calib + 12 * (size_t)b + 2 * (tid - (ST - 2)));
         if (p.do_frustum) {  // the association's radar maps: into L2 while the heat-map streams
             const char* pd = reinterpret_cast<const char*>(p.pc_dep + (size_t)b * 3 * HW);
             const size_t lines = (3 * HW * 4 + 127) / 128;
@@ -529,7 +549,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             // park this lane's candidates (bit j of mask: pixel j of float4 item_of(bit)) in the work list from `slot` on;
             // lanes that hold several park one per round, so that a blob's pixels are written side by side
             uint16_t* wl16 = reinterpret_cast<uint16_t*>(wl);
-            const uint32_t wl_cap = resident ? 2u * WL_CAP : (uint32_t)WL_CAP;
+            const uint32_t wl_cap = resident ? 2u * (uint32_t)p.wl_entries : (uint32_t)p.wl_entries;
             auto park = [&](uint32_t mask, uint32_t slot, int q, auto&& item_of) {
                 for (;;) {
                     const bool mine = mask != 0u;
@@ -607,7 +627,6 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                                 }
                             }
                         }
-                        PROF(21);
                         const uint32_t total = __reduce_add_sync(FULL, (uint32_t)__popc(mask));
                         if (!total) continue;
                         uint32_t slot = 0u;
@@ -713,7 +732,9 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             PROF(14);
             fence_async_smem();
             __syncthreads();
-            // the slot area is free from here on.  Stage the radar depth plane for the association.
+            // the slot area is free from here on: the merge parameters move in (visible after the cluster barrier)
+            if (tid < (int)(sizeof(MergeParams) / 4)) reinterpret_cast<uint32_t*>(smem + p.off_par)[tid] = par_word;
+            // Stage the radar depth plane for the association.
             if (p.do_frustum && p.dep_off >= 0 && tid == 0) {
                 const uint32_t bytes = (uint32_t)(HW * 4);
                 mbar_expect_tx(&dep_bar, bytes);
@@ -726,6 +747,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
 
         // ---- select: the CTAs split the ranking of the jobs' survivor lists; sorted composites land everywhere -------
         unsigned long long* xs_comp = reinterpret_cast<unsigned long long*>(smem + p.off_comp);  // [job][K]
+        const MergeParams& mp = *reinterpret_cast<const MergeParams*>(smem + p.off_par);
         {
             MergeSmem& msm = *reinterpret_cast<MergeSmem*>(smem + p.off_msm);
             const int nj = p.n_jobs;
@@ -742,7 +764,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     li = 0, part = (int)rank, parts = (int)cs;
                 }
                 const uint32_t dst = smem_u32(xs_comp + li * K);
-                merge_select_part<ST>(p.mp, msm, b, li, part, parts, [&](int r, unsigned long long c) {
+                merge_select_part<ST>(mp, msm, b, li, part, parts, [&](int r, unsigned long long c) {
                     for (uint32_t c2 = 0; c2 < cs; ++c2) {
                         const uint32_t ra = cl_map(dst + 8u * (uint32_t)r, c2);
                         cl_st(ra, (uint32_t)c);
@@ -758,8 +780,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         // ---- tail: detection k belongs to CTA k % CS: gathers, frustum geometry / decode outputs ----------------------
         const int n_local = (K - (int)rank + (int)cs - 1) / (int)cs;
         DetParam* sdet = reinterpret_cast<DetParam*>(smem + p.off_det);
-        merge_tail<ST>(p.mp, p.n_jobs, b, (int)rank, (int)cs, n_local, xs_comp, reinterpret_cast<float*>(smem + p.off_gath),
-                       p.GB, sdet);
+        merge_tail<ST>(mp, p.n_jobs, b, (int)rank, (int)cs, n_local, xs_comp, reinterpret_cast<float*>(smem + p.off_gath),
+                       p.GB, sdet, p.do_frustum ? s_cal : nullptr);
         PROF(24);
         if (!p.do_frustum) continue;
 
@@ -821,7 +843,8 @@ static size_t align_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct StagePlan {
     int cs, cs_log2, R, S, slot_floats, hist_words, slot_area, dep_off, n_clusters;
-    int off_comp, off_msm, off_gath, off_det, off_best, off_own, GB;
+    int off_comp, off_msm, off_gath, off_det, off_best, off_par, off_own, GB, wl_entries;
+    bool resident;
     size_t smem;
 };
 
@@ -844,11 +867,23 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
     while (((share + R - 1) / R) * 32 * cs > 65535) ++R;
     const size_t slot_bytes = align_up_sz((size_t)R * Wp * 4, 16);
     const int hist_words = 2 * (HIST_BINS / cs) / 2;
-    const size_t fixed = (size_t)hist_words * 4 + (size_t)WL_CAP * sizeof(uint32_t);
+    size_t fixed = (size_t)hist_words * 4 + (size_t)WL_CAP * sizeof(uint32_t);
     if (fixed + slot_bytes > SMEM_DYN_CAP) return false;
     const long long n = (share + R - 1) / R;
     long long S = (long long)((SMEM_DYN_CAP - fixed) / slot_bytes);
     if (S > MAX_SLOTS) S = MAX_SLOTS;
+    int wl_entries = WL_CAP;
+    if (S < n || !use_tma) {
+        // the share does not stay resident: its CTA sees more candidates (bigger share) and a ring of a few slots less
+        // streams just as well -> room for a long work list
+        const size_t fixed_long = (size_t)hist_words * 4 + (size_t)WL_CAP_RING * sizeof(uint32_t);
+        const long long S_long = fixed_long + slot_bytes <= SMEM_DYN_CAP ? (long long)((SMEM_DYN_CAP - fixed_long) / slot_bytes) : 0;
+        if (S_long >= (use_tma ? 4 : SNW)) {
+            wl_entries = WL_CAP_RING;
+            fixed = fixed_long;
+            S = S_long < MAX_SLOTS ? S_long : MAX_SLOTS;
+        }
+    }
     if (use_tma) {
         if (S > n) S = n;
     } else {
@@ -864,7 +899,8 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
     const size_t off_gath = align_up_sz(off_msm + sizeof(MergeSmem), 128);
     const size_t off_det = align_up_sz(off_gath + 2 * (size_t)GB * GATH_STRIDE * 4, 128);
     const size_t off_best = align_up_sz(off_det + (size_t)n_local_max * sizeof(DetParam), 128);
-    const size_t tail_end = align_up_sz(off_best + (size_t)n_local_max * 8, 128);
+    const size_t off_par = align_up_sz(off_best + (size_t)n_local_max * 8, 128);
+    const size_t tail_end = align_up_sz(off_par + sizeof(MergeParams), 128);
     const size_t off_own = align_up_sz((size_t)K * sizeof(PaintRec), 16);
     size_t area = (size_t)S * slot_bytes;
     if (area < tail_end) area = tail_end;
@@ -892,8 +928,11 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
     pl->off_gath = (int)off_gath;
     pl->off_det = (int)off_det;
     pl->off_best = (int)off_best;
+    pl->off_par = (int)off_par;
     pl->off_own = (int)off_own;
     pl->GB = GB;
+    pl->wl_entries = wl_entries;
+    pl->resident = use_tma && S >= n;
     pl->smem = area + fixed;
     return true;
 }
@@ -949,7 +988,7 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     const bool do_frustum = raw_job && raw_job->epilogue == EPI_FRUSTUM && pc_dep && pc_hm;
     const bool use_tma = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(heat) & 15u) == 0);
     const bool stage_dep = do_frustum && (((size_t)H * W) % 4 == 0) && ((reinterpret_cast<uintptr_t>(pc_dep) & 15u) == 0);
-    // cluster size: fewest rounds over the batch, then the most CTAs per frame
+    // cluster size: cheapest sum of rounds over the batch, then the most CTAs per frame
     StagePlan best;
     long long best_rounds = -1;
     int force_cs = 0;
@@ -965,7 +1004,8 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
         if (getenv("CFD3D_VERBOSE")) fprintf(stderr, "[cfd3d]   cs=%d: %d co-resident clusters (smem %zu)\n", cs, cap, pl.smem);
         if (cap < 1) continue;
         pl.n_clusters = B < cap ? B : cap;
-        const long long rounds = ((long long)B + pl.n_clusters - 1) / pl.n_clusters;
+        // a round over a resident share costs about a third of one that streams its share twice (measured, README)
+        const long long rounds = (((long long)B + pl.n_clusters - 1) / pl.n_clusters) * (pl.resident ? 1 : 3);
         if (best_rounds < 0 || rounds < best_rounds) {
             best = pl;
             best_rounds = rounds;
@@ -996,8 +1036,10 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     p.off_gath = best.off_gath;
     p.off_det = best.off_det;
     p.off_best = best.off_best;
+    p.off_par = best.off_par;
     p.off_own = best.off_own;
     p.GB = best.GB;
+    p.wl_entries = best.wl_entries;
     p.ctr = ws.ctr;
     p.cand = ws.cand;
     p.mp.heat = heat;
