@@ -292,6 +292,10 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         mbar_init(&dep_bar, 1);
         mbar_fence_init();
     }
+    // programmatic dependent launch (see launch_fusion_stage): let the next kernel of the stream place its CTAs as ours
+    // retire, and do not touch global memory before the kernel ahead of us has completed
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     __syncthreads();
 
     int it = 0;
@@ -1083,9 +1087,17 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
         if (e != cudaSuccess) return e;
     }
     cudaLaunchConfig_t cfg;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     memset(&cfg, 0, sizeof(cfg));
     launch_cfg(best, best.n_clusters * best.cs, st, &cfg, attr);
+    if (!getenv("CFD3D_NO_PDL")) {
+        // programmatic dependent launch: this grid's CTAs may be placed (and run their prologue) while the kernel before
+        // it in the stream drains; they touch global memory only after griddepcontrol.wait.  Back-to-back stage calls
+        // (batches streaming through a graph) hide the grid launch latency that way.
+        attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[1].val.programmaticStreamSerializationAllowed = 1;
+        cfg.numAttrs = 2;
+    }
     if (getenv("CFD3D_VERBOSE"))
         fprintf(stderr, "[cfd3d] stage plan: B=%d cs=%d clusters=%d R=%d S=%d slot=%dB area=%d dep_off=%d smem=%zu tma=%d\n", B,
                 best.cs, best.n_clusters, best.R, best.S, best.slot_floats * 4, best.slot_area, best.dep_off, best.smem,
