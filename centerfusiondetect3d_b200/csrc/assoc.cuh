@@ -77,9 +77,20 @@ __device__ __forceinline__ void paint_window(float x1, float y1, float x2, float
     pyslice(wmin, wmax + 2, W, ca, cb);
 }
 
-// The matched pixel of one detection -> paint record + association index (one thread).  best = the reduced roi_scan
+// the window into a detection's parameters (any thread, ahead of the association: it depends on the box alone)
+__device__ __forceinline__ void det_set_window(DetParam& d, int H, int W) {
+    int ra, rb, ca, cb;
+    paint_window(d.x1, d.y1, d.x2, d.y2, H, W, ra, rb, ca, cb);
+    const bool ok = ra < rb && ca < cb;
+    d.ra = ok ? (int16_t)ra : 0;
+    d.rb = ok ? (int16_t)rb : 0;
+    d.ca = ok ? (int16_t)ca : 0;
+    d.cb = ok ? (int16_t)cb : 0;
+}
+
+// The matched pixel of one detection -> paint record + association index (one thread).  d carries its paint window.  best = the reduced roi_scan
 // key (~0 = no radar pixel in range), dep = the frame's pc_dep (3,H,W) in global memory (velocity channels).
-__device__ __forceinline__ PaintRec assoc_finalize(unsigned long long best, const float* __restrict__ dep, int H, int W,
+__device__ __forceinline__ PaintRec assoc_finalize(unsigned long long best, const float* dep, int H, int W,
                                                    const DetParam& d, float max_pc_dist, int32_t* assoc_out) {
     const size_t HW = (size_t)H * W;
     PaintRec r;
@@ -91,16 +102,12 @@ __device__ __forceinline__ PaintRec assoc_finalize(unsigned long long best, cons
         const uint32_t mp = (uint32_t)best;
         a = (int32_t)mp;
         r.v0 = __fdiv_rn(__uint_as_float((uint32_t)(best >> 32)), max_pc_dist);  // :462-466
-        r.v1 = __ldg(dep + HW + mp);
-        r.v2 = __ldg(dep + 2 * HW + mp);
-        int ra, rb, ca, cb;
-        paint_window(d.x1, d.y1, d.x2, d.y2, H, W, ra, rb, ca, cb);
-        if (ra < rb && ca < cb) {
-            r.ra = (int16_t)ra;
-            r.rb = (int16_t)rb;
-            r.ca = (int16_t)ca;
-            r.cb = (int16_t)cb;
-        }
+        r.v1 = dep[HW + mp];
+        r.v2 = dep[2 * HW + mp];
+        r.ra = d.ra;
+        r.rb = d.rb;
+        r.ca = d.ca;
+        r.cb = d.cb;
     }
     if (assoc_out) *assoc_out = a;
     return r;

@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(BW * 32) box_assoc_kernel(const float* __restr
     unsigned long long best = ~0ull;
     DetParam d;
     d.x1 = d.y1 = d.x2 = d.y2 = d.depth = d.thr = 0.0f;
-    d.ind = d.pad_ = 0;
+    d.ra = d.rb = d.ca = d.cb = 0;
     const bool live = !counts || n < counts[b];
     if (live) {
         d.x1 = __ldg(bboxes + 4 * o);
@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(BW * 32) box_assoc_kernel(const float* __restr
         d.depth = __ldg(depth + o);
         d.thr = __ldg(thr + o);
         best = warp_min_u64(roi_scan<16>(dep, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32));
+        det_set_window(d, H, W);
     }
     if (lane == 0) recs[o] = assoc_finalize(best, dep, H, W, d, max_pc_dist, assoc ? assoc + o : nullptr);
 }

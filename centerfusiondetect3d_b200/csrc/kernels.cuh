@@ -17,9 +17,9 @@ constexpr int CTR_STRIDE = 4;                        // per (frame, list): [0] s
 struct __align__(16) DetParam {
     float x1, y1, x2, y2;
     float depth, thr;
-    int32_t ind;  // flat pixel of the peak
-    int32_t pad_;
+    int16_t ra, rb, ca, cb;  // paint window (assoc.cuh paint_window), rb <= ra or cb <= ca: empty
 };
+static_assert(sizeof(DetParam) == 32, "DetParam");
 
 // ordered rectangle paint record: pixel rows [ra,rb) x cols [ca,cb) take (v0,v1,v2); the record with
 // the LARGEST index covering a pixel wins (== the reference's sequential overwrite order)

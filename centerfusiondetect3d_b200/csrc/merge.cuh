@@ -14,6 +14,7 @@
 #pragma once
 #include <math_constants.h>
 
+#include "assoc.cuh"
 #include "geometry.cuh"
 #include "kernels.cuh"
 #include "select.cuh"
@@ -265,23 +266,46 @@ __device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const Mer
     // cal = {calib[0,0], calib[0,2]} of the frame where the caller fetched them ahead of time (the row is cold in DRAM)
     const float* calib = jb.fh.calib + 12 * (size_t)b;
     const float cal0 = cal ? cal[0] : __ldg(calib + 0), cal2 = cal ? cal[1] : __ldg(calib + 2);
-    for (int q0 = 0; q0 < nb; q0 += T / 4) {
-        const int q = q0 + (tid >> 2);
-        const bool live = q < nb;
-        const int kl = kl0 + (live ? q : 0), k = first + kl * stride;
-        const float* g = gath + (live ? q : 0) * GATH_STRIDE;
-        const int ind = (int)(comp_gidx(comps[k]) % (uint32_t)HWi);
+    // box of detection q of this batch (every thread that needs it computes it: a handful of instructions)
+    auto box_of = [&](int q, int& ind, DetParam& d) {
+        const int k = first + (kl0 + q) * stride;
+        const float* g = gath + q * GATH_STRIDE;
+        ind = (int)(comp_gidx(comps[k]) % (uint32_t)HWi);
         const int y = ind / W, x = ind - y * W;
         const float xf = __fadd_rn((float)x, 0.5f), yf = __fadd_rn((float)y, 0.5f);
         float w = g[FS_WH], h = g[FS_WH + 1];
         if (w < 0.0f) w = 0.0f;
         if (h < 0.0f) h = 0.0f;
         const float hw2 = __fdiv_rn(w, 2.0f), hh2 = __fdiv_rn(h, 2.0f);
-        DetParam d;
         d.x1 = __fsub_rn(xf, hw2);
         d.y1 = __fsub_rn(yf, hh2);
         d.x2 = __fadd_rn(xf, hw2);
         d.y2 = __fadd_rn(yf, hh2);
+    };
+    // The paint window of a detection depends on its box alone.  When the quads of the trigonometry leave the upper
+    // half of the thread group idle, those warps work the windows out meanwhile (one thread per detection) instead of
+    // the association's single finishing thread per detection later.
+    const bool side = (T % 64 == 0) && nb * 4 <= T / 2 && nb <= T / 2;
+    if (side && tid >= T / 2) {
+        const int q = tid - T / 2;
+        if (q < nb) {
+            int ind;
+            DetParam d;
+            box_of(q, ind, d);
+            det_set_window(d, p.H, W);
+            *reinterpret_cast<short4*>(&sdet[kl0 + q].ra) = make_short4(d.ra, d.rb, d.ca, d.cb);
+        }
+        return;
+    }
+    for (int q0 = 0; q0 < nb; q0 += T / 4) {
+        const int q = q0 + (tid >> 2);
+        const bool live = q < nb;
+        const int ql = live ? q : 0;
+        const int kl = kl0 + ql, k = first + kl * stride;
+        const float* g = gath + ql * GATH_STRIDE;
+        int ind;
+        DetParam d;
+        box_of(ql, ind, d);
         const float cx = __fdiv_rn(__fadd_rn(d.x1, d.x2), 2.0f);  // :373-379
         const float* r = g + FS_ROT;
         // lane 0: atan2(rot2, rot3), lane 1: atan2(rot6, rot7), lane 2: the ray angle
@@ -293,9 +317,12 @@ __device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const Mer
         if (live && j == 0) {
             d.depth = g[FS_DEPTH];
             d.thr = thr;
-            d.ind = ind;
-            d.pad_ = 0;
-            sdet[kl] = d;
+            *reinterpret_cast<float4*>(&sdet[kl].x1) = make_float4(d.x1, d.y1, d.x2, d.y2);
+            *reinterpret_cast<float2*>(&sdet[kl].depth) = make_float2(d.depth, d.thr);
+            if (!side) {
+                det_set_window(d, p.H, W);
+                *reinterpret_cast<short4*>(&sdet[kl].ra) = make_short4(d.ra, d.rb, d.ca, d.cb);
+            }
             const size_t o = (size_t)b * K + k;
             if (jb.fo.thr) jb.fo.thr[o] = d.thr;
             if (jb.fo.inds) jb.fo.inds[o] = ind;

@@ -367,11 +367,15 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         if (rank == 0 && tid < 2 * CTR_STRIDE) ctr_raw[tid] = 0u;  // ordered before any append by the next barrier
         if (p.do_frustum && tid >= ST - 2)  // (the last warp: it stalls on this DRAM read before its first chunk)
             s_cal[tid - (ST - 2)] = __ldg(p.mp.job[0].fh.calib + 12 * (size_t)b + 2 * (tid - (ST - 2)));
-        if (p.do_frustum) {  // the association's radar maps: into L2 while the heat-map streams
-            const char* pd = reinterpret_cast<const char*>(p.pc_dep + (size_t)b * 3 * HW);
-            const size_t lines = (3 * HW * 4 + 127) / 128;
-            for (size_t l = (size_t)rank * ST + tid; l < lines; l += (size_t)cs * ST)
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(pd + l * 128));
+        if (p.do_frustum && tid == 0) {  // the association's radar maps: into L2 while the heat-map streams
+            const size_t total = 3 * HW * 4, per = ((total + cs - 1) / cs + 15) & ~(size_t)15;
+            const size_t off = per * rank;
+            if (off < total) {
+                const size_t nbytes = (min(per, total - off)) & ~(size_t)15;
+                const char* pd = reinterpret_cast<const char*>(p.pc_dep + (size_t)b * 3 * HW) + off;
+                if (nbytes && ((reinterpret_cast<uintptr_t>(pd) & 15u) == 0))
+                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pd), "r"((uint32_t)nbytes) : "memory");
+            }
         }
         PROF(15);
         cl_wait();
@@ -816,6 +820,11 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 const size_t o = (size_t)b * K + k;
                 const PaintRec r = assoc_finalize(sbest[kl], dep, H, W, sdet[kl], p.max_pc_dist, p.assoc ? p.assoc + o : nullptr);
                 const uint32_t* rw = reinterpret_cast<const uint32_t*>(&r);
+                if (p.prof && tid == 0 && blockIdx.x < 1024) {
+                    long long t_;
+                    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"(rw[0] ^ rw[1] ^ rw[2] ^ rw[3] ^ rw[4]) : "memory");
+                    g_prof[blockIdx.x * PROF_PTS + 27] = t_;
+                }
                 const uint32_t dst = smem_u32(srecs + k);
                 for (uint32_t c = 0; c < cs; ++c) {
                     const uint32_t ra = cl_map(dst, c);
@@ -1077,7 +1086,7 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     p.pc_hm_stride = pc_hm_stride > 0 ? pc_hm_stride : 3ll * H * W;
     p.assoc = assoc;
     p.recs = ws.recs;
-    p.prof = getenv("CFD3D_PROF") ? 1 : 0;
+    p.prof = getenv("CFD3D_PROF") ? atoi(getenv("CFD3D_PROF")) : 0;
     p.mp.prof = p.prof;
 
     cudaError_t e = cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)best.smem);

@@ -53,6 +53,7 @@ for rep in range(6):
     for i, nm in enumerate(names):
         print("   %-14s %7.2f %7.2f %7.2f" % (nm, dt[:, i].min(), dt[:, i].mean(), dt[:, i].max()))
     az = np.diff(buf[:, [24, 25, 26, 9]], axis=1) / 1.965e3
+    print("   assoc finalize (thread 0): record ready %.2f  broadcast %.2f" % tuple((np.diff(buf[:, [26, 27, 9]], axis=1) / 1.965e3).mean(axis=0)))
     print("   assoc: scans (warp 0) %.2f  sync %.2f  finalize+broadcast %.2f" % tuple(az.mean(axis=0)))
     ex = buf[:, [0, 15, 1]], buf[:, [4, 12, 13, 14, 5]]
     mg = np.diff(buf[:, 16:19], axis=1) / 1.965e3
