@@ -59,6 +59,9 @@ SYMBOLS = {
                                                                        C.POINTER(DecodeOut), _vp, _Z, _vp]),
     "cf_fusion_stage_strided": (_I, [_vp] * 7 + [_I] * 5 + [_F] + [_vp, _L] + [_vp] * 3 + [C.POINTER(DecodeHeads), _I, _I, _I,
                                                                                         C.POINTER(DecodeOut), _vp, _Z, _vp]),
+    "cf_fusion_stage_split": (_I, [_vp] * 8 + [_I] * 5 + [_F] + [_vp, _L] + [_vp] * 3 + [C.POINTER(DecodeHeads), _I, _I, _I,
+                                                                                      C.POINTER(DecodeOut), _vp, _Z, _vp]),
+    "cf_stage_depth_plane": (_I, [_vp, _vp, _I, _I, _I, _vp]),
     "cf_radar_sort": (_I, [_vp, _vp, _I, _I, _vp, _vp, _vp]),
     "cf_frustum_boxes": (_I, [_vp] * 5 + [_I] * 4 + [_F, _vp, _vp, _vp, _Z, _vp]),
     "cf_post_process": (_I, [C.POINTER(PostIn), _I, _I, _I, _I, C.POINTER(C.c_float), _vp, _I, C.POINTER(PostOut), _vp]),

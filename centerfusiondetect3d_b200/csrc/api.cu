@@ -79,7 +79,7 @@ static int run_peak_passes(const float* heat, int B, int C, int H, int W, int K,
     if (raw_job) finish_job(raw_job);
     if (nms_job) finish_job(nms_job);
     CF_KERNEL(CF_KERNEL_STAGE, st,
-              launch_fusion_stage(heat, B, C, H, W, K, w, raw_job, nms_job, nullptr, 0.0f, nullptr, 0, nullptr, st, n),
+              launch_fusion_stage(heat, B, C, H, W, K, w, raw_job, nms_job, nullptr, nullptr, 0.0f, nullptr, 0, nullptr, st, n),
               "fusion_stage");
     return 0;
 }
@@ -252,6 +252,16 @@ int cf_fusion_stage_strided(const float* heat, const float* wh, const float* dep
                             float max_pc_dist, float* pc_hm, int64_t pc_hm_batch_stride, int32_t* assoc, float* thr,
                             int64_t* inds, const cf_decode_heads_t* dec_heads, int out_h, int out_w, int norm2d,
                             const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes, void* stream) {
+    return cf_fusion_stage_split(heat, wh, depth, dim, rot, pc_dep, nullptr, calib, B, C, H, W, K, max_pc_dist, pc_hm,
+                                 pc_hm_batch_stride, assoc, thr, inds, dec_heads, out_h, out_w, norm2d, dec_out, ws,
+                                 ws_bytes, stream);
+}
+
+int cf_fusion_stage_split(const float* heat, const float* wh, const float* depth, const float* dim, const float* rot,
+                          const float* pc_dep, const float* pc_dep_vel, const float* calib, int B, int C, int H, int W,
+                          int K, float max_pc_dist, float* pc_hm, int64_t pc_hm_batch_stride, int32_t* assoc, float* thr,
+                          int64_t* inds, const cf_decode_heads_t* dec_heads, int out_h, int out_w, int norm2d,
+                          const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes, void* stream) {
     if (pc_hm_batch_stride < 3ll * H * W) return fail(CF_E_SHAPE, "cf_fusion_stage: pc_hm batch stride < 3*H*W");
     g_launches = 0;
     if (B == 0) return 0;
@@ -287,10 +297,22 @@ int cf_fusion_stage_strided(const float* heat, const float* wh, const float* dep
     finish_job(&fj);
     if (with_decode) finish_job(&dj);
     CF_KERNEL(CF_KERNEL_STAGE, st,
-              launch_fusion_stage(heat, B, C, H, W, K, w, &fj, with_decode ? &dj : nullptr, pc_dep, max_pc_dist, pc_hm,
+              launch_fusion_stage(heat, B, C, H, W, K, w, &fj, with_decode ? &dj : nullptr, pc_dep, pc_dep_vel, max_pc_dist, pc_hm,
                                   (long long)pc_hm_batch_stride, assoc, st, &n),
               "fusion_stage");
     g_launches = n;
+    return 0;
+}
+
+int cf_stage_depth_plane(float* pc_dep_dev, const float* pc_dep_host, int B, int H, int W, void* stream) {
+    g_launches = 0;
+    if (B == 0) return 0;
+    if (!pc_dep_dev || !pc_dep_host) return fail(CF_E_NULL, "cf_stage_depth_plane: NULL pointer");
+    if (B < 0 || H <= 0 || W <= 0) return fail(CF_E_SHAPE, "cf_stage_depth_plane: bad shape");
+    const size_t plane = (size_t)H * W * sizeof(float);
+    CF_CUDA(cudaMemcpy2DAsync(pc_dep_dev, 3 * plane, pc_dep_host, 3 * plane, plane, (size_t)B, cudaMemcpyHostToDevice,
+                              (cudaStream_t)stream),
+            "cf_stage_depth_plane");
     return 0;
 }
 

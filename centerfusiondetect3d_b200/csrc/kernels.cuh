@@ -102,8 +102,8 @@ struct MergeParams {
 // job and pc_dep / pc_hm are given) in ONE launch, one thread-block cluster per frame
 cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, int K, const Workspace& ws,
                                 const MergeJob* raw_job, const MergeJob* nms_job, const float* pc_dep,
-                                float max_pc_dist, float* pc_hm, long long pc_hm_stride, int32_t* assoc, cudaStream_t st,
-                                int* launches);
+                                const float* pc_vel, float max_pc_dist, float* pc_hm, long long pc_hm_stride,
+                                int32_t* assoc, cudaStream_t st, int* launches);
 cudaError_t launch_post_process(const cf_post_in_t& in, int B, int K, int out_h, int out_w, const float* trans_host,
                                 const float* calib, int is_gt, const cf_post_out_t& out, cudaStream_t st,
                                 int* launches);

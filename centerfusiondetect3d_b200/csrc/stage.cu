@@ -146,6 +146,7 @@ struct StageParams {
     int n_jobs;
     int do_frustum;
     const float* pc_dep;
+    const float* pc_vel;  // (B,3,H,W) whose planes 1, 2 hold the velocities (== pc_dep unless they stayed in host memory)
     float max_pc_dist;
     float* pc_hm;
     long long pc_hm_stride;  // floats between the pc_hm of consecutive frames (3*H*W, or 67*H*W inside the combiner input)
@@ -368,7 +369,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         if (p.do_frustum && tid >= ST - 2)  // (the last warp: it stalls on this DRAM read before its first chunk)
             s_cal[tid - (ST - 2)] = __ldg(p.mp.job[0].fh.calib + 12 * (size_t)b + 2 * (tid - (ST - 2)));
         if (p.do_frustum && tid == 0) {  // the association's radar maps: into L2 while the heat-map streams
-            const size_t total = 3 * HW * 4, per = ((total + cs - 1) / cs + 15) & ~(size_t)15;
+            const size_t total = (p.pc_vel == p.pc_dep ? 3 : 1) * HW * 4, per = ((total + cs - 1) / cs + 15) & ~(size_t)15;
             const size_t off = per * rank;
             if (off < total) {
                 const size_t nbytes = (min(per, total - off)) & ~(size_t)15;
@@ -818,7 +819,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             for (int kl = tid; kl < n_local; kl += ST) {
                 const int k = (int)rank + kl * (int)cs;
                 const size_t o = (size_t)b * K + k;
-                const PaintRec r = assoc_finalize(sbest[kl], dep, H, W, sdet[kl], p.max_pc_dist, p.assoc ? p.assoc + o : nullptr);
+                const PaintRec r = assoc_finalize(sbest[kl], p.pc_vel + (size_t)b * 3 * HW, H, W, sdet[kl], p.max_pc_dist, p.assoc ? p.assoc + o : nullptr);
                 const uint32_t* rw = reinterpret_cast<const uint32_t*>(&r);
                 if (p.prof && tid == 0 && blockIdx.x < 1024) {
                     long long t_;
@@ -996,8 +997,8 @@ static int max_clusters(const StagePlan& pl) {
 
 cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, int K, const Workspace& ws,
                                 const MergeJob* raw_job, const MergeJob* nms_job, const float* pc_dep,
-                                float max_pc_dist, float* pc_hm, long long pc_hm_stride, int32_t* assoc, cudaStream_t st,
-                                int* launches) {
+                                const float* pc_vel, float max_pc_dist, float* pc_hm, long long pc_hm_stride,
+                                int32_t* assoc, cudaStream_t st, int* launches) {
     const bool do_frustum = raw_job && raw_job->epilogue == EPI_FRUSTUM && pc_dep && pc_hm;
     const bool use_tma = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(heat) & 15u) == 0);
     const bool stage_dep = do_frustum && (((size_t)H * W) % 4 == 0) && ((reinterpret_cast<uintptr_t>(pc_dep) & 15u) == 0);
@@ -1081,6 +1082,7 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     p.n_jobs = n;
     p.do_frustum = do_frustum ? 1 : 0;
     p.pc_dep = pc_dep;
+    p.pc_vel = pc_vel ? pc_vel : pc_dep;
     p.max_pc_dist = max_pc_dist;
     p.pc_hm = pc_hm;
     p.pc_hm_stride = pc_hm_stride > 0 ? pc_hm_stride : 3ll * H * W;

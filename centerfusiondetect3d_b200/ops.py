@@ -43,11 +43,21 @@ def _ptr(t) -> int | None:
     return None if t is None else t.data_ptr()
 
 
-def _map(t, name: str, ndim: int = 4, dtype=torch.float32) -> torch.Tensor:
+def _map(t, name: str, ndim: int = 4, dtype=torch.float32, pinned_ok: bool = False) -> torch.Tensor:
+    """Validates a map.  `pinned_ok`: the tensor is only GATHERED at the K peak pixels (every head but the heat-map),
+    so a contiguous page-locked host tensor is accepted as it is -- under unified addressing the kernels read those few
+    sectors straight out of host memory over PCIe instead of the caller copying the whole head to the device."""
     if not isinstance(t, torch.Tensor):
         raise TypeError("%s must be a torch.Tensor, got %s" % (name, type(t).__name__))
     if not t.is_cuda:
-        raise ValueError("%s must be a CUDA tensor: the fusion stage has no CPU path" % name)
+        if pinned_ok and t.is_pinned() and t.is_contiguous():
+            if t.dtype != dtype:
+                raise TypeError("%s must be %s, got %s" % (name, dtype, t.dtype))
+            if ndim is not None and t.dim() != ndim:
+                raise ValueError("%s must have %d dimensions, got shape %s" % (name, ndim, tuple(t.shape)))
+            return t
+        raise ValueError("%s must be a CUDA tensor%s: the fusion stage has no CPU path" % (
+            name, " or a contiguous pinned host tensor" if pinned_ok else ""))
     if t.dtype != dtype:
         raise TypeError("%s must be %s, got %s" % (name, dtype, t.dtype))
     if ndim is not None and t.dim() != ndim:
@@ -56,6 +66,17 @@ def _map(t, name: str, ndim: int = 4, dtype=torch.float32) -> torch.Tensor:
 
 
 _ws_cache: dict = {}
+_staging_cache: dict = {}
+
+
+def _staging(dev: torch.device, name: str, shape: tuple) -> torch.Tensor:
+    """Per-(device, stream, name, shape) device buffer for inputs a host-buffer caller hands over in pinned memory."""
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream, name, tuple(shape))
+    buf = _staging_cache.get(key)
+    if buf is None:
+        buf = torch.zeros(shape, dtype=torch.float32, device=dev)
+        _staging_cache[key] = buf
+    return buf
 
 
 def _workspace(dev: torch.device, nbytes: int) -> torch.Tensor:
@@ -195,10 +216,10 @@ def frustum_association(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor,
     (pc_hm (B,3,H,W), assoc (B,K) i32 matched pc_dep pixel or -1, thr (B,K), inds (B,K) i64)."""
     heat = _map(_head(output, "heatmap"), "heatmap")
     B, Cc, H, W = heat.shape
-    wh = _map(_head(output, "widthHeight"), "widthHeight")
-    dep = _map(_head(output, "depth"), "depth")
-    dim = _map(_head(output, "dimension"), "dimension")
-    rot = _map(_head(output, "rotation"), "rotation")
+    wh = _map(_head(output, "widthHeight"), "widthHeight", pinned_ok=True)
+    dep = _map(_head(output, "depth"), "depth", pinned_ok=True)
+    dim = _map(_head(output, "dimension"), "dimension", pinned_ok=True)
+    rot = _map(_head(output, "rotation"), "rotation", pinned_ok=True)
     pcd = _map(pc_dep, "pc_dep")
     if pcd.shape != (B, 3, H, W):
         raise NotImplementedError("pc_dep must be (B,3,H,W) [depth, vx, vz]; ONE_HOT_PC is forbidden together with "
@@ -305,7 +326,7 @@ def _decode_structs(output: dict, K: int, keep: list):
         if name == "rotation" and "rotation2" in output:
             key = "rotation2"
         if key in output:
-            t = _map(output[key], key)
+            t = _map(output[key], key, pinned_ok=True)
             if t.shape != (B, _DEC_CH[name], H, W):
                 raise ValueError("%s must be (%d,%d,%d,%d), got %s" % (key, B, _DEC_CH[name], H, W, tuple(t.shape)))
             src[name] = t
@@ -349,13 +370,30 @@ def fusionDecode(outputs, outputSize=(112, 200), K=100, norm2d=False) -> dict:
     return ret
 
 
+def stage_depth_plane(pc_dep_dev: torch.Tensor, pc_dep_host: torch.Tensor) -> None:
+    """Copies plane 0 (depth) of every frame of a pinned host (B,3,H,W) pc_dep into the CUDA tensor `pc_dep_dev`
+    (same shape) with one strided asynchronous copy on the current stream (cf_stage_depth_plane)."""
+    dev_t = _map(pc_dep_dev, "pc_dep_dev")
+    host_t = _map(pc_dep_host, "pc_dep_host", pinned_ok=True)
+    if dev_t is not pc_dep_dev or host_t.is_cuda or dev_t.shape != host_t.shape or dev_t.shape[1] != 3:
+        raise ValueError("stage_depth_plane: contiguous (B,3,H,W) CUDA destination and pinned host source required")
+    B, _, H, W = dev_t.shape
+    _lib.check(_lib.lib().cf_stage_depth_plane(dev_t.data_ptr(), host_t.data_ptr(), B, H, W, _stream(dev_t)))
+
+
 def fusion_stage(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config, outputSize=None, norm2d=False,
-                 decode_output: dict | None = None, sec_feats: torch.Tensor | None = None):
+                 decode_output: dict | None = None, sec_feats: torch.Tensor | None = None,
+                 pc_vel: torch.Tensor | None = None):
     """getPcFrustumHeatmap + fusionDecode with ONE pass over the heat-map (cf_fusion_stage).
 
     `output` holds the first-stage heads (heatmap, widthHeight, depth, dimension, rotation); `decode_output` the dict
     fusionDecode would receive (defaults to `output`, which then typically also carries reg, depth2, rotation2, ...).
     Returns (pc_hm, ret) exactly as the two reference calls would.
+
+    Host-buffer callers: every head except the heat-map, `calib`, and `pc_dep` may be contiguous PINNED host tensors.
+    Heads and the velocity planes of pc_dep are then read in place at the K peak / matched pixels (a few sectors over
+    PCIe instead of a copy of the whole tensor); a pinned `pc_dep` has its depth plane staged to the device here.
+    `pc_vel`: the caller staged plane 0 into the CUDA tensor `pc_dep` itself and passes the pinned original here.
 
     `sec_feats` (row f3): a pre-allocated contiguous (B, C_img + 3, H, W) fp32 buffer, the input of the secondary heads
     (ConcateCombiner, fusionModules.py:18-35: cat([imgFeatures, pc_hm], 1)).  pc_hm is then painted straight into its
@@ -363,14 +401,28 @@ def fusion_stage(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config
     K, max_pc_dist = _cfg_k_dist(config)
     heat = _map(_head(output, "heatmap"), "heatmap")
     B, Cc, H, W = heat.shape
-    wh = _map(_head(output, "widthHeight"), "widthHeight")
-    dep = _map(_head(output, "depth"), "depth")
-    dim = _map(_head(output, "dimension"), "dimension")
-    rot = _map(_head(output, "rotation"), "rotation")
-    pcd = _map(pc_dep, "pc_dep")
+    wh = _map(_head(output, "widthHeight"), "widthHeight", pinned_ok=True)
+    dep = _map(_head(output, "depth"), "depth", pinned_ok=True)
+    dim = _map(_head(output, "dimension"), "dimension", pinned_ok=True)
+    rot = _map(_head(output, "rotation"), "rotation", pinned_ok=True)
+    pcd_vel = None
+    if isinstance(pc_dep, torch.Tensor) and not pc_dep.is_cuda:
+        # host-buffer caller: only the depth plane is read in full -> staged to the device here (stream-ordered copy of
+        # plane 0 into a cached buffer); the velocity planes are read in place at the matched pixels
+        pcd_vel = _map(pc_dep, "pc_dep", pinned_ok=True)
+        if pcd_vel.shape != (B, 3, H, W):
+            raise ValueError("pc_dep must be (B,3,H,W)")
+        pcd = _staging(heat.device, "pc_dep", (B, 3, H, W))
+        stage_depth_plane(pcd, pcd_vel)
+    else:
+        pcd = _map(pc_dep, "pc_dep")
     if pcd.shape != (B, 3, H, W):
         raise ValueError("pc_dep must be (B,3,H,W)")
-    cal = _map(calib, "calib", ndim=None).view(B, 3, 4)
+    if pc_vel is not None:  # explicit split: pc_dep on the device with plane 0 filled, the whole map in pinned memory
+        pcd_vel = _map(pc_vel, "pc_vel", pinned_ok=True)
+        if pcd_vel.shape != (B, 3, H, W):
+            raise ValueError("pc_vel must be (B,3,H,W)")
+    cal = _map(calib, "calib", ndim=None, pinned_ok=True).view(B, 3, 4)
     dec = output if decode_output is None else decode_output
     dec_in = dict(dec)
     dec_in["heatmap"] = heat  # same storage: the ABI requires one heat-map
@@ -391,11 +443,11 @@ def fusion_stage(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config
         pc_hm = sec_feats[:, sec_feats.shape[1] - 3:]
         stride = sec_feats.shape[1] * H * W
     ws, wsn = _stage_ws(heat.device, B, Cc, H, W, K)
-    _lib.check(_lib.lib().cf_fusion_stage_strided(heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
-                                                  rot.data_ptr(), pcd.data_ptr(), cal.data_ptr(), B, Cc, H, W, K,
-                                                  max_pc_dist, pc_hm.data_ptr(), stride, None, None, None,
-                                                  C.byref(heads), int(outputSize[0]), int(outputSize[1]),
-                                                  int(bool(norm2d)), C.byref(out), ws.data_ptr(), wsn, _stream(heat)))
+    _lib.check(_lib.lib().cf_fusion_stage_split(heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
+                                                rot.data_ptr(), pcd.data_ptr(), _ptr(pcd_vel), cal.data_ptr(), B, Cc, H, W,
+                                                K, max_pc_dist, pc_hm.data_ptr(), stride, None, None, None,
+                                                C.byref(heads), int(outputSize[0]), int(outputSize[1]),
+                                                int(bool(norm2d)), C.byref(out), ws.data_ptr(), wsn, _stream(heat)))
     return pc_hm, ret
 
 

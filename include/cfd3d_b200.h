@@ -142,6 +142,29 @@ CF_API int cf_fusion_stage_strided(const float* heat, const float* wh, const flo
                                    float* thr, int64_t* inds, const cf_decode_heads_t* dec_heads, int out_h, int out_w,
                                    int norm2d, const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- host-buffer callers: velocities read in place ---------------------------------------------------------------
+ * cf_fusion_stage_strided with the radar map split over two memories.  The kernels read plane 0 (depth) of pc_dep in
+ * full but planes 1, 2 (the velocities) only at the <= K matched pixels of a frame, and every head except the heat-map
+ * only at the K peak pixels.  A caller whose inputs live in HOST memory therefore copies just the heat-map, plane 0 of
+ * pc_dep and calib to the device and passes
+ *   - pc_dep:      DEVICE (B,3,H,W) buffer of which only plane 0 of every frame needs to be filled,
+ *   - pc_dep_vel:  the complete (B,3,H,W) tensor in page-locked, device-mapped HOST memory (cudaHostAlloc /
+ *                  cudaHostRegister; under unified addressing the host pointer itself), or NULL (= pc_dep),
+ *   - wh, depth, dim, rot and the decode heads: page-locked host pointers as well, if the caller wishes.
+ * Pageable host memory is not readable by the device: such pointers fault in the kernel.  Results are identical to
+ * cf_fusion_stage_strided (tests/test_gpu_parity.py::test_pinned_host_heads_read_in_place). */
+CF_API int cf_fusion_stage_split(const float* heat, const float* wh, const float* depth, const float* dim,
+                                 const float* rot, const float* pc_dep, const float* pc_dep_vel, const float* calib, int B,
+                                 int C, int H, int W, int K, float max_pc_dist, float* pc_hm, int64_t pc_hm_batch_stride,
+                                 int32_t* assoc, float* thr, int64_t* inds, const cf_decode_heads_t* dec_heads, int out_h,
+                                 int out_w, int norm2d, const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes,
+                                 void* stream);
+
+/* Plane 0 (depth) of every frame of a host (B,3,H,W) pc_dep into the same position of a device (B,3,H,W) buffer: one
+ * strided asynchronous copy on `stream` (the staging step of cf_fusion_stage_split).  Page-locked host memory makes
+ * it asynchronous. */
+CF_API int cf_stage_depth_plane(float* pc_dep_dev, const float* pc_dep_host, int B, int H, int W, void* stream);
+
 /* ---- f2  stable depth sort of the radar points on the device --------------------------------------------------
  * The host-side np.argsort(depth) of src/lib/dataset/datasets/nuscenes.py:195-197 / src/lib/detector.py:281 (default
  * kind: not stable, so the reference's order among equal depths is unspecified) with the order fixed to

@@ -216,6 +216,35 @@ def test_paint_into_combiner_input(ops, oracle):
     eq(npy(sec[:, 64:]), hm_o, "pc_hm vs oracle")
 
 
+def test_pinned_host_heads_read_in_place(ops, oracle):
+    """Host-buffer callers: the gather-only heads may stay in pinned host memory (read in place at the K peak pixels);
+    results are bit-identical to the all-device call and to the oracle."""
+    wl = syn.WORKLOADS["cfg2"]
+    B = 3
+    inp = make_case(wl, B)
+    cfg = type("Cfg", (), {"MODEL": type("M", (), {"K": wl.K})(), "DATASET": type("D", (), {"MAX_PC_DIST": wl.max_pc_dist})()})()
+    pc_hm, ret = ops.fusion_stage(to_cuda(inp, DEC_KEYS, DEV), cu(inp["pc_dep"]), cu(inp["calib"]), cfg)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()  # noqa: E731
+    mk = lambda: {k: (cu(inp[k]) if k == "heatmap" else pin(inp[k])) for k in DEC_KEYS}  # noqa: E731 (calls rename keys)
+    mixed = mk()
+    pc_hm2, ret2 = ops.fusion_stage(mk(), pin(inp["pc_dep"]), pin(inp["calib"]), cfg)  # depth plane staged by ops
+    eq(npy(pc_hm2), npy(pc_hm), "pc_hm")
+    staged = torch.zeros_like(cu(inp["pc_dep"]))
+    staged[:, 0].copy_(cu(inp["pc_dep"])[:, 0])
+    pc_hm3, _ = ops.fusion_stage(mk(), staged, cu(inp["calib"]), cfg, pc_vel=pin(inp["pc_dep"]))
+    eq(npy(pc_hm3), npy(pc_hm), "pc_hm, caller-staged depth plane")
+    assert set(ret2) == set(ret)
+    for k in ret:
+        eq(npy(ret2[k]), npy(ret[k]), k)
+    hm_o = oracle.frustum_pc_hm(inp["heatmap"], inp["widthHeight"], inp["depth"], inp["dimension"], inp["rotation"],
+                                inp["pc_dep"], inp["calib"], wl.K, wl.max_pc_dist)[0]
+    eq(npy(pc_hm2), hm_o, "pc_hm vs oracle")
+    with pytest.raises(ValueError):  # pageable host memory is not readable by the device
+        bad = dict(mixed)
+        bad["depth"] = torch.from_numpy(np.ascontiguousarray(inp["depth"]))
+        ops.fusion_stage(bad, cu(inp["pc_dep"]), cu(inp["calib"]), cfg)
+
+
 def test_radar_sort_on_device(ops, oracle):
     """f2: the device sort is np.argsort(kind="stable") on depth (ties keep source order, padding rows stay), and the
     pillar expansion of device-sorted points equals the one of host-sorted points."""
