@@ -140,7 +140,7 @@ def test_golden_decode_variants(ops):
 # ------------------------------------------------------------------------------------------------
 # 2. oracle differential at BASELINE.json shapes
 # ------------------------------------------------------------------------------------------------
-def _check_stage(ops, oracle, wl, inp, B):
+def _check_stage(ops, oracle, wl, inp, B, need_matches=True):
     fwd = to_cuda(inp, FWD_KEYS, DEV)
     pc_dep = cu(inp["pc_dep"])
     calib = cu(inp["calib"])
@@ -153,7 +153,7 @@ def _check_stage(ops, oracle, wl, inp, B):
     np.testing.assert_allclose(npy(thr), thr_o, rtol=RTOL_THR_ORACLE, atol=0)
     eq(npy(assoc), assoc_o, "association indices")
     eq(npy(pc_hm), hm_o, "pc_hm")
-    assert (assoc_o >= 0).sum() >= B  # the case exercises real matches
+    assert not need_matches or (assoc_o >= 0).sum() >= B  # the case exercises real matches
     # D
     dec_np = {k: inp[k] for k in DEC_KEYS}
     ret_o = oracle.fusion_decode(dec_np, (wl.H, wl.W), wl.K)
@@ -404,6 +404,20 @@ def test_ties_follow_the_documented_total_order(ops, oracle):
             r = ops.topk(cu(heat), K, apply_nms=apply_nms)
             for a, b, nm in zip(r, r_o, ("scores", "inds", "classes", "ys", "xs")):
                 eq(npy(a), b, "K=%d %s nms=%s" % (K, nm, apply_nms))
+
+
+@pytest.mark.parametrize("levels", [4, 64])
+def test_dense_ties_at_reference_size(ops, oracle, levels):
+    """A quantised heat-map at the reference map size: thousands of pixels share the K-th value, so the bound of the
+    stage kernel admits far more candidates than its fast paths hold -- the flagged-group list, the work list and the
+    survivor lists overflow and the exact fall-backs (block scan, in-place append, radix select over the list or the
+    frame) must give the oracle's total order all the same.  The whole stage is compared, not only the top-K."""
+    wl = syn.WORKLOADS["cfg2"]
+    B = 2
+    inp = make_case(wl, B)
+    rng = np.random.default_rng(levels)
+    inp["heatmap"] = (rng.integers(0, levels, size=inp["heatmap"].shape) / float(levels)).astype(np.float32)
+    _check_stage(ops, oracle, wl, inp, B, need_matches=False)  # (the winners of a tie sit wherever the index order puts them)
 
 
 def test_special_values(ops, oracle):
