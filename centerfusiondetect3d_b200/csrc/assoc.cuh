@@ -24,12 +24,21 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
 // the first minimum in row-major ROI order.  Lanes run over columns, rows are unrolled: independent loads, no
 // division.
 // U = row loads in flight per thread: 8 hides shared-memory latency, global (L2) reads want more.
-template <int U = 8>
-__device__ __forceinline__ unsigned long long roi_scan(const float* dep, int H, int W, float x1, float y1,
-                                                       float x2, float y2, float depth, float thr, int t, int NT) {
-    int ya, yb, xa, xb;
+// Three pieces: roi_bounds (the box -> slices), roi_scan_box (the scan of given slices), roi_scan (both).
+
+// ROI of a box: rows [ya,yb) x cols [xa,xb) (python slices of floor / ceil + 1, pointcloud.py:424-433)
+__device__ __forceinline__ void roi_bounds(int H, int W, float x1, float y1, float x2, float y2, int& ya, int& yb, int& xa,
+                                           int& xb) {
     pyslice((long long)floorf(y1), (long long)ceilf(y2) + 1, H, ya, yb);
     pyslice((long long)floorf(x1), (long long)ceilf(x2) + 1, W, xa, xb);
+}
+
+// the scan proper over a given ROI.  W32: the caller is one warp (t < 32, NT == 32) -- the thread -> (row phase, column)
+// map then avoids the two integer divisions (this code runs once per detection on a single warp: it is priced by its
+// instruction count, and a division is ~40 of them).
+template <int U, bool W32>
+__device__ __forceinline__ unsigned long long roi_scan_box(const float* dep, int W, int ya, int yb, int xa, int xb,
+                                                           float depth, float thr, int t, int NT) {
     const float hi = __fadd_rn(depth, thr);
     float lo = __fsub_rn(depth, thr);
     if (!(lo > 0.0f)) lo = 0.0f;  // python max(0, t)
@@ -37,9 +46,19 @@ __device__ __forceinline__ unsigned long long roi_scan(const float* dep, int H, 
     if (ya >= yb || xa >= xb) return best;
     const int w = xb - xa;
     // thread t -> (row phase, column): columns fastest so that a warp reads contiguous runs
-    const int cols = w < NT ? w : NT;       // threads along x
-    const int rows_par = NT / cols;         // rows processed side by side
-    const int ty = t / cols, tx = t - ty * cols;
+    const int cols = w < NT ? w : NT;  // threads along x
+    int rows_par, ty;                  // rows processed side by side, this thread's row phase
+    if (W32) {
+        // floor(32 / cols) and floor(t / cols) for cols in [1,32], t in [0,32): the +0.5 keeps the approximate
+        // quotient on the right side of every integer (no multiple of cols lies in (32, 32.5] or (t, t + 0.5])
+        const float inv = __fdividef(1.0f, (float)cols);
+        rows_par = (int)(32.5f * inv);
+        ty = (int)(((float)t + 0.5f) * inv);
+    } else {
+        rows_par = NT / cols;
+        ty = t / cols;
+    }
+    const int tx = t - ty * cols;
     if (ty >= rows_par) return best;
     for (int xx = xa + tx; xx < xb; xx += cols) {
         for (int y0 = ya + ty; y0 < yb; y0 += U * rows_par) {
@@ -63,6 +82,23 @@ __device__ __forceinline__ unsigned long long roi_scan(const float* dep, int H, 
         }
     }
     return best;
+}
+
+template <int U = 8>
+__device__ __forceinline__ unsigned long long roi_scan(const float* dep, int H, int W, float x1, float y1,
+                                                       float x2, float y2, float depth, float thr, int t, int NT) {
+    int ya, yb, xa, xb;
+    roi_bounds(H, W, x1, y1, x2, y2, ya, yb, xa, xb);
+    return roi_scan_box<U, false>(dep, W, ya, yb, xa, xb, depth, thr, t, NT);
+}
+
+// warp minimum of roi_scan keys with two redux rounds instead of five 64-bit shuffle rounds: smallest depth word first,
+// then the smallest pixel among the lanes that hold it
+__device__ __forceinline__ unsigned long long warp_min_key(unsigned long long v) {
+    const uint32_t hi = (uint32_t)(v >> 32), lo = (uint32_t)v;
+    const uint32_t mh = __reduce_min_sync(FULL, hi);
+    const uint32_t ml = __reduce_min_sync(FULL, hi == mh ? lo : 0xffffffffu);
+    return ((unsigned long long)mh << 32) | ml;
 }
 
 // paint window of cvtPcDepthToHeatmap (pointcloud.py:468-481): rows h_min:h_max+1, cols w_min:w_max+1+1

@@ -260,7 +260,8 @@ __device__ __forceinline__ float frustum_thr_quad(float ay, float ax, float rot1
 // Executed by the thread group [0, T) given as (tid, T): whole warps.
 __device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const MergeJob& jb, int b,
                                                  const unsigned long long* comps, int first, int stride, int kl0, int nb,
-                                                 const float* gath, DetParam* sdet, const float* cal, int tid, int T) {
+                                                 const float* gath, DetParam* sdet, short4* sroi, const float* cal,
+                                                 int tid, int T) {
     const int K = p.K, W = p.W, HWi = p.H * p.W;
     const int j = tid & 3;
     // cal = {calib[0,0], calib[0,2]} of the frame where the caller fetched them ahead of time (the row is cold in DRAM)
@@ -294,6 +295,11 @@ __device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const Mer
             box_of(q, ind, d);
             det_set_window(d, p.H, W);
             *reinterpret_cast<short4*>(&sdet[kl0 + q].ra) = make_short4(d.ra, d.rb, d.ca, d.cb);
+            if (sroi) {  // and the ROI of the association's scan (ya, yb, xa, xb)
+                int ya, yb, xa, xb;
+                roi_bounds(p.H, W, d.x1, d.y1, d.x2, d.y2, ya, yb, xa, xb);
+                sroi[kl0 + q] = make_short4((short)ya, (short)yb, (short)xa, (short)xb);
+            }
         }
         return;
     }
@@ -322,6 +328,11 @@ __device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const Mer
             if (!side) {
                 det_set_window(d, p.H, W);
                 *reinterpret_cast<short4*>(&sdet[kl].ra) = make_short4(d.ra, d.rb, d.ca, d.cb);
+                if (sroi) {
+                    int ya, yb, xa, xb;
+                    roi_bounds(p.H, W, d.x1, d.y1, d.x2, d.y2, ya, yb, xa, xb);
+                    sroi[kl] = make_short4((short)ya, (short)yb, (short)xa, (short)xb);
+                }
             }
             const size_t o = (size_t)b * K + k;
             if (jb.fo.thr) jb.fo.thr[o] = d.thr;
@@ -414,7 +425,7 @@ __device__ __forceinline__ void copy_head(const float* head, float* out, int nch
 template <int T>
 __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int b, int first, int stride, int n_local,
                                            const unsigned long long* xs_comp, float* gath, int GB, DetParam* sdet,
-                                           const float* cal) {
+                                           short4* sroi, const float* cal) {
     const int K = p.K, HWi = p.H * p.W;
     for (int kl0 = 0; kl0 < n_local; kl0 += GB) {
         const int nb = min(GB, n_local - kl0);
@@ -453,7 +464,7 @@ __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int
                     if (jb.topk.xs) jb.topk.xs[o] = x;
                 }
             } else if (jb.epilogue == EPI_FRUSTUM) {
-                epilogue_frustum(p, jb, b, comps, first, stride, kl0, nb, g, sdet, cal, gt, half);
+                epilogue_frustum(p, jb, b, comps, first, stride, kl0, nb, g, sdet, sroi, cal, gt, half);
             } else if (jb.epilogue == EPI_DECODE) {
                 epilogue_decode(p, jb, b, comps, first, stride, kl0, nb, g, gt, half);
                 copy_head(jb.dec.heads.rot, jb.dec.out.rot, 8, DS_ROT, b, K, first, stride, kl0, nb, g, gt, half);

@@ -790,7 +790,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         const int n_local = (K - (int)rank + (int)cs - 1) / (int)cs;
         DetParam* sdet = reinterpret_cast<DetParam*>(smem + p.off_det);
         merge_tail<ST>(mp, p.n_jobs, b, (int)rank, (int)cs, n_local, xs_comp, reinterpret_cast<float*>(smem + p.off_gath),
-                       p.GB, sdet, p.do_frustum ? s_cal : nullptr);
+                       p.GB, sdet, p.do_frustum ? reinterpret_cast<short4*>(smem + p.off_best) : nullptr,
+                       p.do_frustum ? s_cal : nullptr);
         PROF(24);
         if (!p.do_frustum) continue;
 
@@ -804,12 +805,22 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 mbar_wait(&dep_bar, (uint32_t)it & 1u);
                 dep0 = reinterpret_cast<const float*>(smem + p.dep_off);
             }
+            PROF(30);
+            // (the ROI bounds of detection kl wait in sbest[kl], left there by the epilogue's idle warps: this loop runs
+            // once per detection on one warp and is priced by its instruction count)
             for (int kl = warp; kl < n_local; kl += SNW) {
-                const DetParam d = sdet[kl];
-                const unsigned long long best = warp_min_u64(
-                    p.dep_off >= 0 ? roi_scan<8>(dep0, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32)
-                                   : roi_scan<24>(dep0, H, W, d.x1, d.y1, d.x2, d.y2, d.depth, d.thr, lane, 32));
+                const short4 roi = *reinterpret_cast<const short4*>(&sbest[kl]);
+                const float2 dt = *reinterpret_cast<const float2*>(&sdet[kl].depth);
+                __syncwarp();
+                const unsigned long long best = warp_min_key(
+                    p.dep_off >= 0 ? roi_scan_box<8, true>(dep0, W, roi.x, roi.y, roi.z, roi.w, dt.x, dt.y, lane, 32)
+                                   : roi_scan_box<24, true>(dep0, W, roi.x, roi.y, roi.z, roi.w, dt.x, dt.y, lane, 32));
                 if (lane == 0) sbest[kl] = best;
+                if (p.prof && tid == 0 && blockIdx.x < 1024 && kl == 0) {
+                    long long t_;
+                    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"((uint32_t)best) : "memory");
+                    g_prof[blockIdx.x * PROF_PTS + 31] = t_;
+                }
             }
             PROF(25);
             __syncthreads();

@@ -54,6 +54,7 @@ for rep in range(6):
         print("   %-14s %7.2f %7.2f %7.2f" % (nm, dt[:, i].min(), dt[:, i].mean(), dt[:, i].max()))
     az = np.diff(buf[:, [24, 25, 26, 9]], axis=1) / 1.965e3
     print("   assoc finalize (thread 0): record ready %.2f  broadcast %.2f" % tuple((np.diff(buf[:, [26, 27, 9]], axis=1) / 1.965e3).mean(axis=0)))
+    print("   assoc scans (warp 0): wait for the depth plane %.2f  first ROI %.2f  rest %.2f" % tuple((np.diff(buf[:, [24, 30, 31, 25]], axis=1) / 1.965e3).mean(axis=0)))
     print("   assoc: scans (warp 0) %.2f  sync %.2f  finalize+broadcast %.2f" % tuple(az.mean(axis=0)))
     ex = buf[:, [0, 15, 1]], buf[:, [4, 12, 13, 14, 5]]
     mg = np.diff(buf[:, 16:19], axis=1) / 1.965e3
@@ -65,6 +66,5 @@ for rep in range(6):
     print("   passB: barrier waits %.2f flags %.2f sync %.2f" % tuple((np.diff(buf[:, [4, 30, 31, 29]], axis=1) / 1.965e3).mean(axis=0)))
     print("   epilogue (thread 0): operands %.2f  trig %.2f  rest %.2f  wait for the other half %.2f" % tuple((np.diff(buf[:, [19, 21, 22, 23, 20]], axis=1) / 1.965e3).mean(axis=0)))
     print("   passB flag+sync %.2f; flagged groups per CTA:" % ((buf[:, 29] - buf[:, 4]).mean() / 1.965e3), " ".join(str(x) for x in buf[:, 27]))
-    print("   candidates per CTA:", " ".join(str(x) for x in buf[:, 28]))
     for r in range(min(CS, 4)):
         print("   rank %d mean:" % r, " ".join("%6.2f" % x for x in dt[r::CS].mean(axis=0)))
