@@ -98,7 +98,7 @@ __device__ __forceinline__ void cl_st(uint32_t raddr, uint32_t v) {
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // development aid (CFD3D_PROF=1): per-CTA clock64 stamps at the phase boundaries of the last frame a CTA processed
-constexpr int PROF_PTS = 32;
+constexpr int PROF_PTS = 48;
 __device__ long long g_prof[1024 * PROF_PTS];
 #define CF_MERGE_PROF(i)                                                                                  \
     do {                                                                                                  \
@@ -710,33 +710,56 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             PROF(12);
             __syncthreads();
             PROF(13);
-            // B2: one candidate per thread.  Survivors are counted per CTA (shared-memory atomics), the frame's lists
+            // B2: candidates side by side, one per thread and trip.  Survivors are counted per CTA (shared-memory atomics), the frame's lists
             // see ONE reservation per (CTA, list): same-address global atomics serialise at a few per microsecond.
             const uint32_t n_wl = min(s_nwl, wl_cap);
             if (p.prof && tid == 0 && blockIdx.x < 1024) {
                 g_prof[blockIdx.x * PROF_PTS + 27] = (long long)s_nfl;
                 g_prof[blockIdx.x * PROF_PTS + 28] = (long long)s_nwl;
             }
-            for (uint32_t c0 = 0; c0 < n_wl; c0 += ST) {
-                const uint32_t c = c0 + (uint32_t)tid;
-                float v = 0.0f;
-                uint32_t gi = 0u;
-                bool sraw = false, snms = false;
+            // (up to BU candidates per thread in one trip: a CTA that parked more than 512 pays the counting, the two
+            // barriers and the round trip of the reservation once -- such a CTA sets the pace of its whole cluster)
+            constexpr int BU = 3;
+            for (uint32_t c0 = 0; c0 < n_wl; c0 += ST * BU) {
+                unsigned long long comp[BU];
+                uint32_t off[BU], flags = 0u, tot0 = 0u, tot1 = 0u;  // off: position among the warp's survivors (raw | nms << 16)
                 if (tid < 2) s_cnt[tid] = 0u;
                 __syncthreads();
-                if (c < n_wl) cand_eval(resident ? (uint32_t)wl16[c] : wl[c], v, gi, sraw, snms);
-                const unsigned long long comp = make_comp(f2key(v), gi);
-                const uint32_t bal0 = __ballot_sync(FULL, sraw), bal1 = __ballot_sync(FULL, snms);
+#pragma unroll
+                for (int u = 0; u < BU; ++u) {
+                    const uint32_t c = c0 + (uint32_t)(u * ST + tid);
+                    float v = 0.0f;
+                    uint32_t gi = 0u;
+                    bool sraw = false, snms = false;
+                    if (c0 + (uint32_t)(u * ST) < n_wl) {  // (uniform: trips beyond the list cost nothing)
+                        if (c < n_wl) cand_eval(resident ? (uint32_t)wl16[c] : wl[c], v, gi, sraw, snms);
+                        const uint32_t bal0 = __ballot_sync(FULL, sraw), bal1 = __ballot_sync(FULL, snms);
+                        off[u] = (tot0 + (uint32_t)__popc(bal0 & lanemask_lt())) |
+                                 ((tot1 + (uint32_t)__popc(bal1 & lanemask_lt())) << 16);
+                        tot0 += (uint32_t)__popc(bal0);
+                        tot1 += (uint32_t)__popc(bal1);
+                    } else {
+                        off[u] = 0u;
+                    }
+                    comp[u] = make_comp(f2key(v), gi);
+                    flags |= (sraw ? 1u : 0u) << (2 * u) | (snms ? 2u : 0u) << (2 * u);
+                }
                 uint32_t lb0 = 0u, lb1 = 0u;
-                if (bal0 && lane == 0) lb0 = atomicAdd(&s_cnt[0], (uint32_t)__popc(bal0));
-                if (bal1 && lane == 0) lb1 = atomicAdd(&s_cnt[1], (uint32_t)__popc(bal1));
-                lb0 = __shfl_sync(FULL, lb0, 0) + (uint32_t)__popc(bal0 & lanemask_lt());
-                lb1 = __shfl_sync(FULL, lb1, 0) + (uint32_t)__popc(bal1 & lanemask_lt());
+                if (tot0 && lane == 0) lb0 = atomicAdd(&s_cnt[0], tot0);
+                if (tot1 && lane == 0) lb1 = atomicAdd(&s_cnt[1], tot1);
+                lb0 = __shfl_sync(FULL, lb0, 0);
+                lb1 = __shfl_sync(FULL, lb1, 0);
                 __syncthreads();
                 if (tid < 2 && s_cnt[tid]) s_base[tid] = atomicAdd(tid ? ctr_nms : ctr_raw, s_cnt[tid]);
                 __syncthreads();
-                if (sraw && s_base[0] + lb0 < (uint32_t)CAND_CAP) cand_raw[s_base[0] + lb0] = comp;
-                if (snms && s_base[1] + lb1 < (uint32_t)CAND_CAP) cand_nms[s_base[1] + lb1] = comp;
+                lb0 += s_base[0];
+                lb1 += s_base[1];
+#pragma unroll
+                for (int u = 0; u < BU; ++u) {
+                    const uint32_t s0 = lb0 + (off[u] & 0xffffu), s1 = lb1 + (off[u] >> 16);
+                    if ((flags >> (2 * u) & 1u) && s0 < (uint32_t)CAND_CAP) cand_raw[s0] = comp[u];
+                    if ((flags >> (2 * u) & 2u) && s1 < (uint32_t)CAND_CAP) cand_nms[s1] = comp[u];
+                }
             }
             PROF(14);
             fence_async_smem();
@@ -805,7 +828,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 mbar_wait(&dep_bar, (uint32_t)it & 1u);
                 dep0 = reinterpret_cast<const float*>(smem + p.dep_off);
             }
-            PROF(30);
+            PROF(32);
             // (the ROI bounds of detection kl wait in sbest[kl], left there by the epilogue's idle warps: this loop runs
             // once per detection on one warp and is priced by its instruction count)
             for (int kl = warp; kl < n_local; kl += SNW) {
@@ -819,7 +842,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 if (p.prof && tid == 0 && blockIdx.x < 1024 && kl == 0) {
                     long long t_;
                     asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"((uint32_t)best) : "memory");
-                    g_prof[blockIdx.x * PROF_PTS + 31] = t_;
+                    g_prof[blockIdx.x * PROF_PTS + 33] = t_;
                 }
             }
             PROF(25);
@@ -835,7 +858,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 if (p.prof && tid == 0 && blockIdx.x < 1024) {
                     long long t_;
                     asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"(rw[0] ^ rw[1] ^ rw[2] ^ rw[3] ^ rw[4]) : "memory");
-                    g_prof[blockIdx.x * PROF_PTS + 27] = t_;
+                    g_prof[blockIdx.x * PROF_PTS + 34] = t_;
                 }
                 const uint32_t dst = smem_u32(srecs + k);
                 for (uint32_t c = 0; c < cs; ++c) {

@@ -45,7 +45,7 @@ for rep in range(6):
     e1.record()
     torch.cuda.synchronize()
     n_cta = min(B, 148 // CS) * CS
-    buf = np.zeros((n_cta, 32), dtype=np.int64)
+    buf = np.zeros((n_cta, 48), dtype=np.int64)
     L.cf_debug_read_prof(buf.ctypes.data, n_cta)
     dt = np.diff(buf[:, order], axis=1) / 1.965e3  # us at 1965 MHz
     print("rep %d  call %.1f us   per-phase us over %d CTAs (min / mean / max); total mean %.1f" % (
@@ -53,8 +53,8 @@ for rep in range(6):
     for i, nm in enumerate(names):
         print("   %-14s %7.2f %7.2f %7.2f" % (nm, dt[:, i].min(), dt[:, i].mean(), dt[:, i].max()))
     az = np.diff(buf[:, [24, 25, 26, 9]], axis=1) / 1.965e3
-    print("   assoc finalize (thread 0): record ready %.2f  broadcast %.2f" % tuple((np.diff(buf[:, [26, 27, 9]], axis=1) / 1.965e3).mean(axis=0)))
-    print("   assoc scans (warp 0): wait for the depth plane %.2f  first ROI %.2f  rest %.2f" % tuple((np.diff(buf[:, [24, 30, 31, 25]], axis=1) / 1.965e3).mean(axis=0)))
+    print("   assoc finalize (thread 0): record ready %.2f  broadcast %.2f" % tuple((np.diff(buf[:, [26, 34, 9]], axis=1) / 1.965e3).mean(axis=0)))
+    print("   assoc scans (warp 0): wait for the depth plane %.2f  first ROI %.2f  rest %.2f" % tuple((np.diff(buf[:, [24, 32, 33, 25]], axis=1) / 1.965e3).mean(axis=0)))
     print("   assoc: scans (warp 0) %.2f  sync %.2f  finalize+broadcast %.2f" % tuple(az.mean(axis=0)))
     ex = buf[:, [0, 15, 1]], buf[:, [4, 12, 13, 14, 5]]
     mg = np.diff(buf[:, 16:19], axis=1) / 1.965e3
@@ -65,6 +65,6 @@ for rep in range(6):
     print("   passB loop per CTA (warp 0):", " ".join("%.0f" % x for x in (buf[:, 12] - buf[:, 4]) / 1.965e3))
     print("   passB: barrier waits %.2f flags %.2f sync %.2f" % tuple((np.diff(buf[:, [4, 30, 31, 29]], axis=1) / 1.965e3).mean(axis=0)))
     print("   epilogue (thread 0): operands %.2f  trig %.2f  rest %.2f  wait for the other half %.2f" % tuple((np.diff(buf[:, [19, 21, 22, 23, 20]], axis=1) / 1.965e3).mean(axis=0)))
-    print("   passB flag+sync %.2f; flagged groups per CTA:" % ((buf[:, 29] - buf[:, 4]).mean() / 1.965e3), " ".join(str(x) for x in buf[:, 27]))
+    print("   passB flag+sync %.2f; flagged groups per CTA:" % ((buf[:, 29] - buf[:, 4]).mean() / 1.965e3), " ".join(str(x) for x in buf[:, 27]), "\n   candidates per CTA:", " ".join(str(x) for x in buf[:, 28]))
     for r in range(min(CS, 4)):
         print("   rank %d mean:" % r, " ".join("%6.2f" % x for x in dt[r::CS].mean(axis=0)))
