@@ -84,6 +84,56 @@ __device__ __forceinline__ unsigned long long roi_scan_box(const float* dep, int
     return best;
 }
 
+// One warp, four pixels per load: lanes run over column QUADS (float4 loads; W % 4 == 0 and a 16-byte aligned plane
+// required), rows unrolled.  A wide ROI costs a quarter of the load batches of roi_scan_box -- the big boxes set the pace
+// of the association (the cluster waits for the slowest warp of its slowest CTA).  Columns of the first / last quad
+// outside [xa, xb) are masked; the minimum key is the same as roi_scan_box's whatever the visiting order.
+template <int U>
+__device__ __forceinline__ unsigned long long roi_scan_box4(const float* dep, int W, int ya, int yb, int xa, int xb,
+                                                            float depth, float thr, int lane) {
+    const float hi = __fadd_rn(depth, thr);
+    float lo = __fsub_rn(depth, thr);
+    if (!(lo > 0.0f)) lo = 0.0f;  // python max(0, t)
+    unsigned long long best = ~0ull;
+    if (ya >= yb || xa >= xb) return best;
+    const int qa = xa >> 2, qb = (xb + 3) >> 2;  // column quads [qa, qb)
+    const int nq = qb - qa;
+    const int cols = nq < 32 ? nq : 32;
+    const float inv = __fdividef(1.0f, (float)cols);  // see roi_scan_box
+    const int rows_par = (int)(32.5f * inv);
+    const int ty = (int)(((float)lane + 0.5f) * inv), tx = lane - ty * cols;
+    if (ty >= rows_par) return best;
+    for (int q = qa + tx; q < qb; q += cols) {
+        const int x0 = 4 * q;
+        uint32_t mask = 0u;  // columns of this quad inside the ROI
+#pragma unroll
+        for (int j = 0; j < 4; ++j) mask |= (x0 + j >= xa && x0 + j < xb) ? (1u << j) : 0u;
+        for (int y0 = ya + ty; y0 < yb; y0 += U * rows_par) {
+            float4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int yy = y0 + u * rows_par;
+                const int yc = yy < yb ? yy : ya;  // clamped: the load is unconditional
+                v[u] = *reinterpret_cast<const float4*>(dep + (size_t)yc * W + x0);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int yy = y0 + u * rows_par;
+                const float c4[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (c4[j] != 0.0f && c4[j] < hi && c4[j] > lo && yy < yb && (mask >> j & 1u)) {
+                        const unsigned long long key = ((unsigned long long)__float_as_uint(c4[j]) << 32) |
+                                                       (unsigned long long)(uint32_t)(yy * W + x0 + j);
+                        best = key < best ? key : best;
+                    }
+                }
+            }
+        }
+    }
+    return best;
+}
+
 template <int U = 8>
 __device__ __forceinline__ unsigned long long roi_scan(const float* dep, int H, int W, float x1, float y1,
                                                        float x2, float y2, float depth, float thr, int t, int NT) {
@@ -126,20 +176,18 @@ __device__ __forceinline__ void det_set_window(DetParam& d, int H, int W) {
 
 // The matched pixel of one detection -> paint record + association index (one thread).  d carries its paint window.  best = the reduced roi_scan
 // key (~0 = no radar pixel in range), dep = the frame's pc_dep (3,H,W) in global memory (velocity channels).
-__device__ __forceinline__ PaintRec assoc_finalize(unsigned long long best, const float* dep, int H, int W,
-                                                   const DetParam& d, float max_pc_dist, int32_t* assoc_out) {
-    const size_t HW = (size_t)H * W;
+__device__ __forceinline__ PaintRec assoc_record(unsigned long long best, float v1, float v2, const DetParam& d,
+                                                 float max_pc_dist, int32_t* assoc_out) {
     PaintRec r;
     r.ra = r.rb = r.ca = r.cb = 0;
     r.v0 = r.v1 = r.v2 = 0.0f;
     r.pad_ = r.pad2_ = 0;
     int32_t a = -1;
     if (best != ~0ull) {
-        const uint32_t mp = (uint32_t)best;
-        a = (int32_t)mp;
+        a = (int32_t)(uint32_t)best;
         r.v0 = __fdiv_rn(__uint_as_float((uint32_t)(best >> 32)), max_pc_dist);  // :462-466
-        r.v1 = dep[HW + mp];
-        r.v2 = dep[2 * HW + mp];
+        r.v1 = v1;
+        r.v2 = v2;
         r.ra = d.ra;
         r.rb = d.rb;
         r.ca = d.ca;
@@ -147,6 +195,18 @@ __device__ __forceinline__ PaintRec assoc_finalize(unsigned long long best, cons
     }
     if (assoc_out) *assoc_out = a;
     return r;
+}
+// ... with the velocity reads (dep = the frame's pc_dep (3,H,W), planes 1 and 2)
+__device__ __forceinline__ PaintRec assoc_finalize(unsigned long long best, const float* dep, int H, int W,
+                                                   const DetParam& d, float max_pc_dist, int32_t* assoc_out) {
+    const size_t HW = (size_t)H * W;
+    float v1 = 0.0f, v2 = 0.0f;
+    if (best != ~0ull) {
+        const uint32_t mp = (uint32_t)best;
+        v1 = dep[HW + mp];
+        v2 = dep[2 * HW + mp];
+    }
+    return assoc_record(best, v1, v2, d, max_pc_dist, assoc_out);
 }
 
 }  // namespace cf

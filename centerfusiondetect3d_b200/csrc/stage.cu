@@ -764,6 +764,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             PROF(14);
             fence_async_smem();
             __syncthreads();
+            if (tid == 0) s_nfl = 0u;  // becomes the association's work counter
             // the slot area is free from here on: the merge parameters move in (visible after the cluster barrier)
             if (tid < (int)(sizeof(MergeParams) / 4)) reinterpret_cast<uint32_t*>(smem + p.off_par)[tid] = par_word;
             // Stage the radar depth plane for the association.
@@ -831,18 +832,38 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             PROF(32);
             // (the ROI bounds of detection kl wait in sbest[kl], left there by the epilogue's idle warps: this loop runs
             // once per detection on one warp and is priced by its instruction count)
-            for (int kl = warp; kl < n_local; kl += SNW) {
-                const short4 roi = *reinterpret_cast<const short4*>(&sbest[kl]);
-                const float2 dt = *reinterpret_cast<const float2*>(&sdet[kl].depth);
-                __syncwarp();
-                const unsigned long long best = warp_min_key(
-                    p.dep_off >= 0 ? roi_scan_box<8, true>(dep0, W, roi.x, roi.y, roi.z, roi.w, dt.x, dt.y, lane, 32)
-                                   : roi_scan_box<24, true>(dep0, W, roi.x, roi.y, roi.z, roi.w, dt.x, dt.y, lane, 32));
-                if (lane == 0) sbest[kl] = best;
-                if (p.prof && tid == 0 && blockIdx.x < 1024 && kl == 0) {
-                    long long t_;
-                    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"((uint32_t)best) : "memory");
-                    g_prof[blockIdx.x * PROF_PTS + 33] = t_;
+            if (p.dep_off >= 0) {
+                for (int kl = warp; kl < n_local; kl += SNW) {
+                    const short4 roi = *reinterpret_cast<const short4*>(&sbest[kl]);
+                    const float2 dt = *reinterpret_cast<const float2*>(&sdet[kl].depth);
+                    __syncwarp();
+                    const unsigned long long best =
+                        warp_min_key(roi_scan_box<8, true>(dep0, W, roi.x, roi.y, roi.z, roi.w, dt.x, dt.y, lane, 32));
+                    if (lane == 0) sbest[kl] = best;
+                    if (p.prof && tid == 0 && blockIdx.x < 1024 && kl == 0) {
+                        long long t_;
+                        asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"((uint32_t)best) : "memory");
+                        g_prof[blockIdx.x * PROF_PTS + 33] = t_;
+                    }
+                }
+            } else {
+                // A plane too big to stage is read from L2: float4 row loads (fewer, wider requests; the staged plane
+                // is bound by its per-pixel tests, and the narrow ROIs of the reference sizes fill a warp better pixel
+                // by pixel), and the warps take detections from a shared counter as they become free (at K = 500 the
+                // ROI sizes of a CTA's 60-odd detections differ widely).
+                const bool quads = (W & 3) == 0 && (reinterpret_cast<uintptr_t>(dep0) & 15u) == 0;
+                for (;;) {
+                    int kl = 0;
+                    if (lane == 0) kl = (int)atomicAdd(&s_nfl, 1u);  // (pass B's counter, reset when it was done with it)
+                    kl = __shfl_sync(FULL, kl, 0);
+                    if (kl >= n_local) break;
+                    const short4 roi = *reinterpret_cast<const short4*>(&sbest[kl]);
+                    const float2 dt = *reinterpret_cast<const float2*>(&sdet[kl].depth);
+                    __syncwarp();
+                    const unsigned long long best = warp_min_key(
+                        quads ? roi_scan_box4<8>(dep0, W, roi.x, roi.y, roi.z, roi.w, dt.x, dt.y, lane)
+                              : roi_scan_box<24, true>(dep0, W, roi.x, roi.y, roi.z, roi.w, dt.x, dt.y, lane, 32));
+                    if (lane == 0) sbest[kl] = best;
                 }
             }
             PROF(25);
