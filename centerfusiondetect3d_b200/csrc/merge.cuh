@@ -113,12 +113,17 @@ __device__ __forceinline__ void merge_select_part(const MergeParams& p, MergeSme
     const int list = p.list[li];
     const int K = p.K;
     CF_MERGE_PROF(0);
-    const uint32_t n = __ldcg(p.ctr + ((size_t)b * 2 + list) * CTR_STRIDE);  // survivors appended (>= K by construction)
     const unsigned long long* cand = p.cand + ((size_t)b * 2 + list) * CAND_CAP;
+    // the list is read before its length is known (one L2 round trip instead of two; the storage is CAND_CAP entries
+    // whatever the count, entries beyond it are ignored)
+    static_assert(MERGE_WIN == 2 * T && MERGE_WIN <= CAND_CAP, "two speculative entries per thread");
+    const unsigned long long spec0 = __ldcg(cand + tid), spec1 = __ldcg(cand + tid + T);
+    const uint32_t n = __ldcg(p.ctr + ((size_t)b * 2 + list) * CTR_STRIDE);  // survivors appended (>= K by construction)
     int nw;  // entries of win[] to rank
     const bool listed = n <= (uint32_t)MERGE_WIN;
     if (listed) {
-        for (int t = tid; t < (int)n; t += T) sm.win[t] = __ldcg(cand + t);
+        if (tid < (int)n) sm.win[tid] = spec0;
+        if (tid + T < (int)n) sm.win[tid + T] = spec1;
         nw = (int)n;
         __syncthreads();
     } else {

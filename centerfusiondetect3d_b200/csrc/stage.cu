@@ -212,14 +212,17 @@ __device__ __forceinline__ void tau_scan_cluster(uint32_t hist_saddr, int list_w
         uint32_t total[2];
 #pragma unroll
         for (int l = 0; l < 2; ++l) {
-            uint32_t below = carry[l];
-            total[l] = carry[l];
+            // prefix over the warps' totals: every warp scans them itself (lanes 0..NW-1), no extra barrier
+            static_assert(NW <= 32, "one lane per warp total");
+            const uint32_t wt = lane < NW ? s_scan[l * (NW + 1) + lane] : 0u;
+            uint32_t winc = wt;
 #pragma unroll
-            for (int w = 0; w < NW; ++w) {
-                const uint32_t t = s_scan[l * (NW + 1) + w];
-                if (w < warp) below += t;
-                total[l] += t;
+            for (int off = 1; off < NW; off <<= 1) {
+                const uint32_t o = __shfl_up_sync(FULL, winc, off);
+                if (lane >= off) winc += o;
             }
+            const uint32_t below = carry[l] + __shfl_sync(FULL, winc - wt, warp);
+            total[l] = carry[l] + __shfl_sync(FULL, winc, NW - 1);
             inc[l] += below;
             const int bin = (int)top[l] - (round * ST + tid);
             if (!done[l] && inc[l] >= (uint32_t)K && inc[l] - c[l] < (uint32_t)K)
