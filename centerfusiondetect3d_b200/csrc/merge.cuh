@@ -139,11 +139,14 @@ __device__ __forceinline__ void merge_select_part(const MergeParams& p, MergeSme
     static_assert(MERGE_WIN <= 2 * T && MERGE_WIN <= SEL_CAP / 2, "two entries per thread; sorted[] and start[] share surv[]");
     unsigned long long* sorted = sm.sc.surv;
     uint32_t* start = reinterpret_cast<uint32_t*>(sm.sc.surv + MERGE_WIN);
+    unsigned long long* winners = sm.sc.surv + MERGE_WIN + 128;  // behind start[256]
+    constexpr uint32_t WIN_CAP = SEL_CAP - (MERGE_WIN + 128);  // (a hint list: winners beyond it just go unprefetched)
     const int lane = tid & 31;
     if (tid < 256) sm.sc.hist[tid] = 0u;
     if (tid == 0) {
         sm.sc.L = 0xffffffffu;
         sm.sc.kmax = 0u;
+        sm.sc.n_out = 0u;
     }
     unsigned long long me[2];
     uint32_t kmn = 0xffffffffu, kmx = 0u;
@@ -204,9 +207,30 @@ __device__ __forceinline__ void merge_select_part(const MergeParams& p, MergeSme
         const int s0 = (int)start[bk[u]], s1 = s0 + (int)sm.sc.hist[bk[u]];
         int rank = s0;
         for (int jx = s0; jx < s1; ++jx) rank += (sorted[jx] > me[u]) ? 1 : 0;
-        if (rank < K) emit(rank, me[u]);
+        if (rank < K) {
+            emit(rank, me[u]);
+            const uint32_t slot = atomicAdd(&sm.sc.n_out, 1u);
+            if (slot < WIN_CAP) winners[slot] = me[u];
+        }
     }
     __syncthreads();  // win[] is reused by the next job of this CTA
+    // The head values of the winners this CTA has just ranked will be gathered -- by whichever CTA owns the detection --
+    // one cluster barrier from now: 140 k scattered sectors per batch, DRAM random-access bound.  Their L2 prefetches go
+    // out here, a barrier's worth of time earlier, spread over all threads.
+    {
+        const MergeJob& jb = p.job[li];
+        const int N = jb.epilogue == EPI_FRUSTUM ? (int)FS_N : (jb.epilogue == EPI_DECODE ? (int)DS_N : 0);
+        const int total = (int)min(sm.sc.n_out, WIN_CAP) * N;
+        const uint32_t HWu = (uint32_t)(p.H * p.W);
+        for (int t = tid; t < total; t += T) {
+            const int w = t / N, s2 = t - w * N;
+            const float* base = jb.gt.base[s2];
+            if (base) {
+                const uint32_t ind = comp_gidx(winners[w]) % HWu;
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(base + ((size_t)b * jb.gt.nch[s2] + jb.gt.ch[s2]) * HWu + ind));
+            }
+        }
+    }
     CF_MERGE_PROF(2);
 }
 
