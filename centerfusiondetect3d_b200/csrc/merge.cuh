@@ -214,24 +214,29 @@ __device__ __forceinline__ void merge_select_part(const MergeParams& p, MergeSme
         }
     }
     __syncthreads();  // win[] is reused by the next job of this CTA
-    // The head values of the winners this CTA has just ranked will be gathered -- by whichever CTA owns the detection --
-    // one cluster barrier from now: 140 k scattered sectors per batch, DRAM random-access bound.  Their L2 prefetches go
-    // out here, a barrier's worth of time earlier, spread over all threads.
-    {
-        const MergeJob& jb = p.job[li];
-        const int N = jb.epilogue == EPI_FRUSTUM ? (int)FS_N : (jb.epilogue == EPI_DECODE ? (int)DS_N : 0);
-        const int total = (int)min(sm.sc.n_out, WIN_CAP) * N;
-        const uint32_t HWu = (uint32_t)(p.H * p.W);
-        for (int t = tid; t < total; t += T) {
-            const int w = t / N, s2 = t - w * N;
-            const float* base = jb.gt.base[s2];
-            if (base) {
-                const uint32_t ind = comp_gidx(winners[w]) % HWu;
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(base + ((size_t)b * jb.gt.nch[s2] + jb.gt.ch[s2]) * HWu + ind));
-            }
+    CF_MERGE_PROF(2);
+}
+
+// The head values of the winners this CTA has just ranked (merge_select_part leaves their composites behind start[] in
+// the scratch) will be gathered -- by whichever CTA owns the detection -- one cluster barrier from now: 140 k scattered
+// sectors per batch, DRAM random-access bound.  Their L2 prefetches go out a barrier's worth of time earlier, spread
+// over all threads; the caller places this between the arrival at that barrier and the wait.
+template <int T>
+__device__ __forceinline__ void prefetch_winner_heads(const MergeParams& p, MergeSmem& sm, int b, int li) {
+    const unsigned long long* winners = sm.sc.surv + MERGE_WIN + 128;
+    constexpr uint32_t WIN_CAP = SEL_CAP - (MERGE_WIN + 128);
+    const MergeJob& jb = p.job[li];
+    const int N = jb.epilogue == EPI_FRUSTUM ? (int)FS_N : (jb.epilogue == EPI_DECODE ? (int)DS_N : 0);
+    const int total = (int)min(sm.sc.n_out, WIN_CAP) * N;
+    const uint32_t HWu = (uint32_t)(p.H * p.W);
+    for (int t = threadIdx.x; t < total; t += T) {
+        const int w = t / N, s2 = t - w * N;
+        const float* base = jb.gt.base[s2];
+        if (base) {
+            const uint32_t ind = comp_gidx(winners[w]) % HWu;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(base + ((size_t)b * jb.gt.nch[s2] + jb.gt.ch[s2]) * HWu + ind));
         }
     }
-    CF_MERGE_PROF(2);
 }
 
 // detections kl0 .. kl0+nb of this CTA (detection k = first + kl * stride): head values of job N-channel table gt into

@@ -783,6 +783,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
 
         // ---- select: the CTAs split the ranking of the jobs' survivor lists; sorted composites land everywhere -------
         unsigned long long* xs_comp = reinterpret_cast<unsigned long long*>(smem + p.off_comp);  // [job][K]
+        int last_li = 0;
         const MergeParams& mp = *reinterpret_cast<const MergeParams*>(smem + p.off_par);
         {
             MergeSmem& msm = *reinterpret_cast<MergeSmem*>(smem + p.off_msm);
@@ -807,10 +808,16 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                         cl_st(ra + 4u, (uint32_t)(c >> 32));
                     }
                 });
+                if (jj + 1 < n_sel) prefetch_winner_heads<ST>(mp, msm, b, li);  // (the next job reuses the scratch)
+                last_li = li;
             }
         }
         PROF(7);
-        cl_sync();  // sorted top-K of every job known to every CTA
+        // sorted top-K of every job known to every CTA -- and while the barrier gathers the cluster, the prefetches of
+        // this CTA's winners go out
+        cl_arrive();
+        prefetch_winner_heads<ST>(mp, *reinterpret_cast<MergeSmem*>(smem + p.off_msm), b, last_li);
+        cl_wait();
         PROF(8);
 
         // ---- tail: detection k belongs to CTA k % CS: gathers, frustum geometry / decode outputs ----------------------
