@@ -13,7 +13,8 @@ namespace cf {
 // rows [y0,y1) of one frame: fr = the frame's records (SHARED = true: a shared-memory copy; false: global memory),
 // out = the frame's (3,H,W) map, owner = the frame's (H,W) owner map or NULL,
 // sown = shared-memory owner map holding max_rows x W ints.  Whole CTA of T threads; ends with a barrier.
-template <int T, bool SHARED>
+// PREINIT: the caller has already set the owner map of the FIRST piece of the band to -1 (and passed a CTA barrier).
+template <int T, bool SHARED, bool PREINIT = false>
 __device__ __forceinline__ void paint_band(const PaintRec* __restrict__ fr, int n, int H, int W, int y0, int y1,
                                            float* __restrict__ out, int32_t* __restrict__ owner, int* sown,
                                            int max_rows) {
@@ -24,8 +25,10 @@ __device__ __forceinline__ void paint_band(const PaintRec* __restrict__ fr, int 
     for (int ys = y0; ys < y1; ys += max_rows) {
         const int ye = min(y1, ys + max_rows);
         const int npx = (ye - ys) * W;
-        for (int i = tid; i < npx; i += T) sown[i] = -1;
-        __syncthreads();
+        if (!(PREINIT && ys == y0)) {
+            for (int i = tid; i < npx; i += T) sown[i] = -1;
+            __syncthreads();
+        }
         if (SHARED) {
             // records in shared memory: record k on warp k % (T/32), so that all warps paint (a broadcast read each)
             for (int k = warp; k < n; k += T / 32) {

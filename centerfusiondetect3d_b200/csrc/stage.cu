@@ -900,16 +900,23 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             }
         }
         PROF(9);
-        cl_sync();  // paint records complete
-        PROF(10);
-
         // ---- paint: this CTA's band of rows of pc_hm ----------------------------------------------------------------
         {
             const int y0 = (int)((long long)H * rank / cs), y1 = (int)((long long)H * (rank + 1) / cs);
             const size_t own_off = (size_t)p.off_own;
             const int max_rows = max(1, (int)(((size_t)p.slot_area - own_off) / ((size_t)W * sizeof(int))));
-            paint_band<ST, true>(srecs, K, H, W, y0, y1, p.pc_hm + (size_t)b * (size_t)p.pc_hm_stride, nullptr,
-                                 reinterpret_cast<int*>(smem + own_off), max_rows);
+            int* sown = reinterpret_cast<int*>(smem + own_off);
+            // paint records complete in every CTA -- while the barrier gathers the cluster, the owner map of the band's
+            // first piece is cleared (this CTA is done with the scratch it overlays: the barrier below starts with a
+            // CTA-wide one)
+            __syncthreads();
+            cl_arrive();
+            const int npx0 = min(max_rows, y1 - y0) * W;
+            for (int i = tid; i < npx0; i += ST) sown[i] = -1;
+            cl_wait();
+            PROF(10);
+            paint_band<ST, true, true>(srecs, K, H, W, y0, y1, p.pc_hm + (size_t)b * (size_t)p.pc_hm_stride, nullptr, sown,
+                                       max_rows);
         }
         PROF(11);
     }
