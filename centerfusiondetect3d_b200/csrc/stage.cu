@@ -850,6 +850,10 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     const unsigned long long best =
                         warp_min_key(roi_scan_box<8, true>(dep0, W, roi.x, roi.y, roi.z, roi.w, dt.x, dt.y, lane, 32));
                     if (lane == 0) sbest[kl] = best;
+                    if (lane < 2 && best != ~0ull) {  // the match's two velocity values: on their way into L1 for the record
+                        const float* v = p.pc_vel + (size_t)b * 3 * HW + (size_t)(lane + 1) * HW + (uint32_t)best;
+                        asm volatile("prefetch.global.L1 [%0];" ::"l"(v));
+                    }
                     if (p.prof && tid == 0 && blockIdx.x < 1024 && kl == 0) {
                         long long t_;
                         asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"((uint32_t)best) : "memory");
