@@ -181,11 +181,20 @@ def cpu_stage(ob, wl, inp):
     ob.fusion_decode({k: inp[k] for k in STAGE_KEYS}, (wl.H, wl.W), wl.K)
 
 
+def host_threads() -> int:
+    """Host threads the CPU legs use: every core this process may run on.  (Not omp_get_max_threads(): torchrun exports
+    OMP_NUM_THREADS=1 to its workers, which would time the reference arm on one thread at N > 1; the oracle's parallel
+    regions carry an explicit num_threads clause, so the environment variable does not bind them.)"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except (AttributeError, OSError):
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_baseline(wl, inp, B, budget_s=12.0, min_reps=2):
     from oracle import binding as ob
 
-    cores = os.cpu_count() or 1
-    threads = max(1, min(cores, ob.max_threads()))
+    threads = host_threads()
     ob.set_threads(threads)
     cpu_stage(ob, wl, inp)  # warm-up
     t0 = time.perf_counter()
@@ -210,8 +219,7 @@ def run_reference_arm(args, wl, B):
 
     ob.build()
     inp = make_host_inputs(wl, B, seed=1234)
-    cores = os.cpu_count() or 1
-    threads = max(1, min(cores, ob.max_threads()))
+    threads = host_threads()
     ob.set_threads(threads)
     for _ in range(max(1, min(args.warmup, 3))):
         cpu_stage(ob, wl, inp)
