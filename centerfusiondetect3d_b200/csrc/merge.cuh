@@ -108,7 +108,7 @@ __device__ __noinline__ void select_overflow(const MergeParams& p, MergeSmem& sm
 // Composites are distinct, so ranks are a permutation and the parts' outputs are disjoint.
 template <int T, class Emit>
 __device__ __forceinline__ void merge_select_part(const MergeParams& p, MergeSmem& sm, int b, int li, int part,
-                                                  int parts, Emit&& emit) {
+                                                  int parts, uint32_t n, Emit&& emit) {
     const int tid = threadIdx.x;
     const int list = p.list[li];
     const int K = p.K;
@@ -118,7 +118,7 @@ __device__ __forceinline__ void merge_select_part(const MergeParams& p, MergeSme
     // whatever the count, entries beyond it are ignored)
     static_assert(MERGE_WIN == 2 * T && MERGE_WIN <= CAND_CAP, "two speculative entries per thread");
     const unsigned long long spec0 = __ldcg(cand + tid), spec1 = __ldcg(cand + tid + T);
-    const uint32_t n = __ldcg(p.ctr + ((size_t)b * 2 + list) * CTR_STRIDE);  // survivors appended (>= K by construction)
+    // n = survivors appended to the list (>= K by construction; the caller read the cluster's counter)
     int nw;  // entries of win[] to rank
     const bool listed = n <= (uint32_t)MERGE_WIN;
     if (listed) {

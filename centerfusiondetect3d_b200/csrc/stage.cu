@@ -83,6 +83,11 @@ __device__ __forceinline__ uint32_t cl_map(uint32_t saddr, uint32_t rank) {
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
     return r;
 }
+__device__ __forceinline__ uint32_t cl_atom_add(uint32_t raddr, uint32_t v) {
+    uint32_t r;
+    asm volatile("atom.shared::cluster.add.u32 %0, [%1], %2;" : "=r"(r) : "r"(raddr), "r"(v) : "memory");
+    return r;
+}
 __device__ __forceinline__ void cl_red_add(uint32_t raddr, uint32_t v) {
     asm volatile("red.shared::cluster.add.u32 [%0], %1;" ::"r"(raddr), "r"(v) : "memory");
 }
@@ -255,6 +260,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     __shared__ uint32_t s_tops[2][MAX_CS];
     __shared__ uint32_t s_mytop[2];
     __shared__ uint32_t s_nwl;  // entries of the pass-B work list
+    __shared__ uint32_t s_ctr[2];  // in the cluster's CTA 0: survivors appended to the frame's two lists (a shared-memory
+                                   // counter every CTA reaches over DSMEM: a third of the round trip of a global atomic)
     __shared__ float s_cal[2];    // calib[0,0], calib[0,2] of the frame (fetched at frame start)
     __shared__ uint32_t s_nfl;  // pass B, resident shares: flagged groups (a group = the 1/32 of a chunk one lane took in pass A)
     __shared__ uint16_t s_fl[FL_CAP];
@@ -305,8 +312,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     int it = 0;
     for (int b = cluster_id; b < p.B; b += n_clusters, ++it) {
         const float* frame = p.heat + (size_t)b * CH * W;
-        uint32_t* ctr_raw = p.ctr + ((size_t)b * 2) * CTR_STRIDE;
-        uint32_t* ctr_nms = ctr_raw + CTR_STRIDE;
+        const uint32_t ctr_raw = cl_map(smem_u32(&s_ctr[0]), 0u), ctr_nms = cl_map(smem_u32(&s_ctr[1]), 0u);  // CTA 0's
         unsigned long long* cand_raw = p.cand + (size_t)b * 2 * CAND_CAP;
         unsigned long long* cand_nms = cand_raw + CAND_CAP;
 
@@ -362,13 +368,13 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         if (tid < 2 * MAX_CS) (&s_tops[0][0])[tid] = 0u;
         if (tid < 2) s_mytop[tid] = 0u;
         if (tid == 0) s_nwl = s_nfl = 0u;
+        if (tid < 2) s_ctr[tid] = 0u;  // (cleared before this CTA arrives at the frame's first cluster barrier)
         fence_async_smem();  // the previous frame's merge scratch / owner map were generic writes to the slot area
         __syncthreads();
         // "this CTA runs and its histogram part is clear": arrive now, wait right before the first remote reduction
         // (the release fence of the arrival then has nothing outstanding to wait for)
         cl_arrive();
         if (use_tma && tid < (LPF < S ? LPF : S)) issue_load(tid);
-        if (rank == 0 && tid < 2 * CTR_STRIDE) ctr_raw[tid] = 0u;  // ordered before any append by the next barrier
         if (p.do_frustum && tid >= ST - 2)  // (the last warp: it stalls on this DRAM read before its first chunk)
             s_cal[tid - (ST - 2)] = __ldg(p.mp.job[0].fh.calib + 12 * (size_t)b + 2 * (tid - (ST - 2)));
         if (p.do_frustum && tid == 0) {  // the association's radar maps: into L2 while the heat-map streams
@@ -507,12 +513,12 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         float tau_nms = want_nms ? tau_to_float(tau_key[1]) : INF;
         if (want_raw && tau_key[0] == 0u) {
             // fewer than K groups: no useful bound -> the merge selects from the frame itself (list flagged overflowed)
-            if (rank == 0 && tid == 0) atomicAdd(ctr_raw, (uint32_t)CAND_CAP + 1u);
+            if (rank == 0 && tid == 0) atomicAdd(&s_ctr[0], (uint32_t)CAND_CAP + 1u);
             tau_raw = INF;
         }
         if (want_nms && !(tau_nms > 0.0f)) {
             // fewer than K positive peaks: suppressed pixels (worth 0) belong to the top-K too -> same
-            if (rank == 0 && tid == 0) atomicAdd(ctr_nms, (uint32_t)CAND_CAP + 1u);
+            if (rank == 0 && tid == 0) atomicAdd(&s_ctr[1], (uint32_t)CAND_CAP + 1u);
             tau_nms = INF;
         }
 
@@ -582,11 +588,11 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                         bool sraw, snms;
                         cand_eval(code, v, gi, sraw, snms);
                         if (sraw) {
-                            const uint32_t gs = atomicAdd(ctr_raw, 1u);
+                            const uint32_t gs = cl_atom_add(ctr_raw, 1u);
                             if (gs < (uint32_t)CAND_CAP) cand_raw[gs] = make_comp(f2key(v), gi);
                         }
                         if (snms) {
-                            const uint32_t gs = atomicAdd(ctr_nms, 1u);
+                            const uint32_t gs = cl_atom_add(ctr_nms, 1u);
                             if (gs < (uint32_t)CAND_CAP) cand_nms[gs] = make_comp(f2key(v), gi);
                         }
                     }
@@ -753,7 +759,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 lb0 = __shfl_sync(FULL, lb0, 0);
                 lb1 = __shfl_sync(FULL, lb1, 0);
                 __syncthreads();
-                if (tid < 2 && s_cnt[tid]) s_base[tid] = atomicAdd(tid ? ctr_nms : ctr_raw, s_cnt[tid]);
+                if (tid < 2 && s_cnt[tid]) s_base[tid] = cl_atom_add(tid ? ctr_nms : ctr_raw, s_cnt[tid]);
                 __syncthreads();
                 lb0 += s_base[0];
                 lb1 += s_base[1];
@@ -801,7 +807,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     li = 0, part = (int)rank, parts = (int)cs;
                 }
                 const uint32_t dst = smem_u32(xs_comp + li * K);
-                merge_select_part<ST>(mp, msm, b, li, part, parts, [&](int r, unsigned long long c) {
+                const uint32_t n_list = cl_ld(mp.list[li] ? ctr_nms : ctr_raw);  // survivors of the job's list
+                merge_select_part<ST>(mp, msm, b, li, part, parts, n_list, [&](int r, unsigned long long c) {
                     for (uint32_t c2 = 0; c2 < cs; ++c2) {
                         const uint32_t ra = cl_map(dst + 8u * (uint32_t)r, c2);
                         cl_st(ra, (uint32_t)c);
