@@ -1,0 +1,45 @@
+"""Development aid: the oracle differential of tests/test_gpu_parity.py over many seeds and execution plans.
+python tools/stress_parity.py [n_seeds]"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import numpy as np
+
+import helpers
+import test_gpu_parity as T
+from centerfusiondetect3d_b200 import ops, synthetic as syn
+from oracle import binding as oracle
+
+oracle.build()
+n_seeds = int(sys.argv[1]) if len(sys.argv) > 1 else 8
+fails = 0
+runs = 0
+for seed in range(n_seeds):
+    for cfg_name, B in (("cfg2", 5), ("cfg1", 3), ("cfg5", 2)):
+        for cs in (0, 1, 2, 4, 8, 16):
+            if cs:
+                os.environ["CFD3D_CLUSTER"] = str(cs)
+                os.environ["CFD3D_MAX_CLUSTERS"] = "2"
+            else:
+                os.environ.pop("CFD3D_CLUSTER", None)
+                os.environ.pop("CFD3D_MAX_CLUSTERS", None)
+            if cfg_name == "cfg5" and cs in (1, 2) and seed % 4:
+                continue  # (slow on the oracle side; every fourth seed is enough)
+            wl = syn.WORKLOADS[cfg_name]
+            try:
+                inp = helpers.make_case(wl, B, seed=1000 + seed)
+            except TypeError:
+                inp = helpers.make_case(wl, B)
+                rng = np.random.default_rng(seed)
+                inp["heatmap"] = np.clip(inp["heatmap"] + rng.normal(0, 0.02, inp["heatmap"].shape), 1e-4, 0.9999).astype(np.float32)
+            runs += 1
+            try:
+                T._check_stage(ops, oracle, wl, inp, B, need_matches=False)
+            except AssertionError as e:
+                fails += 1
+                print("FAIL seed=%d %s B=%d cs=%d: %s" % (seed, cfg_name, B, cs, str(e)[:200]), flush=True)
+print("stress parity: %d runs, %d failures" % (runs, fails))
+sys.exit(1 if fails else 0)
