@@ -850,7 +850,12 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             // (the ROI bounds of detection kl wait in sbest[kl], left there by the epilogue's idle warps: this loop runs
             // once per detection on one warp and is priced by its instruction count)
             if (p.dep_off >= 0) {
-                for (int kl = warp; kl < n_local; kl += SNW) {
+                for (int kl = warp;; kl = SNW) {
+                    if (kl >= SNW) {  // first detection by warp index, the rest from the shared counter (big ROIs wait less)
+                        if (lane == 0) kl = SNW + (int)atomicAdd(&s_nfl, 1u);
+                        kl = __shfl_sync(FULL, kl, 0);
+                    }
+                    if (kl >= n_local) break;
                     const short4 roi = *reinterpret_cast<const short4*>(&sbest[kl]);
                     const float2 dt = *reinterpret_cast<const float2*>(&sdet[kl].depth);
                     __syncwarp();
