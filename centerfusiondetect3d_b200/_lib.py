@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcfd3d_b200.so")
+# CFD3D_LIB: development override (the -DCFD3D_PROFILE build of tools/prof_phases.py, A/B builds)
+LIB_PATH = os.environ.get("CFD3D_LIB") or os.path.join(_HERE, "libcfd3d_b200.so")
 
 _vp = C.c_void_p
 
@@ -32,6 +33,12 @@ class PostIn(C.Structure):
     _fields_ = [(n, _vp) for n in ("class_ids", "centers", "bboxes", "depth", "rot", "dim", "amodal", "velocity")]
 
 
+class PlanInfo(C.Structure):
+    """cf_plan_info_t"""
+    _fields_ = [(n, C.c_int) for n in ("cluster_size", "n_clusters", "rounds", "resident", "depth_plane_staged",
+                                       "chunk_rows", "slots", "smem_bytes")]
+
+
 class PostOut(C.Structure):
     """cf_post_out_t"""
     _fields_ = [(n, _vp) for n in ("centers", "bboxes", "alpha", "locations", "yaws", "bboxes3d")]
@@ -44,6 +51,8 @@ SYMBOLS = {
     "cf_last_error": (C.c_char_p, []),
     "cf_last_launch_count": (_I, []),
     "cf_set_kernel_events": (_I, [_I, _vp, _vp]),
+    "cf_last_plan": (_I, [C.POINTER(PlanInfo)]),
+    "cf_debug_set_plan": (_I, [_I, _I]),
     "cf_workspace_bytes": (_Z, [_I] * 5),
     "cf_pillars_workspace_bytes": (_Z, [_I, _I]),
     "cf_nms": (_I, [_vp, _I, _I, _I, _I, _vp, _vp]),

@@ -1,6 +1,9 @@
 """Builds libcfd3d_b200.so (the C-ABI CUDA library) in-tree with nvcc for sm_100a.
 
-    python -m centerfusiondetect3d_b200.build [--force]
+    python -m centerfusiondetect3d_b200.build [--force] [--prof]
+
+--prof builds libcfd3d_b200_prof.so with -DCFD3D_PROFILE (in-kernel phase clocks, tools/prof_phases.py; select it with
+CFD3D_LIB=<path>); the product library carries no instrumentation.
 
 nvcc cross-compiles without a GPU; the resulting .so travels to the GPU box with the repo snapshot.
 Flags: -fmad=false keeps one rounding per written fp32/fp64 operation (parity contract),
@@ -24,21 +27,25 @@ NVCC_FLAGS = [
 ]
 
 
-def _stale() -> bool:
-    if not os.path.isfile(LIB):
+LIB_PROF = os.path.join(HERE, "libcfd3d_b200_prof.so")
+
+
+def _stale(lib: str = LIB) -> bool:
+    if not os.path.isfile(lib):
         return True
-    t = os.path.getmtime(LIB)
+    t = os.path.getmtime(lib)
     deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__)]
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not _stale():
-        return LIB
+def build(force: bool = False, verbose: bool = False, prof: bool = False) -> str:
+    lib = LIB_PROF if prof else LIB
+    if not force and not _stale(lib):
+        return lib
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    cmd = [nvcc] + NVCC_FLAGS + (["-DCFD3D_PROFILE"] if prof else []) + ["-o", lib] + [os.path.join(CSRC, s) for s in SOURCES]
     res = subprocess.run(cmd, capture_output=True, text=True)
-    log = os.path.join(HERE, "build.log")
+    log = os.path.join(HERE, "build_prof.log" if prof else "build.log")
     with open(log, "w") as f:
         f.write(" ".join(cmd) + "\n" + res.stdout + res.stderr)
     if res.returncode != 0:
@@ -46,8 +53,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed building libcfd3d_b200.so (see %s)" % log)
     if verbose:
         sys.stderr.write(res.stderr)
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose=True))
+    print(build(force="--force" in sys.argv, verbose=True, prof="--prof" in sys.argv))

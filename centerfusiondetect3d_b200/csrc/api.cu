@@ -57,6 +57,7 @@ static int cuda_fail(cudaError_t e, const char* what) {
 static int check_dims(int B, int C, int H, int W) {
     if (B < 0 || C < 1 || H < 1 || W < 1) return fail(CF_E_SHAPE, "bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
     if ((long long)C * H * W >= (1ll << 31)) return fail(CF_E_RANGE, "C*H*W does not fit 31 bits");
+    if (H > 32767 || W > 32767) return fail(CF_E_RANGE, "H, W must be <= 32767 (paint windows and ROI slices are 16-bit)");
     return 0;
 }
 static int check_k(int K, int H, int W) {
@@ -101,8 +102,20 @@ int cf_set_kernel_events(int kernel_id, void* ev_start, void* ev_stop) {
     return 0;
 }
 
-__attribute__((visibility("default"))) int cf_debug_read_prof(long long* out_host, int n_cta) {
-    return debug_read_prof(out_host, n_cta);
+#ifdef CFD3D_PROFILE
+int cf_debug_read_prof(long long* out_host, int n_cta) { return debug_read_prof(out_host, n_cta); }
+#endif
+
+int cf_last_plan(cf_plan_info_t* out) {
+    if (!out) return fail(CF_E_NULL, "cf_last_plan: out is NULL");
+    last_plan(out);
+    return 0;
+}
+int cf_debug_set_plan(int force_cluster_size, int max_clusters) {
+    if (force_cluster_size < 0 || max_clusters < 0 || (force_cluster_size & (force_cluster_size - 1)) || force_cluster_size > 16)
+        return fail(CF_E_SHAPE, "cf_debug_set_plan: cluster size must be 0 or a power of two <= 16");
+    debug_set_plan(force_cluster_size, max_clusters);
+    return 0;
 }
 
 size_t cf_workspace_bytes(int B, int C, int H, int W, int K) {

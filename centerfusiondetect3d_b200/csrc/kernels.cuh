@@ -112,7 +112,9 @@ cudaError_t launch_box_assoc(const float* pc_dep, const float* bboxes, const flo
                              int32_t* assoc, cudaStream_t st, int* launches);
 cudaError_t launch_radar_sort(const double* points, const int32_t* counts, int B, int Nmax, double* out, int32_t* order,
                               cudaStream_t st, int* launches);
-int debug_read_prof(long long* out, int n_cta);
+int debug_read_prof(long long* out, int n_cta);  // -DCFD3D_PROFILE builds only
+void debug_set_plan(int force_cs, int max_clusters);
+void last_plan(cf_plan_info_t* out);
 cudaError_t launch_paint(const PaintRec* recs, int n_per_frame, int rec_stride, const int32_t* counts, int B, int H,
                          int W, float* out, int32_t* owner, cudaStream_t st, int* launches);
 cudaError_t launch_nms(const float* heat, int B, int C, int H, int W, float* out, cudaStream_t st, int* launches);

@@ -40,6 +40,8 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <atomic>
+#include <cstring>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -102,7 +104,9 @@ __device__ __forceinline__ void cl_st(uint32_t raddr, uint32_t v) {
 // generic-proxy accesses to shared memory before this fence are ordered before later async-proxy (TMA) accesses
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// development aid (CFD3D_PROF=1): per-CTA clock64 stamps at the phase boundaries of the last frame a CTA processed
+// development aid (library built with -DCFD3D_PROFILE, tools/prof_phases.py): per-CTA clock64 stamps at the phase
+// boundaries of the last frame a CTA processed.  The product build carries neither the array nor the stamps.
+#ifdef CFD3D_PROFILE
 constexpr int PROF_PTS = 48;
 __device__ long long g_prof[1024 * PROF_PTS];
 #define CF_MERGE_PROF(i)                                                                                  \
@@ -121,6 +125,25 @@ __device__ long long g_prof[1024 * PROF_PTS];
     do {                                                                                     \
         if (p.prof && tid == 0 && blockIdx.x < 1024) g_prof[blockIdx.x * PROF_PTS + (i)] = clock64(); \
     } while (0)
+#define PROF_VAL(i, v)                                                                         \
+    do {                                                                                     \
+        if (p.prof && tid == 0 && blockIdx.x < 1024) g_prof[blockIdx.x * PROF_PTS + (i)] = (long long)(v); \
+    } while (0)
+#define PROF_DEP(i, val)                                                                        \
+    do {                                                                                     \
+        if (p.prof && tid == 0 && blockIdx.x < 1024) {                                       \
+            long long t_;                                                                    \
+            asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"(val) : "memory");         \
+            g_prof[blockIdx.x * PROF_PTS + (i)] = t_;                                        \
+        }                                                                                    \
+    } while (0)
+#else
+#define CF_MERGE_PROF(i) do { } while (0)
+#define CF_MERGE_PROF_DEP(i, val) do { } while (0)
+#define PROF(i) do { } while (0)
+#define PROF_VAL(i, v) do { } while (0)
+#define PROF_DEP(i, val) do { } while (0)
+#endif
 
 }  // namespace cf
 #include "merge.cuh"
@@ -722,10 +745,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             // B2: candidates side by side, one per thread and trip.  Survivors are counted per CTA (shared-memory atomics), the frame's lists
             // see ONE reservation per (CTA, list): same-address global atomics serialise at a few per microsecond.
             const uint32_t n_wl = min(s_nwl, wl_cap);
-            if (p.prof && tid == 0 && blockIdx.x < 1024) {
-                g_prof[blockIdx.x * PROF_PTS + 27] = (long long)s_nfl;
-                g_prof[blockIdx.x * PROF_PTS + 28] = (long long)s_nwl;
-            }
+            PROF_VAL(27, s_nfl);
+            PROF_VAL(28, s_nwl);
             // (up to BU candidates per thread in one trip: a CTA that parked more than 512 pays the counting, the two
             // barriers and the round trip of the reservation once -- such a CTA sets the pace of its whole cluster)
             constexpr int BU = 3;
@@ -866,11 +887,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                         const float* v = p.pc_vel + (size_t)b * 3 * HW + (size_t)(lane + 1) * HW + (uint32_t)best;
                         asm volatile("prefetch.global.L1 [%0];" ::"l"(v));
                     }
-                    if (p.prof && tid == 0 && blockIdx.x < 1024 && kl == 0) {
-                        long long t_;
-                        asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"((uint32_t)best) : "memory");
-                        g_prof[blockIdx.x * PROF_PTS + 33] = t_;
-                    }
+                    if (kl == 0) PROF_DEP(33, (uint32_t)best);
                 }
             } else {
                 // A plane too big to stage is read from L2: float4 row loads (fewer, wider requests; the staged plane
@@ -902,11 +919,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 const size_t o = (size_t)b * K + k;
                 const PaintRec r = assoc_finalize(sbest[kl], p.pc_vel + (size_t)b * 3 * HW, H, W, sdet[kl], p.max_pc_dist, p.assoc ? p.assoc + o : nullptr);
                 const uint32_t* rw = reinterpret_cast<const uint32_t*>(&r);
-                if (p.prof && tid == 0 && blockIdx.x < 1024) {
-                    long long t_;
-                    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"(rw[0] ^ rw[1] ^ rw[2] ^ rw[3] ^ rw[4]) : "memory");
-                    g_prof[blockIdx.x * PROF_PTS + 34] = t_;
-                }
+                PROF_DEP(34, rw[0] ^ rw[1] ^ rw[2] ^ rw[3] ^ rw[4]);
                 const uint32_t dst = smem_u32(srecs + k);
                 for (uint32_t c = 0; c < cs; ++c) {
                     const uint32_t ra = cl_map(dst, c);
@@ -941,6 +954,26 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
 // -----------------------------------------------------------------------------------------------------
 // host side: plan + launch
 // -----------------------------------------------------------------------------------------------------
+// Development switches, read from the environment ONCE per process (never on the launch path).
+struct StageEnv {
+    bool verbose, no_pdl;
+    int prof;
+    long long chunk_bytes;
+    StageEnv() {
+        verbose = getenv("CFD3D_VERBOSE") != nullptr;
+        no_pdl = getenv("CFD3D_NO_PDL") != nullptr;
+        prof = getenv("CFD3D_PROF") ? atoi(getenv("CFD3D_PROF")) : 0;
+        chunk_bytes = 8192;
+        if (const char* e = getenv("CFD3D_CHUNK_BYTES")) {
+            if (atoll(e) >= 256) chunk_bytes = atoll(e);
+        }
+    }
+};
+static const StageEnv& stage_env() {
+    static const StageEnv e;
+    return e;
+}
+
 static size_t align_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct StagePlan {
@@ -958,10 +991,7 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
     int cs_log2 = 0;
     while ((1 << cs_log2) < cs) ++cs_log2;
     const long long share = (CH + cs - 1) / cs;  // rows of the largest share
-    long long chunk_bytes = 8192;
-    if (const char* e = getenv("CFD3D_CHUNK_BYTES")) {
-        if (atoll(e) >= 256) chunk_bytes = atoll(e);
-    }
+    const long long chunk_bytes = stage_env().chunk_bytes;
     long long R = chunk_bytes / ((long long)Wp * 4);
     if (R < 1) R = 1;
     if (R > share) R = share;
@@ -1054,56 +1084,71 @@ static cudaError_t launch_cfg(const StagePlan& pl, int grid, cudaStream_t st, cu
     return cudaSuccess;
 }
 
-// co-resident clusters of this size with this much shared memory (cached per device)
-static int max_clusters(const StagePlan& pl) {
+// test hook (cf_debug_set_plan): pin the cluster size / cap the co-resident clusters; part of the plan-cache key
+static std::atomic<int> g_force_cs{0}, g_force_cap{0};
+void debug_set_plan(int force_cs, int max_clusters) {
+    g_force_cs.store(force_cs > 0 ? force_cs : 0);
+    g_force_cap.store(max_clusters > 0 ? max_clusters : 0);
+}
+static thread_local cf_plan_info_t g_last_plan = {0, 0, 0, 0, 0, 0, 0, 0};
+void last_plan(cf_plan_info_t* out) { *out = g_last_plan; }
+
+// The kernel's function attributes are process-wide state of the CUDA runtime: they are set ONCE per device, to the
+// largest values any plan uses, so that concurrent host threads with different shapes never race on them.
+static cudaError_t device_setup(int dev) {
     static std::mutex mu;
-    static std::map<std::tuple<int, int, size_t>, int> cache;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    const auto key = std::make_tuple(dev, pl.cs, pl.smem);
-    {
-        std::lock_guard<std::mutex> g(mu);
-        auto f = cache.find(key);
-        if (f != cache.end()) return f->second;
-    }
-    int n = 0;
-    if (cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem) ==
-            cudaSuccess &&
-        (pl.cs <= 8 ||
-         cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess)) {
-        cudaLaunchConfig_t cfg;
-        cudaLaunchAttribute attr[1];
-        memset(&cfg, 0, sizeof(cfg));
-        launch_cfg(pl, pl.cs, nullptr, &cfg, attr);
-        if (cudaOccupancyMaxActiveClusters(&n, fusion_stage_kernel, &cfg) != cudaSuccess) n = 0;
-    }
-    cudaGetLastError();  // a refused cluster size is not an error of the call
+    static std::map<int, cudaError_t> done;
     std::lock_guard<std::mutex> g(mu);
-    cache[key] = n;
+    auto f = done.find(dev);
+    if (f != done.end()) return f->second;
+    cudaError_t e = cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_DYN_CAP);
+    if (e == cudaSuccess) {
+        // clusters of 16 are an opt-in; a device that refuses just never gets such a plan (occupancy query says 0)
+        if (cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
+            cudaGetLastError();
+    }
+    done[dev] = e;
+    return e;
+}
+
+// co-resident clusters of this size with this much shared memory
+static int max_clusters(const StagePlan& pl) {
+    int n = 0;
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    memset(&cfg, 0, sizeof(cfg));
+    launch_cfg(pl, pl.cs, nullptr, &cfg, attr);
+    if (cudaOccupancyMaxActiveClusters(&n, fusion_stage_kernel, &cfg) != cudaSuccess) n = 0;
+    cudaGetLastError();  // a refused cluster size is not an error of the call
     return n;
 }
 
-cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, int K, const Workspace& ws,
-                                const MergeJob* raw_job, const MergeJob* nms_job, const float* pc_dep,
-                                const float* pc_vel, float max_pc_dist, float* pc_hm, long long pc_hm_stride,
-                                int32_t* assoc, cudaStream_t st, int* launches) {
-    const bool do_frustum = raw_job && raw_job->epilogue == EPI_FRUSTUM && pc_dep && pc_hm;
-    const bool use_tma = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(heat) & 15u) == 0);
-    const bool stage_dep = do_frustum && (((size_t)H * W) % 4 == 0) && ((reinterpret_cast<uintptr_t>(pc_dep) & 15u) == 0);
-    // cluster size: cheapest sum of rounds over the batch, then the most CTAs per frame
+// cluster size: cheapest sum of rounds over the batch, then the most CTAs per frame.  Cached per
+// (device, shape, flags): a steady-state call does one map lookup under a mutex and no CUDA runtime query.
+static bool choose_plan(int dev, int B, int C, int H, int W, int K, bool use_tma, bool stage_dep, StagePlan* out) {
+    typedef std::tuple<int, int, int, int, int, int, int, int, int> Key;
+    static std::mutex mu;
+    static std::map<Key, std::pair<bool, StagePlan>> cache;
+    const int force_cs = g_force_cs.load(), force_cap = g_force_cap.load();
+    const Key key(dev, B, C, H, W, K, (use_tma ? 1 : 0) | (stage_dep ? 2 : 0), force_cs, force_cap);
+    {
+        std::lock_guard<std::mutex> g(mu);
+        auto f = cache.find(key);
+        if (f != cache.end()) {
+            *out = f->second.second;
+            return f->second.first;
+        }
+    }
     StagePlan best;
+    memset(&best, 0, sizeof(best));
     long long best_rounds = -1;
-    int force_cs = 0;
-    if (const char* e = getenv("CFD3D_CLUSTER")) force_cs = atoi(e);
     for (int cs = MAX_CS; cs >= 1; cs >>= 1) {
         if (force_cs && cs != force_cs) continue;
         StagePlan pl;
         if (!plan_for_cs(cs, C, H, W, K, use_tma, stage_dep, &pl)) continue;
         int cap = max_clusters(pl);
-        if (const char* e = getenv("CFD3D_MAX_CLUSTERS")) {  // tests: force several frames per cluster
-            if (atoi(e) >= 1 && atoi(e) < cap) cap = atoi(e);
-        }
-        if (getenv("CFD3D_VERBOSE")) fprintf(stderr, "[cfd3d]   cs=%d: %d co-resident clusters (smem %zu)\n", cs, cap, pl.smem);
+        if (force_cap && force_cap < cap) cap = force_cap;  // tests: force several frames per cluster
+        if (stage_env().verbose) fprintf(stderr, "[cfd3d]   cs=%d: %d co-resident clusters (smem %zu)\n", cs, cap, pl.smem);
         if (cap < 1) continue;
         pl.n_clusters = B < cap ? B : cap;
         // a round over a resident share costs about a third of one that streams its share twice (measured, README)
@@ -1113,7 +1158,26 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
             best_rounds = rounds;
         }
     }
-    if (best_rounds < 0) return cudaErrorInvalidConfiguration;
+    std::lock_guard<std::mutex> g(mu);
+    cache[key] = std::make_pair(best_rounds >= 0, best);
+    *out = best;
+    return best_rounds >= 0;
+}
+
+cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, int K, const Workspace& ws,
+                                const MergeJob* raw_job, const MergeJob* nms_job, const float* pc_dep,
+                                const float* pc_vel, float max_pc_dist, float* pc_hm, long long pc_hm_stride,
+                                int32_t* assoc, cudaStream_t st, int* launches) {
+    const bool do_frustum = raw_job && raw_job->epilogue == EPI_FRUSTUM && pc_dep && pc_hm;
+    const bool use_tma = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(heat) & 15u) == 0);
+    const bool stage_dep = do_frustum && (((size_t)H * W) % 4 == 0) && ((reinterpret_cast<uintptr_t>(pc_dep) & 15u) == 0);
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    e = device_setup(dev);
+    if (e != cudaSuccess) return e;
+    StagePlan best;
+    if (!choose_plan(dev, B, C, H, W, K, use_tma, stage_dep, &best)) return cudaErrorInvalidConfiguration;
 
     StageParams p;
     memset(&p, 0, sizeof(p));
@@ -1176,20 +1240,14 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     p.pc_hm_stride = pc_hm_stride > 0 ? pc_hm_stride : 3ll * H * W;
     p.assoc = assoc;
     p.recs = ws.recs;
-    p.prof = getenv("CFD3D_PROF") ? atoi(getenv("CFD3D_PROF")) : 0;
+    p.prof = stage_env().prof;
     p.mp.prof = p.prof;
 
-    cudaError_t e = cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)best.smem);
-    if (e != cudaSuccess) return e;
-    if (best.cs > 8) {
-        e = cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-        if (e != cudaSuccess) return e;
-    }
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[2];
     memset(&cfg, 0, sizeof(cfg));
     launch_cfg(best, best.n_clusters * best.cs, st, &cfg, attr);
-    if (!getenv("CFD3D_NO_PDL")) {
+    if (!stage_env().no_pdl) {
         // programmatic dependent launch: this grid's CTAs may be placed (and run their prologue) while the kernel before
         // it in the stream drains; they touch global memory only after griddepcontrol.wait.  Back-to-back stage calls
         // (batches streaming through a graph) hide the grid launch latency that way.
@@ -1197,18 +1255,28 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
         attr[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.numAttrs = 2;
     }
-    if (getenv("CFD3D_VERBOSE"))
+    if (stage_env().verbose)
         fprintf(stderr, "[cfd3d] stage plan: B=%d cs=%d clusters=%d R=%d S=%d slot=%dB area=%d dep_off=%d smem=%zu tma=%d\n", B,
                 best.cs, best.n_clusters, best.R, best.S, best.slot_floats * 4, best.slot_area, best.dep_off, best.smem,
                 (int)use_tma);
+    g_last_plan.cluster_size = best.cs;
+    g_last_plan.n_clusters = best.n_clusters;
+    g_last_plan.rounds = (B + best.n_clusters - 1) / best.n_clusters;
+    g_last_plan.resident = best.resident ? 1 : 0;
+    g_last_plan.depth_plane_staged = best.dep_off >= 0 ? 1 : 0;
+    g_last_plan.chunk_rows = best.R;
+    g_last_plan.slots = best.S;
+    g_last_plan.smem_bytes = (int)best.smem;
     e = cudaLaunchKernelEx(&cfg, fusion_stage_kernel, p);
     if (e == cudaSuccess) ++*launches;
     return e;
 }
 
+#ifdef CFD3D_PROFILE
 int debug_read_prof(long long* out, int n_cta) {
     if (n_cta > 1024) n_cta = 1024;
     return (int)cudaMemcpyFromSymbol(out, g_prof, sizeof(long long) * PROF_PTS * n_cta);
 }
+#endif
 
 }  // namespace cf

@@ -26,7 +26,7 @@ from ._lib import DecodeHeads, DecodeOut, PostIn, PostOut
 __all__ = [
     "nms", "topk", "getFeature", "transposeAndGetFeature", "get_alpha", "getDistanceThresh",
     "getPcFrustumHeatmap", "cvtPcDepthToHeatmap", "fusionDecode", "radar_to_pc_dep", "fusion_stage",
-    "frustum_association", "last_launch_count", "postProcess", "inverse_output_affine", "frustum_targets", "radar_sort",
+    "frustum_association", "last_launch_count", "last_plan", "debug_set_plan", "release_buffers", "postProcess", "inverse_output_affine", "frustum_targets", "radar_sort",
     "_nms", "_topk", "_gather_feat", "_tranpose_and_gather_feat", "generate_pc_hm", "get_pc_hm",
     "pc_dep_to_hm_torch", "fusion_decode", "get_dist_thresh",
 ]
@@ -65,28 +65,73 @@ def _map(t, name: str, ndim: int = 4, dtype=torch.float32, pinned_ok: bool = Fal
     return t.contiguous()  # the reference accepts any strides
 
 
-_ws_cache: dict = {}
-_staging_cache: dict = {}
+class _Lru(dict):
+    """Small bounded cache of device buffers keyed by (device, stream, ...): streams come and go (their handles can
+    even be reused), so the least recently used buffers are dropped instead of kept for the life of the process."""
+
+    def __init__(self, cap: int):
+        super().__init__()
+        self.cap = cap
+
+    def lookup(self, key):
+        v = self.pop(key, None)
+        if v is not None:
+            self[key] = v  # most recently used last
+        return v
+
+    def store(self, key, v):
+        self.pop(key, None)
+        self[key] = v
+        while len(self) > self.cap:
+            self.pop(next(iter(self)))
+
+
+_ws_cache = _Lru(16)
+_staging_cache = _Lru(16)
+
+
+def release_buffers() -> None:
+    """Drops the cached workspaces / staging buffers (they are re-created on demand)."""
+    _ws_cache.clear()
+    _staging_cache.clear()
 
 
 def _staging(dev: torch.device, name: str, shape: tuple) -> torch.Tensor:
     """Per-(device, stream, name, shape) device buffer for inputs a host-buffer caller hands over in pinned memory."""
     key = (dev.index, torch.cuda.current_stream(dev).cuda_stream, name, tuple(shape))
-    buf = _staging_cache.get(key)
+    buf = _staging_cache.lookup(key)
     if buf is None:
         buf = torch.zeros(shape, dtype=torch.float32, device=dev)
-        _staging_cache[key] = buf
+        _staging_cache.store(key, buf)
     return buf
 
 
 def _workspace(dev: torch.device, nbytes: int) -> torch.Tensor:
     """Grow-only per-(device, stream) scratch buffer: no allocation on the steady-state path."""
     key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
-    buf = _ws_cache.get(key)
+    buf = _ws_cache.lookup(key)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=dev)
-        _ws_cache[key] = buf
+        _ws_cache.store(key, buf)
     return buf
+
+
+def _call(dev: torch.device, name: str, *args) -> None:
+    """One ABI call with `dev` current: the kernels, their function attributes and the occupancy-based launch plans all
+    act on the current device, which in a single-process multi-GPU program need not be the tensors' device."""
+    fn = getattr(_lib.lib(), name)
+    if dev.index is None or dev.index == torch.cuda.current_device():
+        _lib.check(fn(*args))
+    else:
+        with torch.cuda.device(dev):
+            _lib.check(fn(*args))
+
+
+def _same_device(*tensors) -> None:
+    """Every CUDA tensor of a call lives on one device (pinned host tensors are readable from any)."""
+    devs = {t.device for t in tensors if isinstance(t, torch.Tensor) and t.is_cuda}
+    if len(devs) > 1:
+        raise ValueError("all CUDA tensors of a call must be on one device, got %s" % sorted(str(d) for d in devs))
 
 
 def _stage_ws(dev, B, Cc, H, W, K):
@@ -103,6 +148,20 @@ def last_launch_count() -> int:
     return int(_lib.lib().cf_last_launch_count())
 
 
+def last_plan() -> dict:
+    """Execution plan of the last fused-stage launch on this thread (cf_last_plan): cluster_size, n_clusters, rounds,
+    resident, depth_plane_staged, chunk_rows, slots, smem_bytes."""
+    info = _lib.PlanInfo()
+    _lib.check(_lib.lib().cf_last_plan(C.byref(info)))
+    return {n: int(getattr(info, n)) for n, _ in _lib.PlanInfo._fields_}
+
+
+def debug_set_plan(force_cluster_size: int = 0, max_clusters: int = 0) -> None:
+    """Test hook (cf_debug_set_plan): pin the cluster size / cap the co-resident clusters of later stage launches;
+    (0, 0) restores the planner's own choice."""
+    _lib.check(_lib.lib().cf_debug_set_plan(int(force_cluster_size), int(max_clusters)))
+
+
 # ------------------------------------------------------------------------------------------------------
 # a1-a3  heat-map peak decode primitives                                   src/lib/model/utils.py
 # ------------------------------------------------------------------------------------------------------
@@ -113,7 +172,7 @@ def nms(heatmap: torch.Tensor, kernel: int = 3) -> torch.Tensor:
     heat = _map(heatmap, "heatmap")
     B, Cc, H, W = heat.shape
     out = torch.empty_like(heat)
-    _lib.check(_lib.lib().cf_nms(heat.data_ptr(), B, Cc, H, W, out.data_ptr(), _stream(heat)))
+    _call(heat.device, "cf_nms", heat.data_ptr(), B, Cc, H, W, out.data_ptr(), _stream(heat))
     return out
 
 
@@ -131,9 +190,9 @@ def topk(heatmap: torch.Tensor, K: int = 100, *, apply_nms: bool = False):
     ys = torch.empty((B, K), dtype=torch.int64, device=dev)
     xs = torch.empty((B, K), dtype=torch.int64, device=dev)
     ws, wsn = _stage_ws(dev, B, Cc, H, W, K)
-    _lib.check(_lib.lib().cf_peak_topk(heat.data_ptr(), B, Cc, H, W, K, int(bool(apply_nms)), scores.data_ptr(),
+    _call(dev, "cf_peak_topk", heat.data_ptr(), B, Cc, H, W, K, int(bool(apply_nms)), scores.data_ptr(),
                                        inds.data_ptr(), classes.data_ptr(), ys.data_ptr(), xs.data_ptr(),
-                                       ws.data_ptr(), wsn, _stream(heat)))
+                                       ws.data_ptr(), wsn, _stream(heat))
     return scores, inds, classes, ys, xs
 
 
@@ -146,8 +205,8 @@ def transposeAndGetFeature(feature: torch.Tensor, indices: torch.Tensor) -> torc
         raise ValueError("indices batch %d != feature batch %d" % (ind.shape[0], B))
     M = ind.shape[1]
     out = torch.empty((B, M, ch), dtype=torch.float32, device=feat.device)
-    _lib.check(_lib.lib().cf_gather_nchw(feat.data_ptr(), B, ch, H * W, ind.data_ptr(), M, out.data_ptr(),
-                                         _stream(feat)))
+    _call(feat.device, "cf_gather_nchw", feat.data_ptr(), B, ch, H * W, ind.data_ptr(), M, out.data_ptr(),
+                                         _stream(feat))
     return out
 
 
@@ -169,7 +228,7 @@ def get_alpha(rotation: torch.Tensor) -> torch.Tensor:
     if rot.shape[-1] != 8:
         raise ValueError("rotation must end in 8 bins, got %s" % (tuple(rot.shape),))
     out = torch.empty(rot.shape[:-1], dtype=torch.float32, device=rot.device)
-    _lib.check(_lib.lib().cf_get_alpha(rot.data_ptr(), out.numel(), out.data_ptr(), _stream(rot)))
+    _call(rot.device, "cf_get_alpha", rot.data_ptr(), out.numel(), out.data_ptr(), _stream(rot))
     return out
 
 
@@ -185,8 +244,8 @@ def getDistanceThresh(calib: torch.Tensor, center: torch.Tensor, dim: torch.Tens
     dim = _map(dim, "dim", ndim=3)
     alpha = _map(alpha, "alpha", ndim=None).reshape(B, K)
     out = torch.empty((B, K), dtype=torch.float32, device=center.device)
-    _lib.check(_lib.lib().cf_dist_thresh(calib.data_ptr(), center.data_ptr(), dim.data_ptr(), alpha.data_ptr(), B, K,
-                                         out.data_ptr(), _stream(center)))
+    _call(center.device, "cf_dist_thresh", calib.data_ptr(), center.data_ptr(), dim.data_ptr(), alpha.data_ptr(), B, K,
+                                         out.data_ptr(), _stream(center))
     return out
 
 
@@ -228,16 +287,17 @@ def frustum_association(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor,
         if t.shape != (B, ch, H, W):
             raise ValueError("%s must be (%d,%d,%d,%d), got %s" % (nm, B, ch, H, W, tuple(t.shape)))
     cal = _map(calib, "calib", ndim=None).view(B, 3, 4)
+    _same_device(heat, wh, dep, dim, rot, pcd, cal)
     dev = heat.device
     pc_hm = torch.empty_like(pcd)
     assoc = torch.empty((B, K), dtype=torch.int32, device=dev)
     thr = torch.empty((B, K), dtype=torch.float32, device=dev)
     inds = torch.empty((B, K), dtype=torch.int64, device=dev)
     ws, wsn = _stage_ws(dev, B, Cc, H, W, K)
-    _lib.check(_lib.lib().cf_frustum_pc_hm(heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
+    _call(dev, "cf_frustum_pc_hm", heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
                                            rot.data_ptr(), pcd.data_ptr(), cal.data_ptr(), B, Cc, H, W, int(K),
                                            float(max_pc_dist), pc_hm.data_ptr(), assoc.data_ptr(), thr.data_ptr(),
-                                           inds.data_ptr(), ws.data_ptr(), wsn, _stream(heat)))
+                                           inds.data_ptr(), ws.data_ptr(), wsn, _stream(heat))
     return pc_hm, assoc, thr, inds
 
 
@@ -271,8 +331,8 @@ def cvtPcDepthToHeatmap(pc_hm, pc_dep, depth, bbox, distanceThreshold, max_pc_di
         [float(v) for v in bbox], dtype=torch.float32, device=dev)
     if bb.numel() != 4:
         raise ValueError("bbox must have 4 elements")
-    _lib.check(_lib.lib().cf_pc_dep_to_hm_single(hm.data_ptr(), pcd.data_ptr(), H, W, d.data_ptr(), bb.data_ptr(),
-                                                 t.data_ptr(), float(max_pc_dist), None, _stream(hm)))
+    _call(dev, "cf_pc_dep_to_hm_single", hm.data_ptr(), pcd.data_ptr(), H, W, d.data_ptr(), bb.data_ptr(),
+                                                 t.data_ptr(), float(max_pc_dist), None, _stream(hm))
 
 
 def frustum_targets(pc_dep: torch.Tensor, bboxes: torch.Tensor, depth: torch.Tensor, distanceThreshold: torch.Tensor,
@@ -293,9 +353,9 @@ def frustum_targets(pc_dep: torch.Tensor, bboxes: torch.Tensor, depth: torch.Ten
     pc_hm = torch.empty_like(pcd)
     assoc = torch.empty((B, N), dtype=torch.int32, device=pcd.device) if return_assoc else None
     ws = _workspace(pcd.device, B * N * 32 + 256)
-    _lib.check(_lib.lib().cf_frustum_boxes(pcd.data_ptr(), bb.data_ptr(), dp.data_ptr(), th.data_ptr(), _ptr(cn), B, N, H, W,
+    _call(pcd.device, "cf_frustum_boxes", pcd.data_ptr(), bb.data_ptr(), dp.data_ptr(), th.data_ptr(), _ptr(cn), B, N, H, W,
                                            float(max_pc_dist), pc_hm.data_ptr(), _ptr(assoc), ws.data_ptr(), ws.numel(),
-                                           _stream(pcd)))
+                                           _stream(pcd))
     return (pc_hm, assoc) if return_assoc else pc_hm
 
 
@@ -364,9 +424,10 @@ def fusionDecode(outputs, outputSize=(112, 200), K=100, norm2d=False) -> dict:
     K = int(K)
     keep: list = []
     heads, out, ret, (B, Cc, H, W), heat = _decode_structs(layers[0], K, keep)
+    _same_device(*keep)
     ws, wsn = _stage_ws(heat.device, B, Cc, H, W, K)
-    _lib.check(_lib.lib().cf_fusion_decode(C.byref(heads), B, Cc, H, W, K, int(outputSize[0]), int(outputSize[1]),
-                                           int(bool(norm2d)), C.byref(out), ws.data_ptr(), wsn, _stream(heat)))
+    _call(heat.device, "cf_fusion_decode", C.byref(heads), B, Cc, H, W, K, int(outputSize[0]), int(outputSize[1]),
+                                           int(bool(norm2d)), C.byref(out), ws.data_ptr(), wsn, _stream(heat))
     return ret
 
 
@@ -378,7 +439,7 @@ def stage_depth_plane(pc_dep_dev: torch.Tensor, pc_dep_host: torch.Tensor) -> No
     if dev_t is not pc_dep_dev or host_t.is_cuda or dev_t.shape != host_t.shape or dev_t.shape[1] != 3:
         raise ValueError("stage_depth_plane: contiguous (B,3,H,W) CUDA destination and pinned host source required")
     B, _, H, W = dev_t.shape
-    _lib.check(_lib.lib().cf_stage_depth_plane(dev_t.data_ptr(), host_t.data_ptr(), B, H, W, _stream(dev_t)))
+    _call(dev_t.device, "cf_stage_depth_plane", dev_t.data_ptr(), host_t.data_ptr(), B, H, W, _stream(dev_t))
 
 
 def fusion_stage(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config, outputSize=None, norm2d=False,
@@ -428,6 +489,7 @@ def fusion_stage(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config
     dec_in["heatmap"] = heat  # same storage: the ABI requires one heat-map
     keep: list = []
     heads, out, ret, _, _ = _decode_structs(dec_in, K, keep)
+    _same_device(heat, wh, dep, dim, rot, pcd, cal, sec_feats, *keep)
     if "rotation2" in dec:
         dec["rotation"] = dec.pop("rotation2")
     if outputSize is None:
@@ -443,11 +505,11 @@ def fusion_stage(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config
         pc_hm = sec_feats[:, sec_feats.shape[1] - 3:]
         stride = sec_feats.shape[1] * H * W
     ws, wsn = _stage_ws(heat.device, B, Cc, H, W, K)
-    _lib.check(_lib.lib().cf_fusion_stage_split(heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
+    _call(heat.device, "cf_fusion_stage_split", heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
                                                 rot.data_ptr(), pcd.data_ptr(), _ptr(pcd_vel), cal.data_ptr(), B, Cc, H, W,
                                                 K, max_pc_dist, pc_hm.data_ptr(), stride, None, None, None,
                                                 C.byref(heads), int(outputSize[0]), int(outputSize[1]),
-                                                int(bool(norm2d)), C.byref(out), ws.data_ptr(), wsn, _stream(heat)))
+                                                int(bool(norm2d)), C.byref(out), ws.data_ptr(), wsn, _stream(heat))
     return pc_hm, ret
 
 
@@ -503,8 +565,8 @@ def postProcess(y: dict, center, scale, height, width, calibs, isGt=False) -> di
     pin = PostIn(_ptr(cls), _ptr(cen), _ptr(bb), _ptr(dep), _ptr(rot), _ptr(dim), _ptr(amo), _ptr(vel))
     pout = PostOut(_ptr(o_cen), _ptr(o_bb), _ptr(o_alpha), _ptr(o_loc), _ptr(o_yaw), _ptr(o_b3))
     tarr = (C.c_float * 6)(*[float(v) for v in trans.reshape(-1)])
-    _lib.check(_lib.lib().cf_post_process(C.byref(pin), B, K, int(height), int(width), tarr, _ptr(cal),
-                                          int(bool(isGt)), C.byref(pout), _stream(scores)))
+    _call(dev, "cf_post_process", C.byref(pin), B, K, int(height), int(width), tarr, _ptr(cal),
+                                          int(bool(isGt)), C.byref(pout), _stream(scores))
     y["centers"] = o_cen
     if bb is not None:
         y["bboxes"] = o_bb
@@ -529,8 +591,8 @@ def radar_sort(points: torch.Tensor, counts: torch.Tensor, return_order: bool = 
     cnt = _map(counts, "counts", ndim=1, dtype=torch.int32)
     out = torch.empty_like(pts)
     order = torch.empty((B, Nmax), dtype=torch.int32, device=pts.device) if return_order else None
-    _lib.check(_lib.lib().cf_radar_sort(_ptr(pts) if Nmax else None, cnt.data_ptr(), B, Nmax, out.data_ptr(), _ptr(order),
-                                        _stream(pts)))
+    _call(pts.device, "cf_radar_sort", _ptr(pts) if Nmax else None, cnt.data_ptr(), B, Nmax, out.data_ptr(), _ptr(order),
+                                        _stream(pts))
     return (out, order) if return_order else out
 
 
@@ -559,10 +621,10 @@ def radar_to_pc_dep(points: torch.Tensor, counts: torch.Tensor, cam: torch.Tenso
     n = _lib.lib().cf_pillars_workspace_bytes(B, Nmax)
     ws = _workspace(dev, n)
     pd = (C.c_double * 3)(*[float(v) for v in pillar_dims])
-    _lib.check(_lib.lib().cf_radar_pillars(_ptr(pts) if Nmax else None, cnt.data_ptr(), B, Nmax, cam.data_ptr(),
+    _call(dev, "cf_radar_pillars", _ptr(pts) if Nmax else None, cnt.data_ptr(), B, Nmax, cam.data_ptr(),
                                            cal.data_ptr(), A.data_ptr(), int(img_wh[0]), int(img_wh[1]), H, W, pd,
                                            float(max_dist), float(z_offset), pc_dep.data_ptr(), _ptr(owner),
-                                           ws.data_ptr(), ws.numel(), _stream(pts)))
+                                           ws.data_ptr(), ws.numel(), _stream(pts))
     return (pc_dep, owner) if return_owner else pc_dep
 
 

@@ -4,7 +4,8 @@
  * One shared library, extern "C", plain pointers and sizes, no torch types.  Every pointer is a DEVICE
  * pointer unless its name ends in `_host`.  All maps are fp32, NCHW, contiguous.  Every call is
  * stream-ordered on `stream` (a cudaStream_t passed as void*), never allocates, never synchronises the
- * host and keeps no global state other than a thread-local error string: the caller owns every buffer
+ * host and keeps no mutable global state other than a thread-local error string and a mutex-protected cache of
+ * launch plans per (device, shape): the caller owns every buffer
  * including the workspace (`cf_workspace_bytes`).  Return value: 0 = ok, >0 = the cudaError_t of a
  * failed launch, <0 = argument error (CF_E_*); `cf_last_error()` describes the last failure.
  *
@@ -237,16 +238,37 @@ CF_API int cf_last_launch_count(void);
  * call's stream right before kernel `kernel_id` and `ev_stop` right after it (both cudaEvent_t created by the
  * caller with timing enabled).  kernel_id < 0 or NULL events clear the hook.  No reference counterpart. */
 enum {
-    CF_KERNEL_PEAK_SELECT = 0, /* bound pass: the HBM read of the heat-map, 3x3 max + group maxima -> tau (dominant) */
-    CF_KERNEL_MERGE = 1,       /* frame-wide sorted top-K + gathers + frustum geometry / decode epilogue */
-    CF_KERNEL_ASSOC = 2,       /* per-ROI nearest-depth radar association */
-    CF_KERNEL_PAINT = 3,       /* ordered pc_hm / pc_dep paint */
-    CF_KERNEL_PILLAR_RECTS = 4, /* radar point -> pillar rectangle */
-    CF_KERNEL_PEAK_FILTER = 5,  /* filter pass: re-read (L2) + survivors >= tau */
-    CF_KERNEL_POST = 7,         /* postProcess */
-    CF_KERNEL_STAGE = 6         /* the fused stage kernel: one cluster per frame, all of the above in one launch */
+    CF_KERNEL_ASSOC = 2,        /* box_assoc_kernel: per-ROI association of given boxes (cf_frustum_boxes) */
+    CF_KERNEL_PAINT = 3,        /* paint_kernel: ordered pc_hm / pc_dep paint (cf_frustum_boxes, cf_radar_pillars) */
+    CF_KERNEL_PILLAR_RECTS = 4, /* pillar_rects_kernel: radar point -> pillar rectangle */
+    CF_KERNEL_STAGE = 6,        /* fusion_stage_kernel: one cluster per frame, the whole stage in one launch */
+    CF_KERNEL_POST = 7          /* post_process_kernel */
 };
 CF_API int cf_set_kernel_events(int kernel_id, void* ev_start, void* ev_stop);
+
+/* Execution plan of the last fused-stage launch on this thread (cf_peak_topk, cf_fusion_decode, cf_frustum_pc_hm,
+ * cf_fusion_stage*): the host picks cluster size and residency per (device, shape) -- tests assert it so that a
+ * planner change cannot silently move them off the benchmarked path. */
+typedef struct {
+    int cluster_size;       /* CTAs per frame (thread-block cluster) */
+    int n_clusters;         /* clusters launched; a cluster takes frames b = id, id + n_clusters, ... */
+    int rounds;             /* ceil(B / n_clusters) */
+    int resident;           /* 1: each CTA's heat-map share stays in shared memory between the two looks; 0: ring */
+    int depth_plane_staged; /* 1: pc_dep[b,0] is staged in shared memory for the ROI scans; 0: scanned from L2 */
+    int chunk_rows, slots;  /* rows per bulk copy, shared-memory slots */
+    int smem_bytes;         /* dynamic shared memory per CTA */
+} cf_plan_info_t;
+CF_API int cf_last_plan(cf_plan_info_t* out);
+
+/* Test hook: pin the cluster size (0 = planner's choice) and cap the co-resident clusters (0 = no cap) of later
+ * fused-stage launches of this process, so that tests reach every execution plan on any batch size. */
+CF_API int cf_debug_set_plan(int force_cluster_size, int max_clusters);
+
+#ifdef CFD3D_PROFILE
+/* Development build only (nvcc -DCFD3D_PROFILE, `python -m centerfusiondetect3d_b200.build --prof`): the in-kernel
+ * phase clocks of the last launch (48 x int64 per CTA, first n_cta CTAs) into host memory. */
+CF_API int cf_debug_read_prof(long long* out_host, int n_cta);
+#endif
 
 #ifdef __cplusplus
 }

@@ -207,10 +207,116 @@ def gen_post_process():
     save("post_process", **arrs)
 
 
+def gen_cfg1_model():
+    """BASELINE.json configs[0] / SURVEY.md 8(c) Recipe B: the reference's OWN network (random-init DLA-34 `DLASeg`,
+    seed 0, one 448x800 frame, 100 radar points through the reference pillar code) run end to end on CPU.  Stored: the
+    first- and second-stage head maps the model produced, pc_dep, calib, and the reference's pc_hm (from
+    CenterFusionHead.forward and from getPcFrustumHeatmap on those maps), association indices, fusionDecode and
+    postProcess outputs.  The -m gpu test replays the stored head maps through the ops.
+
+    The reference initialises its head convolutions with std 0.001 (model/utils.py initConv2dWeights), which leaves
+    every untrained head within 1e-5 of its bias: no boxes, no associations.  The fixture therefore rescales the LAST
+    convolution of every head (weight *= target_std / measured_std, bias = target mean) so that the heads span the
+    ranges of a trained model; the maps are still outputs of the reference's network code (spatially correlated conv
+    features, post-sigmoid heat-map, depth = 1/(sigmoid+1e-6)-1), which is what distinguishes them from synthetic.py."""
+    import refimport as R
+
+    K, H, W = 100, 112, 200
+    cfg = R.make_model_config(K=K)
+    model = R.build_model(cfg, seed=0)
+    # An untrained DLA-34 in eval mode (BatchNorm running statistics 0 / 1) maps any image to spatially constant
+    # features (relative variation 1e-4: a few hundred distinct fp32 levels, i.e. a heat-map full of exact ties).  The
+    # backbone's BatchNorm layers therefore normalise with the statistics of the frame itself (their train-mode
+    # arithmetic), which is what gives an untrained network feature maps with structure.  The model and its heads stay
+    # in eval mode: CenterFusionHead.forward takes its frustum branch (detectHeads.py:176).
+    for m_ in model.modules():
+        if isinstance(m_, torch.nn.BatchNorm2d):
+            m_.train()
+    assert not model.training and not model.detectHead_0.training
+    head = model.detectHead_0
+    targets = {  # head -> (mean per channel or scalar, std) of the pre-activation output
+        "heatmap": (-4.6, 0.6), "reg": (0.5, 0.2), "widthHeight": (12.0, 9.0), "depth": (-3.0, 0.45),
+        "depth2": (-3.0, 0.45), "rotation": (0.0, 1.0), "rotation2": (0.0, 1.0), "dimension": ([1.6, 1.8, 4.5], 0.3),
+        "amodal_offset": (0.0, 2.0), "nuscenes_att": (0.0, 1.0), "velocity": (0.0, 3.0)}
+    x = None  # drawn below: the first image seed whose heat-map is tie-free in the top-K region
+    rng = np.random.default_rng(2024)
+    pts, _ = syn.make_radar(rng, 1, 100)
+    calib64 = syn.make_calib(rng, 1)
+    A = syn.output_affine(H, W)
+    pc_dep = ref_pc_dep_from_points(ns, pts[0], calib64[0], A, (1600, 900), R.make_config(K=K, out_hw=(H, W)))[None]
+    calib = calib64.astype(np.float32)
+
+    def last_conv(seq):
+        return [m for m in seq.modules() if isinstance(m, torch.nn.Conv2d)][-1]
+
+    def forward():
+        with torch.no_grad():
+            return model(x, pc_dep=t(pc_dep).clone(), calib=t(calib))[0]
+
+    def calibrate():
+        pre = {}
+        hooks = [last_conv(getattr(head, h)).register_forward_hook(lambda m, i, o, h=h: pre.__setitem__(h, o.detach().clone()))
+                 for h in cfg.heads]
+        forward()
+        for hk in hooks:
+            hk.remove()
+        for h, (mean, std) in targets.items():
+            conv = last_conv(getattr(head, h))
+            ch_mean = pre[h].mean(dim=(0, 2, 3))
+            f = std / max(float((pre[h] - ch_mean.view(1, -1, 1, 1)).std()), 1e-12)
+            with torch.no_grad():  # new output = f * (old - old bias) + new bias: per-channel mean = target
+                want = torch.as_tensor(mean, dtype=torch.float32).expand_as(conv.bias)
+                new_bias = want - f * (ch_mean - conv.bias)
+                conv.weight.mul_(f)
+                conv.bias.copy_(new_bias)
+
+    for x_seed in range(20):  # the first image seed whose heat-map is tie-free in the top-K region
+        x = torch.randn(1, 3, 448, 800, generator=torch.Generator().manual_seed(x_seed))
+        calibrate()
+        calibrate()  # second round: the secondary heads see the pc_hm of calibrated first-stage heads
+        y = forward()
+        heads = {k: y[k].numpy().copy() for k in cfg.heads}
+        if tie_free(heads["heatmap"], K + 32):
+            print("cfg1 model: image seed", x_seed)
+            break
+    else:
+        raise RuntimeError("no tie-free heat-map in 20 image seeds")
+    probe = {k: heads[k].copy() for k in ("heatmap", "widthHeight", "depth", "dimension", "rotation")}
+    probe["calib"] = calib
+    assert ensure_margins(probe, pc_dep, K, 60.0) == 0, "a borderline association: change the seed"
+    fcfg = R.make_config(K=K, out_hw=(H, W))
+    out5 = {k: t(heads[k]) for k in ("heatmap", "widthHeight", "depth", "dimension", "rotation")}
+    pc_hm = ns.getPcFrustumHeatmap(out5, t(pc_dep), t(calib), fcfg).numpy()
+    assert np.array_equal(pc_hm[:, 0:1], y["pc_hm"].numpy()), "forward's pc_hm != getPcFrustumHeatmap on its heads"
+    assoc, thr = ref_assoc_indices(ns, {**heads, "calib": calib}, pc_dep, K, 60.0)
+    print("cfg1 model: matched", int((assoc >= 0).sum()), "of", assoc.size, "| heat max %.3f" % heads["heatmap"].max(),
+          "| negative widthHeight at %.1f %% of the pixels" % (100.0 * (heads["widthHeight"] < 0).mean()))
+    dec_in = {k: t(v).clone() for k, v in heads.items()}
+    dec = ns.fusionDecode([dec_in], outputSize=(H, W), K=K)
+    assert "rotation2" not in dec_in
+    center, scale = np.array([800.0, 450.0], dtype=np.float32), 1600.0
+    post = ns.postProcess({k: v.clone() for k, v in dec.items()}, center, scale, H, W, t(calib))
+    arrs = {"in_" + k: v for k, v in heads.items()}
+    arrs.update(in_pc_dep=pc_dep, in_calib=calib, in_K=np.int64(K), in_max_pc_dist=np.float32(60.0),
+                in_center=center, in_scale=np.float32(scale),
+                in_trans=ns.getAffineTransform(center, scale, 0, (W, H), inverse=True).astype(np.float32),
+                out_pc_hm=pc_hm, out_assoc=assoc, out_thr=thr)
+    for k, v in dec.items():
+        arrs["out_dec_" + k] = v.numpy()
+    for k, v in post.items():
+        arrs["out_post_" + k] = v.numpy()
+    save("cfg1_model", **arrs)
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1:  # python tests/golden/make_golden.py gen_cfg1_model
+        for name in sys.argv[1:]:
+            globals()[name]()
+        sys.exit(0)
     gen_topk_nms()
     gen_alpha_thr()
     gen_pillars()
     gen_pc2hm_quirks()
     gen_frustum_and_decode()
     gen_post_process()
+    gen_cfg1_model()

@@ -194,3 +194,69 @@ def ref_process_point_cloud(ns, pc_2d, pc_3d, A_out, calib, cfg):
         setattr(self, name, types.MethodType(getattr(NU, name), self))
     img_info = {"calib": np.asarray(calib, dtype=np.float64).tolist()}
     return self.processPointCloud(pc_2d, pc_3d, None, A_out, A_out, img_info)
+
+
+# ----------------------------------------------------------------------------------------------
+# Recipe B: the reference's whole model, random init, on CPU
+# ----------------------------------------------------------------------------------------------
+def make_model_config(K=100, in_hw=(448, 800), num_classes=10):
+    """The keys config/utils.py:69-166 derives for configs/centerfusion_debug.yaml (MODEL.FRUSTUM true,
+    FUSION_STRATEGY middle, DLA-34), as an attribute dict.  LOAD_DIR is non-empty so that dla.py:596-598 does not try
+    to download ImageNet weights; loadModel is never called (random init)."""
+    out_hw = [in_hw[0] // 4, in_hw[1] // 4]
+    heads = AttrDict(heatmap=num_classes, reg=2, widthHeight=2, depth=1, rotation=8, dimension=3, amodal_offset=2,
+                     nuscenes_att=8, velocity=3, depth2=1, rotation2=8)
+    head_conv = AttrDict({h: [256] for h in heads})
+    for h in ("depth2", "rotation2", "velocity", "nuscenes_att"):
+        head_conv[h] = [256, 256, 256]
+    return AttrDict(
+        DEBUG=0,
+        heads=heads,
+        head_conv=head_conv,
+        MODEL=AttrDict(ARCH="dla_34", FUSION_STRATEGY="middle", FRUSTUM=True, K=K, INPUT_SIZE=list(in_hw),
+                       OUTPUT_SIZE=out_hw, LOAD_DIR="random-init", FREEZE_BACKBONE=True, NORM_EVAL=False, NORM_2D=False,
+                       DLA=AttrDict(NODE="DeformConv")),
+        DATASET=AttrDict(DATASET="nuscenes", RADAR_PC=True, ONE_HOT_PC=False, MAX_PC_DIST=60.0, MAX_PC=1000,
+                         PC_ROI_METHOD="pillars", PILLAR_DIMS=[1.5, 0.2, 0.2], PC_Z_OFFSET=0, PC_REVERSE=True,
+                         NUM_CLASSES=num_classes),
+        TRAIN=AttrDict(UNCERTAINTY_LOSS=False),
+    )
+
+
+def load_model_modules():
+    """The reference's model-side modules (unmodified): model.networks.{fusionModules,detectHeads,base_model,dla},
+    model.model, model.losses.  Returns a namespace; load_reference() has run first."""
+    ns = load_reference()
+    if "model_ns" in _loaded:
+        return _loaded["model_ns"]
+    if "tune_mode_convbn" not in sys.modules:
+        spec = importlib.util.spec_from_file_location("tune_mode_convbn", os.path.join(REF_ROOT, "src", "tune_mode_convbn.py"))
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules["tune_mode_convbn"] = mod
+        spec.loader.exec_module(mod)
+    nets = _stub("model.networks")
+    nets.__path__ = [os.path.join(REF_LIB, "model", "networks")]
+    fm = _load("model.networks.fusionModules", "model/networks/fusionModules.py")
+    dh = _load("model.networks.detectHeads", "model/networks/detectHeads.py")
+    bm = _load("model.networks.base_model", "model/networks/base_model.py")
+    dla = _load("model.networks.dla", "model/networks/dla.py")
+    mm = _load("model.model", "model/model.py")
+    losses = _load("model.losses", "model/losses.py")
+    model_pkg = sys.modules["model"]
+    # what model/__init__.py:1-2 exports (the package object here is a stub with the real __path__)
+    model_pkg.getModel, model_pkg.loadModel, model_pkg.fusionDecode = mm.getModel, getattr(mm, "loadModel", None), ns.decode.fusionDecode
+    mns = types.SimpleNamespace(ref=ns, fusionModules=fm, detectHeads=dh, base_model=bm, dla=dla, model=mm, losses=losses,
+                                model_pkg=model_pkg)
+    _loaded["model_ns"] = mns
+    return mns
+
+
+def build_model(cfg, seed=0):
+    """Random-init DLASeg (21.4 M parameters) in eval mode."""
+    import torch
+
+    mns = load_model_modules()
+    torch.manual_seed(seed)
+    m = mns.model.getModel(cfg)
+    m.eval()
+    return m

@@ -137,6 +137,51 @@ def test_golden_decode_variants(ops):
                 eq(npy(ret[k]), refv, f"{vname} {k}")
 
 
+def test_golden_cfg1_whole_model(ops):
+    """BASELINE.json configs[0] / SURVEY.md 8(c) item (3): the head maps the reference's own random-init DLA-34 forward
+    produced (CenterFusionHead.forward, detectHeads.py:165-191; fixture from tests/golden/make_golden.py
+    gen_cfg1_model) replayed through the ops that replace its calls -- getPcFrustumHeatmap, fusionDecode,
+    postProcess -- against the reference's own outputs: indices and associations bit-exact, values 1e-5."""
+    from test_oracle_golden import CFG1_HEADS
+    g = load_golden("cfg1_model")
+    K = int(g["in_K"])
+    H, W = g["in_heatmap"].shape[2:]
+    cfg = Cfg(K, float(g["in_max_pc_dist"]))
+    y = {k: cu(g["in_" + k]) for k in CFG1_HEADS}
+    pc_dep, calib = cu(g["in_pc_dep"]), cu(g["in_calib"])
+    # the call of detectHeads.py:176-177
+    eq(npy(ops.getPcFrustumHeatmap(y, pc_dep, calib, cfg)), g["out_pc_hm"], "pc_hm")
+    _, assoc, thr, _ = ops.frustum_association(y, pc_dep, calib, K, cfg.DATASET.MAX_PC_DIST)
+    known = g["out_assoc"] != -2
+    assert np.array_equal(npy(assoc)[known], g["out_assoc"][known])
+    np.testing.assert_allclose(npy(thr), g["out_thr"], rtol=RTOL_THR_REF, atol=5e-6)
+    # detector.py:414-424 / progressBar.py:96-104: fusionDecode then postProcess
+    ret = ops.fusionDecode([dict(y)], (H, W), K)
+    ref_keys = sorted(k[len("out_dec_"):] for k in g if k.startswith("out_dec_"))
+    assert sorted(ret) == ref_keys
+    for k in ref_keys:
+        eq(npy(ret[k]), g["out_dec_" + k], "decode " + k)
+    out = ops.postProcess(ret, g["in_center"], float(g["in_scale"]), H, W, calib)
+    post_keys = sorted(k[len("out_post_"):] for k in g if k.startswith("out_post_"))
+    assert sorted(out) == post_keys
+    for k in post_keys:
+        np.testing.assert_allclose(npy(out[k]), g["out_post_" + k], rtol=1e-5, atol=1e-5, err_msg="post " + k)
+    # and the fused call on the same maps
+    pc_hm2, ret2 = ops.fusion_stage(dict(y), pc_dep, calib, cfg)
+    eq(npy(pc_hm2), g["out_pc_hm"], "fused pc_hm")
+    for k in ref_keys:
+        eq(npy(ret2[k]), g["out_dec_" + k], "fused decode " + k)
+
+
+def test_get_feature_bnc_form(ops):
+    """a3, the (B,N,ch) form (model/utils.py:41-55): out[b,m,c] = feature[b,indices[b,m],c]."""
+    rng = np.random.default_rng(12)
+    feat = rng.normal(size=(3, 50, 7)).astype(np.float32)
+    ind = rng.integers(0, 50, size=(3, 11)).astype(np.int64)
+    want = np.take_along_axis(feat, ind[:, :, None].repeat(7, axis=2), axis=1)
+    eq(npy(ops.getFeature(cu(feat), cu(ind))), want, "getFeature")
+
+
 # ------------------------------------------------------------------------------------------------
 # 2. oracle differential at BASELINE.json shapes
 # ------------------------------------------------------------------------------------------------
@@ -164,6 +209,7 @@ def _check_stage(ops, oracle, wl, inp, B, need_matches=True):
     # F + D fused: one pass over the heat-map
     dec2 = to_cuda(inp, DEC_KEYS, DEV)
     pc_hm2, ret2 = ops.fusion_stage(dec2, pc_dep, calib, Cfg(wl.K, wl.max_pc_dist))
+    plan = ops.last_plan()  # of the fused call: the one bench.py measures
     eq(npy(pc_hm2), hm_o, "fused pc_hm")
     for k in ret2:
         eq(npy(ret2[k]), ret_o[k], "fused decode " + k)
@@ -173,6 +219,7 @@ def _check_stage(ops, oracle, wl, inp, B, need_matches=True):
         r = ops.topk(fwd["heatmap"], wl.K, apply_nms=apply_nms)
         for a, b, nm in zip(r, r_o, ("scores", "inds", "classes", "ys", "xs")):
             eq(npy(a), b, "topk %s nms=%s" % (nm, apply_nms))
+    return plan
 
 
 @pytest.mark.parametrize("cfg_name,B", [("cfg1", 1), ("cfg2", 4), ("cfg5", 2)])
@@ -184,16 +231,59 @@ def test_oracle_stage(ops, oracle, cfg_name, B):
 
 @pytest.mark.parametrize("cs", [1, 2, 4, 8, 16])
 @pytest.mark.parametrize("cfg_name,B", [("cfg1", 3), ("cfg5", 3)])
-def test_oracle_stage_forced_plans(ops, oracle, monkeypatch, cfg_name, B, cs):
+def test_oracle_stage_forced_plans(ops, oracle, cfg_name, B, cs):
     """Every execution plan of the fused stage kernel gives the oracle's result: cluster sizes 1..16 (heat-map share
     resident in shared memory, or streamed through the slot ring and re-fetched by the filter pass) and clusters that
-    process several frames one after the other.  The host picks the plan per call; the two environment variables
-    (development aids of stage.cu) pin it."""
-    monkeypatch.setenv("CFD3D_CLUSTER", str(cs))
-    monkeypatch.setenv("CFD3D_MAX_CLUSTERS", "2")
+    process several frames one after the other.  The host picks the plan per call; the ABI's test hook
+    (cf_debug_set_plan) pins it."""
     wl = syn.WORKLOADS[cfg_name]
     inp = make_case(wl, B)
+    ops.debug_set_plan(cs, 2)
+    try:
+        plan = _check_stage(ops, oracle, wl, inp, B)
+        assert plan["cluster_size"] == cs and plan["n_clusters"] == 2 and plan["rounds"] == 2, plan
+    finally:
+        ops.debug_set_plan(0, 0)
+
+
+# the plans bench.py runs (no forcing): workload, frames per GPU, expected (cluster size, resident share, staged plane)
+BENCH_PLANS = [("cfg2", 32, dict(cluster_size=4, n_clusters=32, rounds=1, resident=1, depth_plane_staged=1)),
+               ("cfg3", 256, None),
+               ("cfg4", 64, dict(cluster_size=4, resident=1, depth_plane_staged=1, rounds=2)),
+               ("cfg5", 8, dict(n_clusters=8, rounds=1))]
+
+
+@pytest.mark.parametrize("cfg_name,B,expect", BENCH_PLANS)
+def test_oracle_stage_bench_shapes(ops, oracle, cfg_name, B, expect):
+    """Oracle differential at the EXACT batch sizes and execution plans bench.py measures (BASELINE.json configs 2-5:
+    the planner chooses from B, so small-batch tests do not reach these plans).  The chosen plan is asserted through
+    cf_last_plan so that a planner change cannot silently move this test off the benchmarked path."""
+    wl = syn.WORKLOADS[cfg_name]
+    inp = make_case(wl, B, seed=4242)
+    ops.debug_set_plan(0, 0)
+    plan = _check_stage(ops, oracle, wl, inp, B)
+    for k, v in (expect or {}).items():
+        assert plan[k] == v, (cfg_name, k, plan)
+    n_sm = torch.cuda.get_device_properties(0).multi_processor_count
+    assert plan["n_clusters"] * plan["cluster_size"] <= n_sm
+    if expect is None:  # cfg3 on one GPU: more frames than clusters -> every cluster loops over several frames
+        assert plan["rounds"] >= 2 and plan["n_clusters"] * plan["cluster_size"] > n_sm // 2, plan
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3, 4, 5, 6, 7, 8])
+def test_oracle_stage_seeds_and_plans(ops, oracle, seed):
+    """Seeded stress (tools/stress_parity.py folded into the suite): a fresh cfg2-shaped case per seed, run under the
+    planner's plan and under a forced plan that changes with the seed (cluster size x frames per cluster)."""
+    wl = syn.WORKLOADS["cfg2"]
+    B = 2 + seed % 4
+    inp = make_case(wl, B, seed=9000 + 17 * seed)
     _check_stage(ops, oracle, wl, inp, B)
+    cs = (1, 2, 4, 8, 16)[seed % 5]
+    ops.debug_set_plan(cs, 1 + seed % 3)
+    try:
+        _check_stage(ops, oracle, wl, inp, B)
+    finally:
+        ops.debug_set_plan(0, 0)
 
 
 def test_paint_into_combiner_input(ops, oracle):

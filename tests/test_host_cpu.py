@@ -25,6 +25,7 @@ def lib():
 
 def declared_symbols():
     txt = open(HEADER).read()
+    txt = re.sub(r"#ifdef CFD3D_PROFILE.*?#endif", "", txt, flags=re.S)  # development build only
     return sorted(set(re.findall(r"CF_API\s+[\w\s\*]+?\b(cf_\w+)\s*\(", txt)))
 
 
@@ -83,6 +84,8 @@ def test_missing_library_fails_loudly(monkeypatch, lib):
 
 
 def test_patch_swaps_and_restores_reference_names():
+    """Mock modules (the real-tree version is tests/test_patch_reference.py): every swapped name is a dispatcher that
+    sends CUDA fp32 no-grad tensors to the op and everything else to the original."""
     from centerfusiondetect3d_b200 import ops, patch
 
     def mk(**kw):
@@ -91,19 +94,28 @@ def test_patch_swaps_and_restores_reference_names():
             setattr(m, k, v)
         return m
 
-    o = {n: (lambda *a, _n=n: _n) for n in ("getPcFrustumHeatmap", "cvtPcDepthToHeatmap", "nms", "topk",
-                                              "transposeAndGetFeature", "fusionDecode")}
+    o = {n: (lambda *a, _n=n, **k: _n) for n in ("getPcFrustumHeatmap", "cvtPcDepthToHeatmap", "nms", "topk",
+                                                   "transposeAndGetFeature", "fusionDecode", "get_alpha")}
     mods = {"utils.pointcloud": mk(getPcFrustumHeatmap=o["getPcFrustumHeatmap"], cvtPcDepthToHeatmap=o["cvtPcDepthToHeatmap"],
-                                   topk=o["topk"], transposeAndGetFeature=o["transposeAndGetFeature"]),
+                                   topk=o["topk"], transposeAndGetFeature=o["transposeAndGetFeature"], get_alpha=o["get_alpha"]),
             "model.utils": mk(nms=o["nms"], topk=o["topk"], transposeAndGetFeature=o["transposeAndGetFeature"]),
             "model.decode": mk(fusionDecode=o["fusionDecode"], nms=o["nms"], topk=o["topk"]),
+            "model.losses": mk(transposeAndGetFeature=o["transposeAndGetFeature"], get_alpha=o["get_alpha"]),
             "detector": mk(fusionDecode=o["fusionDecode"])}
     undo = patch.apply(mods)
-    assert mods["utils.pointcloud"].getPcFrustumHeatmap is ops.getPcFrustumHeatmap
-    assert mods["model.utils"].topk is ops.topk and mods["model.decode"].nms is ops.nms
-    assert mods["detector"].fusionDecode is ops.fusionDecode
-    # NumPy inputs keep the reference's own code (training-target path), CUDA tensors would go to the kernel
+    assert mods["utils.pointcloud"].getPcFrustumHeatmap.__cfd3d_op__ is ops.getPcFrustumHeatmap
+    assert mods["model.utils"].topk.__cfd3d_op__ is ops.topk and mods["model.decode"].nms.__cfd3d_op__ is ops.nms
+    assert mods["detector"].fusionDecode.__cfd3d_op__ is ops.fusionDecode
+    assert mods["model.utils"].topk is mods["model.decode"].topk       # one dispatcher per original
+    # the training losses keep the reference's autograd-capable functions (model/losses.py:15,18)
+    assert mods["model.losses"].transposeAndGetFeature is o["transposeAndGetFeature"]
+    assert mods["model.losses"].get_alpha is o["get_alpha"]
+    # NumPy, CPU tensors, non-fp32 and grad-requiring tensors keep the reference's own code
     assert mods["utils.pointcloud"].cvtPcDepthToHeatmap(np.zeros((3, 2, 2)), None, 0, None, 0, 60) == "cvtPcDepthToHeatmap"
+    assert mods["model.utils"].topk(torch.rand(1, 1, 2, 2), K=2) == "topk"
+    assert mods["utils.pointcloud"].get_alpha(rotation=torch.rand(2, 8)) == "get_alpha"
+    assert not patch.takes_cuda_path(np.zeros(3)) and not patch.takes_cuda_path(torch.zeros(3))
+    assert not patch.takes_cuda_path() and not patch.takes_cuda_path({"a": None})
     undo()
     assert mods["utils.pointcloud"].getPcFrustumHeatmap is o["getPcFrustumHeatmap"]
     assert mods["model.utils"].topk is o["topk"] and mods["detector"].fusionDecode is o["fusionDecode"]

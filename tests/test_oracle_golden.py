@@ -135,3 +135,32 @@ def test_post_process_variants(oracle):
     # a detection with a non-positive dimension has its 3-D box zeroed (postProcess.py:81)
     _, _, ref = post_case(g, "amodal")
     assert not ref["bboxes3d"][0, 3].any() and not ref["bboxes3d"][1, 5].any()
+
+
+CFG1_HEADS = ("heatmap", "reg", "widthHeight", "depth", "depth2", "rotation", "rotation2", "dimension",
+              "amodal_offset", "nuscenes_att", "velocity")
+
+
+def test_cfg1_whole_model_fixture(oracle):
+    """BASELINE.json configs[0]: head maps produced by the reference's own random-init DLA-34 forward (Recipe B,
+    tests/golden/make_golden.py gen_cfg1_model) -- the oracle reproduces the reference's pc_hm (also what
+    CenterFusionHead.forward itself emitted), association indices, fusionDecode and postProcess outputs on them."""
+    g = load_golden("cfg1_model")
+    K = int(g["in_K"])
+    H, W = g["in_heatmap"].shape[2:]
+    pc_hm, assoc, thr, _ = oracle.frustum_pc_hm(g["in_heatmap"], g["in_widthHeight"], g["in_depth"], g["in_dimension"],
+                                                g["in_rotation"], g["in_pc_dep"], g["in_calib"], K,
+                                                float(g["in_max_pc_dist"]))
+    np.testing.assert_allclose(thr, g["out_thr"], rtol=2e-5, atol=5e-6)
+    known = g["out_assoc"] != -2
+    assert np.array_equal(assoc[known], g["out_assoc"][known])
+    assert (g["out_assoc"] >= 0).sum() >= 10 and (g["in_widthHeight"] < 0).any()
+    assert np.array_equal(pc_hm.view(np.uint32), g["out_pc_hm"].view(np.uint32))
+    ret = oracle.fusion_decode({k: g["in_" + k] for k in CFG1_HEADS}, (H, W), K)
+    ref_keys = sorted(k[len("out_dec_"):] for k in g if k.startswith("out_dec_"))
+    assert sorted(k for k in ret if not k.startswith("_")) == ref_keys
+    for k in ref_keys:
+        assert np.array_equal(ret[k].view(np.uint32), g["out_dec_" + k].view(np.uint32)), k
+    post = oracle.post_process({k: g["out_dec_" + k].copy() for k in ref_keys}, g["in_trans"], (H, W), g["in_calib"], False)
+    for k in (k[len("out_post_"):] for k in g if k.startswith("out_post_")):
+        np.testing.assert_allclose(post[k], g["out_post_" + k], rtol=1e-5, atol=1e-5, err_msg=k)

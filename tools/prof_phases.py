@@ -5,6 +5,8 @@ import sys
 
 os.environ["CFD3D_PROF"] = "1"
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+# the instrumented build (python -m centerfusiondetect3d_b200.build --prof); the product library has no phase clocks
+os.environ.setdefault("CFD3D_LIB", os.path.join(ROOT, "centerfusiondetect3d_b200", "libcfd3d_b200_prof.so"))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np

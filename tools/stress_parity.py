@@ -20,12 +20,7 @@ runs = 0
 for seed in range(n_seeds):
     for cfg_name, B in (("cfg2", 5), ("cfg1", 3), ("cfg5", 2)):
         for cs in (0, 1, 2, 4, 8, 16):
-            if cs:
-                os.environ["CFD3D_CLUSTER"] = str(cs)
-                os.environ["CFD3D_MAX_CLUSTERS"] = "2"
-            else:
-                os.environ.pop("CFD3D_CLUSTER", None)
-                os.environ.pop("CFD3D_MAX_CLUSTERS", None)
+            ops.debug_set_plan(cs, 2 if cs else 0)
             if cfg_name == "cfg5" and cs in (1, 2) and seed % 4:
                 continue  # (slow on the oracle side; every fourth seed is enough)
             wl = syn.WORKLOADS[cfg_name]
