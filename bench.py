@@ -13,7 +13,13 @@ frames and the data path has no collective ("scaling": "weak": B frames per GPU 
 Timing: CUDA events on the launching stream around exactly K steps, barrier + synchronize on both sides, max over
 ranks.  Cold-cache discipline: the step rotates through NSETS distinct resident input sets whose fully-read maps
 (heat-map + pc_dep) together exceed 2x the 126 MB L2, so no step finds its inputs in L2 ("l2": "rotating_inputs").
-The timed loop replays one CUDA graph per input set (4 kernels each); nothing is allocated or synchronised inside.
+The timed region is ONE CUDA-graph launch whose nodes are the K steps (one fused kernel each; cfg4 adds the two pillar
+kernels); nothing is allocated, launched from the host or synchronised inside it.
+
+Both arms (--impl native / reference) print the same `config` dict; run-time details of the native arm go to `run`.
+At N > 1 the line also carries per-rank step times (min / median / max), the NCCL gather of the detections for
+reporting (shard.gather_detections: microseconds, bytes, checked on rank 0), per-rank H2D rates of the e2e leg and, as
+`config3_strong`, BASELINE config 3's split (256 frames over the N GPUs) timed the same way.
 """
 from __future__ import annotations
 
@@ -46,14 +52,33 @@ def algorithmic_bytes_per_frame(wl, with_pillars: bool) -> int:
     return b
 
 
-def peak_select_bytes_per_frame(wl) -> int:
-    """Dominant kernel (peak_select): reads the heat-map once, writes two K-candidate lists per (class, band)."""
-    return 4 * wl.H * wl.W * wl.C
-
-
 # --------------------------------------------------------------------------------------------------------
 # clocks
 # --------------------------------------------------------------------------------------------------------
+def bind_to_gpu_numa(index: int) -> str:
+    """Pins this process to the CPUs NVML reports as local to its GPU before any pinned buffer is allocated (first-touch
+    puts the pages on that NUMA node), so that at N > 1 every rank's H2D traffic starts from its own socket.  Returns a
+    note for the record; a host that reports one node for every GPU is left as it is."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        phys = int(vis.split(",")[index]) if vis and vis.split(",")[index].isdigit() else index
+        h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+        cpus = {w * 64 + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+        allowed = set(os.sched_getaffinity(0))
+        want = (cpus & allowed) or allowed
+        if want != allowed:
+            os.sched_setaffinity(0, want)
+        return "gpu %d: %d local cpus of %d allowed%s" % (phys, len(cpus & allowed), len(allowed),
+                                                          " (bound)" if want != allowed else " (all local: unchanged)")
+    except Exception as e:  # pragma: no cover
+        return "unavailable: %r" % (e,)
+
+
 class ClockSampler:
     """Samples SM clock and throttle reasons through NVML while the timed region runs."""
 
@@ -139,6 +164,19 @@ def make_host_inputs(wl, B: int, seed: int):
     return inp
 
 
+def config_dict(wl, B: int, world: int) -> dict:
+    """What both arms measure (identical dict from --impl native and --impl reference)."""
+    return {"workload": wl.name, "frames_per_gpu_per_step": B, "global_frames_per_step": B * world, "K": wl.K,
+            "classes": wl.C, "map": [wl.H, wl.W], "radar_points": wl.n_radar,
+            "stage": ("radar_pillars + " if wl.with_pillars else "") + "getPcFrustumHeatmap + fusionDecode"}
+
+
+# BASELINE.md section 2: the unmodified Python reference measured in the survey container (it cannot travel to the GPU box)
+PY_REFERENCE_NOTE = ("the unmodified Python reference (getPcFrustumHeatmap alone, 8 torch threads, survey container, "
+                     "BASELINE.md section 2) ran 11.3 frames/s at 112x200 / K=100 and 7.9 frames/s at 225x400 / K=500: "
+                     "the C/OpenMP port timed here is ~500x faster than it, i.e. a conservative baseline")
+
+
 STAGE_KEYS = ("heatmap", "reg", "widthHeight", "depth", "depth2", "rotation", "rotation2", "dimension",
               "amodal_offset", "nuscenes_att", "velocity")
 PILLAR_KEYS = ("radar_points", "radar_counts", "cam", "calib64", "A_out")
@@ -207,7 +245,7 @@ def cpu_baseline(wl, inp, B, budget_s=12.0, min_reps=2):
     dt = time.perf_counter() - t0
     return {"value": B * reps / dt, "unit": UNIT, "cores": threads, "kind": "port",
             "sample": "%d passes over one %d-frame batch of %s (oracle/cfd3d_oracle.c, OpenMP over frames x classes, "
-                      "%.1f s)" % (reps, B, wl.name, dt)}
+                      "%.1f s); %s" % (reps, B, wl.name, dt, PY_REFERENCE_NOTE)}
 
 
 def run_reference_arm(args, wl, B):
@@ -238,11 +276,11 @@ def run_reference_arm(args, wl, B):
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps_eff,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / steps_eff, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl.name, "frames_per_step": B, "K": wl.K, "map": [wl.H, wl.W], "radar_points": wl.n_radar,
-                   "note": "reference algorithm on host CPU cores (C/OpenMP port in oracle/; the Python reference "
-                           "cannot travel to the GPU box); rank 0 only"},
+        "config": config_dict(wl, B, int(os.environ.get("WORLD_SIZE", "1"))),
+        "note": "reference algorithm on host CPU cores (C/OpenMP port in oracle/; the Python reference cannot travel to "
+                "the GPU box); rank 0 only, one batch of frames_per_gpu_per_step frames per step",
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": "%d passes over one %d-frame batch" % (steps_eff, B)},
+                         "sample": "%d passes over one %d-frame batch; %s" % (steps_eff, B, PY_REFERENCE_NOTE)},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -310,6 +348,8 @@ def main() -> int:
     assert torch.cuda.is_available(), "bench.py (native arm) needs a CUDA device: there is no CPU fallback"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # (N = 1 keeps the whole affinity mask: the cpu_baseline leg of this process uses every host core)
+    affinity_note = bind_to_gpu_numa(local) if world > 1 else "not bound (single rank)"
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     from centerfusiondetect3d_b200 import _lib, ops
@@ -325,24 +365,24 @@ def main() -> int:
         sets.append({k: torch.from_numpy(np.ascontiguousarray(np.roll(host[k], j, axis=0))).to(dev) for k in keys})
     torch.cuda.synchronize()
 
-    # -- correctness guard: the bench measures a path that agrees with the oracle on its own inputs (small sample) --
+    # -- correctness guard: the measured call agrees with the oracle on the bench's own inputs, ALL B frames of input set 0,
+    #    under the very execution plan the timed loop runs (same shapes, same batch) ------------------------------------
+    plan = None
     if rank == 0 and not os.environ.get("CFD3D_STOP_AFTER"):
         from oracle import binding as ob
 
-        nb = min(B, 2)
-        sub = {k: (v[:nb] if isinstance(v, np.ndarray) and v.ndim and v.shape[0] == B else v) for k, v in host.items()}
-        d_sub = {k: torch.from_numpy(np.ascontiguousarray(sub[k])).to(dev) for k in keys}
-        hm, ret, _ = run_stage(ops, wl, d_sub, cfg)
-        ob.set_threads(min(ob.max_threads(), 8))
-        hm_o = ob.frustum_pc_hm(sub["heatmap"], sub["widthHeight"], sub["depth"], sub["dimension"], sub["rotation"],
-                                sub["pc_dep"], sub["calib"], wl.K, wl.max_pc_dist)[0]
-        ret_o = ob.fusion_decode({k: sub[k] for k in STAGE_KEYS}, (wl.H, wl.W), wl.K)
+        hm, ret, _ = run_stage(ops, wl, sets[0], cfg)
+        plan = ops.last_plan()
+        ob.set_threads(host_threads())
+        hm_o = ob.frustum_pc_hm(host["heatmap"], host["widthHeight"], host["depth"], host["dimension"], host["rotation"],
+                                host["pc_dep"], host["calib"], wl.K, wl.max_pc_dist)[0]
+        ret_o = ob.fusion_decode({k: host[k] for k in STAGE_KEYS}, (wl.H, wl.W), wl.K)
         torch.cuda.synchronize()
-        check_ok = bool(np.array_equal(hm.cpu().numpy(), hm_o)) and all(
-            np.array_equal(v.cpu().numpy(), ret_o[k]) for k, v in ret.items() if k != "scores") and bool(
-            np.array_equal(ret["scores"].cpu().numpy(), ret_o["scores"]))
+        check_ok = bool(np.array_equal(hm.cpu().numpy().view(np.uint32), hm_o.view(np.uint32))) and all(
+            np.array_equal(v.cpu().numpy().view(np.uint32), ret_o[k].view(np.uint32)) for k, v in ret.items())
+        check_frames = B
     else:
-        check_ok = True
+        check_ok, check_frames = True, 0
 
     # -- capture one CUDA graph per input set -----------------------------------------------------------------
     launches_per_step = 0
@@ -370,6 +410,17 @@ def main() -> int:
             with torch.cuda.graph(cycle, stream=stream):
                 cycle_outs = [run_stage(ops, wl, s, cfg) for s in sets]
 
+    # The timed region itself: ONE graph whose nodes are the K steps (set i % nsets at step i), so that no host-side
+    # launch sits inside a sub-millisecond window (at N > 1 the ranks' Python processes contend for the host).  The
+    # steps' outputs are dropped as they are captured: the graph's private pool reuses their memory step after step.
+    timed = None
+    if graphs and not args.no_cycle_graph and args.steps <= 8192:
+        with torch.cuda.stream(stream):
+            timed = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(timed, stream=stream):
+                for i in range(args.steps):
+                    run_stage(ops, wl, sets[i % nsets], cfg)
+
     def step(i):
         if graphs:
             graphs[i % nsets].replay()
@@ -394,19 +445,27 @@ def main() -> int:
 
     with torch.cuda.stream(stream):
         run_steps(max(args.warmup, 3))
+        if timed is not None:
+            timed.replay()  # (untimed: the graph's first launch uploads it)
         barrier()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         clocks = ClockSampler(local)
         with clocks:
             ev0.record(stream)
-            run_steps(args.steps)
+            if timed is not None:
+                timed.replay()
+            else:
+                run_steps(args.steps)
             ev1.record(stream)
             barrier()
         ms = ev0.elapsed_time(ev1)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    per_rank_ms = [ms]
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        per_rank_ms = [float(x.item()) for x in allt]
+    ms_max = max(per_rank_ms)
     frames_total = B * world * args.steps
     value = frames_total / (ms_max * 1e-3)
 
@@ -416,9 +475,7 @@ def main() -> int:
     if rank == 0:
         n_roof = min(args.steps, 100)
         L = _lib.lib()
-        legacy = bool(os.environ.get("CFD3D_LEGACY"))
-        kernel_ids = ({"peak_bound": 0, "peak_filter": 5, "merge": 1, "assoc": 2, "paint": 3} if legacy
-                      else {"fusion_stage": 6})
+        kernel_ids = {"fusion_stage": 6}  # CF_KERNEL_STAGE
         kernel_us = {}
         for kname, kid in kernel_ids.items():
             pairs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_roof)]
@@ -441,14 +498,14 @@ def main() -> int:
                 stream.synchronize()
             d = np.array([a.elapsed_time(b) for a, b in pairs]) * 1e3
             kernel_us[kname] = {"mean": float(d.mean()), "min": float(d.min()), "median": float(np.median(d))}
-        dom = "peak_bound" if legacy else "fusion_stage"
+        dom = "fusion_stage"
         dur = kernel_us[dom]["mean"] * 1e-6
         timed_how = "CUDA events the ABI records around the kernel (cf_set_kernel_events), one launch at a time"
-        if not legacy and launches_per_step == 1:
+        if launches_per_step == 1:
             # the step IS this one kernel: its average duration over the timed region (graph replay, events on the
             # launching stream) is the step time itself; the event-pair figure above includes ~5 us of event overhead
             dur = ms_max * 1e-3 / args.steps
-            timed_how = "the timed region itself: one kernel per step, CUDA events around %d graph replays" % args.steps
+            timed_how = "the timed region itself: one kernel per step, CUDA events around one graph launch of %d steps" % args.steps
         peaks = {}
         pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         peak, peak_src = 6650.0, "fallback"
@@ -459,7 +516,7 @@ def main() -> int:
             except Exception:
                 pass
         # the fused kernel is the whole stage (SURVEY.md 8d bytes per frame, pillar bytes excluded: separate kernels)
-        alg = (peak_select_bytes_per_frame(wl) if legacy else algorithmic_bytes_per_frame(wl, False)) * B
+        alg = algorithmic_bytes_per_frame(wl, False) * B
         ach = alg / dur / 1e9
         stage_alg = algorithmic_bytes_per_frame(wl, wl.with_pillars) * B
         stage_ach = stage_alg / (ms_max * 1e-3 / args.steps) / 1e9
@@ -473,7 +530,7 @@ def main() -> int:
         roof = {"bound": "hbm", "kernel": dom + "_kernel", "achieved": ach, "peak": peak, "unit": "GB/s",
                 "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg, "kernel_us": dur * 1e6,
-                "launches_timed": args.steps if launches_per_step == 1 and not legacy else n_roof, "timed": timed_how,
+                "launches_timed": args.steps if launches_per_step == 1 else n_roof, "timed": timed_how,
                 "l2": "rotating input sets larger than 2 x L2",
                 "kernels_us": kernel_us,
                 "stage": {"algorithmic_bytes_per_step": stage_alg, "achieved": stage_ach, "frac": stage_ach / peak}}
@@ -559,10 +616,74 @@ def main() -> int:
     wall_ms = (time.perf_counter() - t0) * 1e3
     e2e_ms = max(e2e_ms, 0.0)
     t = torch.tensor([e2e_ms, wall_ms], dtype=torch.float64, device=dev)
+    e2e_rank_ms = [e2e_ms]
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        alle = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(alle, t)
+        e2e_rank_ms = [float(x[0].item()) for x in alle]
+        t = torch.stack(alle).max(dim=0).values
     e2e_ms_max = float(t[0].item())
     e2e_val = B * world * e2e_steps / (e2e_ms_max * 1e-3)
+    # achieved host -> device rate of every rank over its own e2e region (copied bytes only): at N > 1 the ranks share
+    # the host's memory and PCIe root, which is what bounds this leg
+    h2d_gbs_per_rank = [h2d_copied * e2e_steps / (m * 1e-3) / 1e9 for m in e2e_rank_ms]
+
+    # -- reporting only: the detections of all ranks gathered over NCCL (shard.gather_detections replaces the reference's
+    #    all_gather of the whole head-output dict, model/progressBar.py:85-91); untimed by the bench metric ------------
+    gather_info = None
+    if world > 1:
+        from centerfusiondetect3d_b200.shard import gather_detections
+
+        _, ret_g, _ = run_stage(ops, wl, sets[0], cfg)
+        ret_g = {k: v.clone() for k, v in ret_g.items()}
+        gather_detections(ret_g)  # warm-up (communicator set-up)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        full = gather_detections(ret_g)
+        g1.record()
+        torch.cuda.synchronize()
+        g_us = torch.tensor([g0.elapsed_time(g1) * 1e3], dtype=torch.float64, device=dev)
+        dist.all_reduce(g_us, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            ok = all(tuple(v.shape[1:]) == tuple(ret_g[k].shape[1:]) and v.shape[0] == B * world for k, v in full.items())
+            ok = ok and all(torch.equal(full[k][:B], ret_g[k]) for k in ret_g)  # rank 0's shard leads the gathered tensor
+            # every rank decoded a rolled copy of a seeded batch: scores of every gathered frame are sorted and finite
+            sc = full["scores"]
+            ok = ok and bool(torch.isfinite(sc).all()) and bool((sc[:, :-1] >= sc[:, 1:]).all())
+            gather_info = {"us": float(g_us.item()), "bytes_per_rank": int(sum(v.numel() * v.element_size() for v in ret_g.values())),
+                           "gathered_frames": int(sc.shape[0]), "tensors": len(full), "checked": bool(ok),
+                           "how": "shard.gather_detections: all_gather_into_tensor of the (B_local, K, .) detection tensors "
+                                  "over NCCL, after the timed region (reporting only)"}
+
+    # -- BASELINE config 3 as written (256 frames split over the N GPUs: strong scaling), timed like the main region --
+    strong = None
+    if world > 1 and wl.name.startswith("cfg2") and not os.environ.get("CFD3D_NO_STRONG"):
+        Bs = max(1, 256 // world)
+        reps = -(-Bs // B)
+        big = {k: torch.cat([sets[r % nsets][k] for r in range(reps)], 0)[:Bs].contiguous() for k in keys}
+        bigs = [big, {k: torch.roll(v, 1, 0) for k, v in big.items()}]
+        with torch.cuda.stream(stream):
+            for sset in bigs:
+                run_stage(ops, wl, sset, cfg)
+            stream.synchronize()
+            n_st = 20
+            gs = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gs, stream=stream):
+                for i in range(n_st):
+                    run_stage(ops, wl, bigs[i % 2], cfg)
+            gs.replay()
+            barrier()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record(stream)
+            gs.replay()
+            s1.record(stream)
+            barrier()
+        st = torch.tensor([s0.elapsed_time(s1)], dtype=torch.float64, device=dev)
+        dist.all_reduce(st, op=dist.ReduceOp.MAX)
+        strong = {"workload": "cfg3: 256 frames split over the GPUs", "frames_per_gpu_per_step": Bs, "steps": n_st,
+                  "ms_per_step": float(st.item()) / n_st, "value": Bs * world * n_st / (float(st.item()) * 1e-3), "unit": UNIT,
+                  "scaling": "strong"}
 
     if rank == 0:
         cpu = None if args.no_cpu or world > 1 else cpu_baseline(wl, host, B)
@@ -570,15 +691,18 @@ def main() -> int:
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_max / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl.name, "frames_per_gpu_per_step": B, "global_frames_per_step": B * world,
-                       "K": wl.K, "classes": wl.C, "map": [wl.H, wl.W], "radar_points": wl.n_radar,
-                       "stage": ("radar_pillars + " if wl.with_pillars else "") + "getPcFrustumHeatmap + fusionDecode",
-                       "l2": "rotating_inputs", "input_sets": nsets, "cuda_graph": not args.no_graph, "graph_steps_per_launch": (nsets if cycle is not None else 1),
-                       "parallelism": "frames sharded across ranks, no data-path collective"},
+            "config": config_dict(wl, B, world),
+            "run": {"l2": "rotating_inputs", "input_sets": nsets, "cuda_graph": not args.no_graph,
+                    "graph_steps_per_launch": (args.steps if timed is not None else (nsets if cycle is not None else 1)),
+                    "parallelism": "frames sharded across ranks, no data-path collective", "plan": plan,
+                    "cpu_affinity": affinity_note},
+            "per_rank_ms_per_step": {"min": min(per_rank_ms) / args.steps, "median": float(np.median(per_rank_ms)) / args.steps,
+                                     "max": max(per_rank_ms) / args.steps, "all": [m / args.steps for m in per_rank_ms]},
             "clocks": clocks.summary(),
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": e2e_steps, "ms_per_step": e2e_ms_max / e2e_steps, "wall_ms_per_step": float(t[1].item()) / e2e_steps,
                     "h2d_copied_bytes_per_step": h2d_copied, "heads_read_in_place": zero_keys,
+                    "per_rank_ms_per_step": [m / e2e_steps for m in e2e_rank_ms], "h2d_gbs_per_rank": h2d_gbs_per_rank,
                     "how": "ops.fusion_stage from pinned host buffers; 3-deep pipeline over copy-in / compute / "
                            "copy-out streams; every step copies the fully-read inputs (heat-map, depth plane of pc_dep / radar "
                            "points, calib) H2D and pc_hm + detections D2H; the gather-only heads and the velocity planes "
@@ -591,6 +715,9 @@ def main() -> int:
             "roofline": roof,
             "cpu_baseline": cpu,
             "parity_check": check_ok,
+            "parity_check_frames": check_frames,
+            "detection_gather": gather_info,
+            "config3_strong": strong,
         }
         emit_line(line)
     if world > 1:

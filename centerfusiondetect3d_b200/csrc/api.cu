@@ -213,6 +213,7 @@ static int check_decode_args(const cf_decode_heads_t* h, const cf_decode_out_t* 
     if ((h->wh && !o->bboxes) || (h->depth && !o->depth) || (h->rot && !o->rot) || (h->dim && !o->dim) ||
         (h->amodal && !o->amodal) || (h->nuscenes_att && !o->nuscenes_att) || (h->velocity && !o->velocity))
         return fail(CF_E_NULL, "decode: a head is present but its output pointer is NULL");
+    if (o->bboxes && (reinterpret_cast<uintptr_t>(o->bboxes) & 15u)) return fail(CF_E_ALIGN, "decode: bboxes must be 16-byte aligned");
     return 0;
 }
 
@@ -357,6 +358,28 @@ int cf_frustum_boxes(const float* pc_dep, const float* bboxes, const float* dept
     CF_KERNEL(CF_KERNEL_ASSOC, st,
               launch_box_assoc(pc_dep, bboxes, depth, thr, counts, B, N, H, W, max_pc_dist, (PaintRec*)ws, assoc, st, &n),
               "box_assoc");
+    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint((const PaintRec*)ws, N, N, counts, B, H, W, pc_hm, nullptr, st, &n), "paint");
+    g_launches = n;
+    return 0;
+}
+
+int cf_frustum_boxes_f64(const float* pc_dep, const double* bboxes, const double* depth, const double* thr,
+                         const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, int flags, float* pc_hm,
+                         int32_t* assoc, void* ws, size_t ws_bytes, void* stream) {
+    g_launches = 0;
+    if (!pc_dep || !pc_hm || (N > 0 && (!bboxes || !depth || !thr))) return fail(CF_E_NULL, "cf_frustum_boxes_f64: NULL pointer");
+    if (B < 0 || N < 0 || H < 1 || W < 1 || H > 32767 || W > 32767) return fail(CF_E_SHAPE, "cf_frustum_boxes_f64: bad shape");
+    if (flags & ~(CF_BOX_F32 | CF_THR_F32)) return fail(CF_E_SHAPE, "cf_frustum_boxes_f64: unknown flag");
+    const size_t need = (size_t)B * N * sizeof(PaintRec);
+    if (need) {
+        if (int rc = check_ws(ws, ws_bytes, need)) return rc;
+    }
+    if (B == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    int n = 0;
+    CF_KERNEL(CF_KERNEL_ASSOC, st,
+              launch_box_assoc_np(pc_dep, bboxes, depth, thr, counts, B, N, H, W, max_pc_dist, flags, (PaintRec*)ws, assoc, st, &n),
+              "box_assoc_np");
     CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint((const PaintRec*)ws, N, N, counts, B, H, W, pc_hm, nullptr, st, &n), "paint");
     g_launches = n;
     return 0;

@@ -102,6 +102,86 @@ cudaError_t launch_box_assoc(const float* pc_dep, const float* bboxes, const flo
     return e;
 }
 
+// f4 on the reference's own branch: the NumPy form of cvtPcDepthToHeatmap as the DataLoader calls it
+// (dataset/generic_dataset.py:673-687, utils/pointcloud.py:411-481 with lib = np) under NumPy >= 2 promotion.  Boxes,
+// depths and thresholds arrive as float64 (the exact container of either dtype); `flags` says which arithmetic the
+// caller's dtypes select: CF_BOX_F32 -- the box was float32 (transformBbox, generic_dataset.py:507-526): centre, 0.3 * w
+// and the int() of the paint window are float32 operations, else the centre is rounded to float32 and the rest is float64;
+// CF_THR_F32 -- the threshold was np.float32 (what getDistanceThresh's NumPy branch returns): depth +- thr and the two
+// strict compares are float32, else float64 on the exactly widened pixel.  One warp per box.
+__global__ void __launch_bounds__(BW * 32) box_assoc_np_kernel(const float* __restrict__ pc_dep, const double* __restrict__ bboxes,
+                                                               const double* __restrict__ depth, const double* __restrict__ thr,
+                                                               const int32_t* __restrict__ counts, int N, int H, int W,
+                                                               float max_pc_dist, int flags, PaintRec* __restrict__ recs,
+                                                               int32_t* __restrict__ assoc) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n = blockIdx.x * BW + warp, b = blockIdx.y;
+    if (n >= N) return;
+    const size_t o = (size_t)b * N + n;
+    const float* dep = pc_dep + (size_t)b * 3 * H * W;
+    unsigned long long best = ~0ull;
+    DetParam d;
+    d.x1 = d.y1 = d.x2 = d.y2 = d.depth = d.thr = 0.0f;
+    d.ra = d.rb = d.ca = d.cb = 0;
+    const bool live = !counts || n < counts[b];
+    if (live) {
+        const double x1 = __ldg(bboxes + 4 * o), y1 = __ldg(bboxes + 4 * o + 1), x2 = __ldg(bboxes + 4 * o + 2),
+                     y2 = __ldg(bboxes + 4 * o + 3);
+        const double dp = __ldg(depth + o), th = __ldg(thr + o);
+        int ya, yb, xa, xb;
+        pyslice((long long)floor(y1), (long long)ceil(y2) + 1, H, ya, yb);
+        pyslice((long long)floor(x1), (long long)ceil(x2) + 1, W, xa, xb);
+        double hi = __dadd_rn(dp, th), lo = __dsub_rn(dp, th);
+        if (flags & CF_THR_F32) {
+            hi = (double)__fadd_rn((float)dp, (float)th);
+            lo = (double)__fsub_rn((float)dp, (float)th);
+        }
+        if (!(lo > 0.0)) lo = 0.0;  // python max(0, t)
+        if (ya < yb && xa < xb) {
+            const int w = xb - xa, cnt = (yb - ya) * w;
+            for (int i = lane; i < cnt; i += 32) {
+                const int ry = i / w, yy = ya + ry, xx = xa + (i - ry * w);
+                const float v = dep[(size_t)yy * W + xx];
+                if (v != 0.0f && (double)v < hi && (double)v > lo) {
+                    const unsigned long long key =
+                        ((unsigned long long)__float_as_uint(v) << 32) | (unsigned long long)(uint32_t)(yy * W + xx);
+                    best = key < best ? key : best;
+                }
+            }
+        }
+        best = warp_min_u64(best);
+        int ra, rb, ca, cb;
+        if (flags & CF_BOX_F32) {
+            paint_window((float)x1, (float)y1, (float)x2, (float)y2, H, W, ra, rb, ca, cb);
+        } else {
+            const float cx = (float)__ddiv_rn(__dadd_rn(x1, x2), 2.0), cy = (float)__ddiv_rn(__dadd_rn(y1, y2), 2.0);
+            const double hw_ = __ddiv_rn(__dmul_rn(0.3, __dsub_rn(x2, x1)), 2.0);
+            const double hh_ = __ddiv_rn(__dmul_rn(0.3, __dsub_rn(y2, y1)), 2.0);
+            const long long wmin = (long long)__dsub_rn((double)cx, hw_), wmax = (long long)__dadd_rn((double)cx, hw_);
+            const long long hmin = (long long)__dsub_rn((double)cy, hh_), hmax = (long long)__dadd_rn((double)cy, hh_);
+            pyslice(hmin, hmax + 1, H, ra, rb);
+            pyslice(wmin, wmax + 2, W, ca, cb);
+        }
+        const bool ok = ra < rb && ca < cb;
+        d.ra = ok ? (int16_t)ra : 0;
+        d.rb = ok ? (int16_t)rb : 0;
+        d.ca = ok ? (int16_t)ca : 0;
+        d.cb = ok ? (int16_t)cb : 0;
+    }
+    if (lane == 0) recs[o] = assoc_finalize(best, dep, H, W, d, max_pc_dist, assoc ? assoc + o : nullptr);
+}
+
+cudaError_t launch_box_assoc_np(const float* pc_dep, const double* bboxes, const double* depth, const double* thr,
+                                const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, int flags,
+                                PaintRec* recs, int32_t* assoc, cudaStream_t st, int* launches) {
+    if (B == 0 || N == 0) return cudaSuccess;
+    box_assoc_np_kernel<<<dim3((N + BW - 1) / BW, B), BW * 32, 0, st>>>(pc_dep, bboxes, depth, thr, counts, N, H, W,
+                                                                         max_pc_dist, flags, recs, assoc);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) ++*launches;
+    return e;
+}
+
 // -----------------------------------------------------------------------------------------------------
 // cvtPcDepthToHeatmap, one detection, in place                      reference pointcloud.py:397-481
 // -----------------------------------------------------------------------------------------------------

@@ -110,6 +110,9 @@ cudaError_t launch_post_process(const cf_post_in_t& in, int B, int K, int out_h,
 cudaError_t launch_box_assoc(const float* pc_dep, const float* bboxes, const float* depth, const float* thr,
                              const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, PaintRec* recs,
                              int32_t* assoc, cudaStream_t st, int* launches);
+cudaError_t launch_box_assoc_np(const float* pc_dep, const double* bboxes, const double* depth, const double* thr,
+                                const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, int flags,
+                                PaintRec* recs, int32_t* assoc, cudaStream_t st, int* launches);
 cudaError_t launch_radar_sort(const double* points, const int32_t* counts, int B, int Nmax, double* out, int32_t* order,
                               cudaStream_t st, int* launches);
 int debug_read_prof(long long* out, int n_cta);  // -DCFD3D_PROFILE builds only

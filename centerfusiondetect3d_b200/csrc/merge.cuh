@@ -2,8 +2,9 @@
 // (score desc, class asc, index asc) + the topk / frustum / decode epilogue.  Device code of the fused stage kernel
 // (stage.cu), spread over the CTAs of a frame's cluster:
 //
-//   select    the CTAs split the ranking of a job's survivor list between them (rank by counting); every ranked
-//             element is delivered to every CTA's shared memory (xs_comp[job][rank], st.shared::cluster);
+//   select    every CTA ranks the jobs' survivor lists itself (rank by counting over key buckets), the two jobs side by
+//             side on the two halves of the CTA: the sorted top-K lands in its own shared memory (xs_comp[job][rank])
+//             and the tail follows without a cluster barrier;
 //   tail      detection k belongs to CTA k % CS from here on: that CTA gathers the head values of ITS detections (all
 //             loads of both jobs issued back to back: one DRAM round trip; one SM sustains only a few hundred
 //             outstanding scattered loads, so the cluster shares them), runs the frustum geometry / decode epilogue
@@ -22,6 +23,7 @@
 #ifndef CF_MERGE_PROF
 #define CF_MERGE_PROF(i) do { } while (0)
 #define CF_MERGE_PROF_DEP(i, v) do { } while (0)
+#define CF_PROF_SLOT(thr, i, v) do { } while (0)
 #endif
 
 namespace cf {
@@ -104,78 +106,76 @@ __device__ __noinline__ void select_overflow(const MergeParams& p, MergeSmem& sm
     __syncthreads();
 }
 
-// part `part` of `parts` of the ranking of job li: emit(rank, composite) for this part's elements of the K best.
-// Composites are distinct, so ranks are a permutation and the parts' outputs are disjoint.
-template <int T, class Emit>
-__device__ __forceinline__ void merge_select_part(const MergeParams& p, MergeSmem& sm, int b, int li, int part,
-                                                  int parts, uint32_t n, Emit&& emit) {
-    const int tid = threadIdx.x;
+// barrier of a thread group: the whole CTA (BAR == 0) or one of its halves (named barrier BAR, T threads)
+template <int T, bool WHOLE>
+__device__ __forceinline__ void group_sync(int bar) {
+    if (WHOLE) __syncthreads();
+    else asm volatile("bar.sync %0, %1;" ::"r"(bar), "r"(T) : "memory");
+}
+
+// The sorted top-K of job li by the thread group (tid in [0, T); named barrier `bar`, or the whole CTA): emit(rank, composite) for every element
+// of the K best.  Composites are distinct, so ranks are a permutation.  n = survivors appended to the job's list (>= K by
+// construction; the caller read the cluster's counter).  Lists longer than the rank window (dense ties) or flagged
+// overflowed need the exact block-level selection first, which only the whole CTA can run (WHOLE).
+template <int T, bool WHOLE, class Emit>
+__device__ __forceinline__ void merge_select(const MergeParams& p, MergeSmem& sm, int b, int li, int tid, int bar, uint32_t n,
+                                             Emit&& emit) {
     const int list = p.list[li];
     const int K = p.K;
+    constexpr int U = MERGE_WIN / T;  // list entries per thread
+    static_assert(MERGE_WIN % T == 0 && MERGE_WIN <= CAND_CAP && MERGE_WIN <= SEL_CAP / 2, "rank window");
     CF_MERGE_PROF(0);
     const unsigned long long* cand = p.cand + ((size_t)b * 2 + list) * CAND_CAP;
-    // the list is read before its length is known (one L2 round trip instead of two; the storage is CAND_CAP entries
-    // whatever the count, entries beyond it are ignored)
-    static_assert(MERGE_WIN == 2 * T && MERGE_WIN <= CAND_CAP, "two speculative entries per thread");
-    const unsigned long long spec0 = __ldcg(cand + tid), spec1 = __ldcg(cand + tid + T);
-    // n = survivors appended to the list (>= K by construction; the caller read the cluster's counter)
     int nw;  // entries of win[] to rank
-    const bool listed = n <= (uint32_t)MERGE_WIN;
-    if (listed) {
-        if (tid < (int)n) sm.win[tid] = spec0;
-        if (tid + T < (int)n) sm.win[tid + T] = spec1;
+    unsigned long long me[U];
+    if (n <= (uint32_t)MERGE_WIN) {
         nw = (int)n;
-        __syncthreads();
+#pragma unroll
+        for (int u = 0; u < U; ++u) me[u] = tid + u * T < nw ? __ldcg(cand + tid + u * T) : 0ull;
     } else {
-        select_overflow<T>(p, sm, b, list, n, cand);  // rare, out of line: keeps the common path's code small
+        if (WHOLE) select_overflow<T>(p, sm, b, list, n, cand);  // rare, out of line: keeps the common path's code small
         nw = K;
+#pragma unroll
+        for (int u = 0; u < U; ++u) me[u] = tid + u * T < nw ? sm.win[tid + u * T] : 0ull;
+        group_sync<T, WHOLE>(bar);  // win[] is read; surv[] (the selection's scratch) is free again
     }
     CF_MERGE_PROF(1);
     // Rank = number of larger composites.  Counting over the whole list costs n^2 compares (microseconds at n ~ 500),
     // so the list is first bucketed by key (256 linear buckets over [min key, max key], a counting sort in shared
-    // memory): rank = entries of the higher buckets + larger entries of the own bucket.  Every CTA of the job builds
-    // the same buckets; the CTAs split the final counting by pixel identity (the order inside win[] / a bucket may
-    // differ from CTA to CTA, the ranks cannot: composites are pairwise distinct).
-    static_assert(MERGE_WIN <= 2 * T && MERGE_WIN <= SEL_CAP / 2, "two entries per thread; sorted[] and start[] share surv[]");
+    // memory): rank = entries of the higher buckets + larger entries of the own bucket.
     unsigned long long* sorted = sm.sc.surv;
     uint32_t* start = reinterpret_cast<uint32_t*>(sm.sc.surv + MERGE_WIN);
-    unsigned long long* winners = sm.sc.surv + MERGE_WIN + 128;  // behind start[256]
-    constexpr uint32_t WIN_CAP = SEL_CAP - (MERGE_WIN + 128);  // (a hint list: winners beyond it just go unprefetched)
     const int lane = tid & 31;
     if (tid < 256) sm.sc.hist[tid] = 0u;
     if (tid == 0) {
         sm.sc.L = 0xffffffffu;
         sm.sc.kmax = 0u;
-        sm.sc.n_out = 0u;
     }
-    unsigned long long me[2];
     uint32_t kmn = 0xffffffffu, kmx = 0u;
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-        const int t = tid + u * T;
-        me[u] = t < nw ? sm.win[t] : 0ull;
-        if (t < nw) {
+    for (int u = 0; u < U; ++u) {
+        if (tid + u * T < nw) {
             kmn = min(kmn, comp_key(me[u]));
             kmx = max(kmx, comp_key(me[u]));
         }
     }
     kmn = __reduce_min_sync(FULL, kmn);
     kmx = __reduce_max_sync(FULL, kmx);
-    __syncthreads();
+    group_sync<T, WHOLE>(bar);
     if (lane == 0 && kmn <= kmx) {
         atomicMin(&sm.sc.L, kmn);
         atomicMax(&sm.sc.kmax, kmx);
     }
-    __syncthreads();
+    group_sync<T, WHOLE>(bar);
     const uint32_t kmin = sm.sc.L, range = sm.sc.kmax - kmin;
     const int shift = range < 256u ? 0 : 24 - __clz(range);  // (range >> shift) < 256
-    uint32_t bk[2], pos[2];
+    uint32_t bk[U], pos[U];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < U; ++u) {
         bk[u] = (comp_key(me[u]) - kmin) >> shift;
         if (tid + u * T < nw) pos[u] = atomicAdd(&sm.sc.hist[bk[u]], 1u);
     }
-    __syncthreads();
+    group_sync<T, WHOLE>(bar);
     if (tid < 32) {  // start[b] = entries of the buckets above b
         uint32_t h[8], sum = 0u;
 #pragma unroll
@@ -196,78 +196,48 @@ __device__ __forceinline__ void merge_select_part(const MergeParams& p, MergeSme
             acc += h[j];
         }
     }
-    __syncthreads();
+    group_sync<T, WHOLE>(bar);
 #pragma unroll
-    for (int u = 0; u < 2; ++u)
+    for (int u = 0; u < U; ++u)
         if (tid + u * T < nw) sorted[start[bk[u]] + pos[u]] = me[u];
-    __syncthreads();
+    group_sync<T, WHOLE>(bar);
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-        if (tid + u * T >= nw || (int)(comp_gidx(me[u]) % (uint32_t)parts) != part) continue;
+    for (int u = 0; u < U; ++u) {
+        if (tid + u * T >= nw) continue;
         const int s0 = (int)start[bk[u]], s1 = s0 + (int)sm.sc.hist[bk[u]];
+        if (s0 >= K) continue;  // K or more elements in higher buckets: not a winner
         int rank = s0;
         for (int jx = s0; jx < s1; ++jx) rank += (sorted[jx] > me[u]) ? 1 : 0;
-        if (rank < K) {
-            emit(rank, me[u]);
-            const uint32_t slot = atomicAdd(&sm.sc.n_out, 1u);
-            if (slot < WIN_CAP) winners[slot] = me[u];
-        }
+        if (rank < K) emit(rank, me[u]);
     }
-    __syncthreads();  // win[] is reused by the next job of this CTA
+    group_sync<T, WHOLE>(bar);  // the scratch is reused by the next job of this group
     CF_MERGE_PROF(2);
 }
 
-// The head values of the winners this CTA has just ranked (merge_select_part leaves their composites behind start[] in
-// the scratch) will be gathered -- by whichever CTA owns the detection -- one cluster barrier from now: 140 k scattered
-// sectors per batch, DRAM random-access bound.  Their L2 prefetches go out a barrier's worth of time earlier, spread
-// over all threads; the caller places this between the arrival at that barrier and the wait.
-template <int T>
-__device__ __forceinline__ void prefetch_winner_heads(const MergeParams& p, MergeSmem& sm, int b, int li) {
-    const unsigned long long* winners = sm.sc.surv + MERGE_WIN + 128;
-    constexpr uint32_t WIN_CAP = SEL_CAP - (MERGE_WIN + 128);
-    const MergeJob& jb = p.job[li];
-    const int N = jb.epilogue == EPI_FRUSTUM ? (int)FS_N : (jb.epilogue == EPI_DECODE ? (int)DS_N : 0);
-    const int total = (int)min(sm.sc.n_out, WIN_CAP) * N;
-    const uint32_t HWu = (uint32_t)(p.H * p.W);
-    for (int t = threadIdx.x; t < total; t += T) {
-        const int w = t / N, s2 = t - w * N;
-        const float* base = jb.gt.base[s2];
-        if (base) {
-            const uint32_t ind = comp_gidx(winners[w]) % HWu;
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(base + ((size_t)b * jb.gt.nch[s2] + jb.gt.ch[s2]) * HWu + ind));
-        }
-    }
+// ---- asynchronous global -> shared copies of single values (cp.async, SASS LDGSTS): no register is held while the
+// value is on its way, and a thread can wait for an older group of copies while a younger one is still in flight
+__device__ __forceinline__ void cp_async4(float* dst_smem, const float* src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {  // all but the N youngest groups of this thread have landed
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-// detections kl0 .. kl0+nb of this CTA (detection k = first + kl * stride): head values of job N-channel table gt into
-// gath[(kl - kl0) * GATH_STRIDE + slot].  comps = the job's sorted composites xs_comp[job].
-// Executed by the thread group [0, T) given as (tid, T).
+// detections kl0 .. kl0+nb of this CTA (detection k = first + kl * stride): the head values of a job's N-channel table
+// gt on their way into gath[(kl - kl0) * GATH_STRIDE + slot].  inds = the job's peak pixels inds[rank].
+// Executed by the thread group [0, T) given as (tid, T); the caller commits the group and waits for it.
 template <int N>
-__device__ __forceinline__ void gather_local(const GatherTab& gt, int b, size_t HW, const unsigned long long* comps,
-                                             int first, int stride, int kl0, int nb, float* gath, int tid, int T) {
+__device__ __forceinline__ void gather_issue(const GatherTab& gt, int b, size_t HW, const int32_t* inds, int first,
+                                             int stride, int kl0, int nb, float* gath, int tid, int T) {
     const int total = nb * N;
-    constexpr int U = 4;
-    for (int t0 = tid; t0 < total; t0 += T * U) {
-        float v[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int t = t0 + u * T;
-            v[u] = 0.0f;
-            if (t < total) {
-                const int kl = t / N, s = t - kl * N;
-                const float* base = gt.base[s];
-                const uint32_t ind = comp_gidx(comps[first + (kl0 + kl) * stride]) % (uint32_t)HW;
-                if (base) v[u] = __ldg(base + ((size_t)b * gt.nch[s] + gt.ch[s]) * HW + ind);
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const int t = t0 + u * T;
-            if (t < total) {
-                const int kl = t / N, s = t - kl * N;
-                gath[kl * GATH_STRIDE + s] = v[u];
-            }
-        }
+    for (int t = tid; t < total; t += T) {
+        const int kl = t / N, s = t - kl * N;
+        const float* base = gt.base[s];
+        float* dst = gath + kl * GATH_STRIDE + s;
+        if (base) cp_async4(dst, base + ((size_t)b * gt.nch[s] + gt.ch[s]) * HW + (uint32_t)inds[first + (kl0 + kl) * stride]);
+        else *dst = 0.0f;
     }
 }
 
@@ -293,9 +263,9 @@ __device__ __forceinline__ float frustum_thr_quad(float ay, float ax, float rot1
 // reference src/lib/utils/pointcloud.py:348-380
 // Executed by the thread group [0, T) given as (tid, T): whole warps.
 __device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const MergeJob& jb, int b,
-                                                 const unsigned long long* comps, int first, int stride, int kl0, int nb,
-                                                 const float* gath, DetParam* sdet, short4* sroi, const float* cal,
-                                                 int tid, int T) {
+                                                 const unsigned long long* comps, const int32_t* inds, int first, int stride,
+                                                 int kl0, int nb, const float* gath, DetParam* sdet, short4* sroi,
+                                                 const float* cal, int tid, int T) {
     const int K = p.K, W = p.W, HWi = p.H * p.W;
     const int j = tid & 3;
     // cal = {calib[0,0], calib[0,2]} of the frame where the caller fetched them ahead of time (the row is cold in DRAM)
@@ -305,7 +275,7 @@ __device__ __forceinline__ void epilogue_frustum(const MergeParams& p, const Mer
     auto box_of = [&](int q, int& ind, DetParam& d) {
         const int k = first + (kl0 + q) * stride;
         const float* g = gath + q * GATH_STRIDE;
-        ind = (int)(comp_gidx(comps[k]) % (uint32_t)HWi);
+        ind = inds[k];
         const int y = ind / W, x = ind - y * W;
         const float xf = __fadd_rn((float)x, 0.5f), yf = __fadd_rn((float)y, 0.5f);
         float w = g[FS_WH], h = g[FS_WH + 1];
@@ -385,13 +355,17 @@ __device__ __forceinline__ float comp_score(const MergeParams& p, int b, unsigne
 }
 
 // reference src/lib/model/decode.py:38-41, :80-85, :132-165
+// Four lanes per detection, each with its own part of the outputs (this code runs once per frame on a few threads: its
+// cost is the length of the longest thread's instruction sequence): lane 0 score / class / centre / index, lane 1 the
+// 2-D box, lane 2 amodal offset and depth.
 __device__ __forceinline__ void epilogue_decode(const MergeParams& p, const MergeJob& jb, int b,
                                                 const unsigned long long* comps, int first, int stride, int kl0, int nb,
                                                 const float* gath, int tid, int T) {
     const int K = p.K, HWi = p.H * p.W;
     const cf_decode_heads_t& hd = jb.dec.heads;
     const cf_decode_out_t& o = jb.dec.out;
-    for (int q = tid; q < nb; q += T) {
+    const int j = tid & 3;
+    for (int q = tid >> 2; q < nb; q += T >> 2) {
         const int k = first + (kl0 + q) * stride;
         const unsigned long long c = comps[k];
         const uint32_t gi = comp_gidx(c);
@@ -399,47 +373,49 @@ __device__ __forceinline__ void epilogue_decode(const MergeParams& p, const Merg
         const int ind = (int)(gi - (uint32_t)cls * (uint32_t)HWi);
         const int y = ind / p.W, x = ind - y * p.W;
         const float* g = gath + q * GATH_STRIDE;
-        float score = comp_score(p, b, c, cls, ind);
         const size_t ok = (size_t)b * K + k;
-        if (hd.uncertainty) score = __fmul_rn(score, expf(-expf(g[DS_UNC])));
-        o.scores[ok] = score;
-        o.class_ids[ok] = (float)cls;
         const float xn = __fdiv_rn((float)x, (float)p.W), yn = __fdiv_rn((float)y, (float)p.H);
-        o.centers[2 * ok + 0] = xn;
-        o.centers[2 * ok + 1] = yn;
-        float xs = __fmul_rn(xn, (float)jb.dec.out_w), ys = __fmul_rn(yn, (float)jb.dec.out_h);
-        if (hd.reg) {
-            xs = __fadd_rn(xs, g[DS_REG]);
-            ys = __fadd_rn(ys, g[DS_REG + 1]);
-        } else {
-            xs = __fadd_rn(xs, 0.5f);
-            ys = __fadd_rn(ys, 0.5f);
-        }
-        if (hd.wh) {
-            float w = g[DS_WH], h = g[DS_WH + 1];
-            if (w < 0.0f) w = 0.0f;
-            if (h < 0.0f) h = 0.0f;
-            if (jb.dec.norm2d) {
-                w = __fmul_rn(w, (float)jb.dec.out_w);
-                h = __fmul_rn(h, (float)jb.dec.out_h);
+        if (j == 0) {
+            float score = comp_score(p, b, c, cls, ind);
+            if (hd.uncertainty) score = __fmul_rn(score, expf(-expf(g[DS_UNC])));
+            o.scores[ok] = score;
+            o.class_ids[ok] = (float)cls;
+            o.centers[2 * ok + 0] = xn;
+            o.centers[2 * ok + 1] = yn;
+            if (o.inds) o.inds[ok] = ind;
+        } else if (j == 1) {
+            if (hd.wh) {
+                float xs = __fmul_rn(xn, (float)jb.dec.out_w), ys = __fmul_rn(yn, (float)jb.dec.out_h);
+                if (hd.reg) {
+                    xs = __fadd_rn(xs, g[DS_REG]);
+                    ys = __fadd_rn(ys, g[DS_REG + 1]);
+                } else {
+                    xs = __fadd_rn(xs, 0.5f);
+                    ys = __fadd_rn(ys, 0.5f);
+                }
+                float w = g[DS_WH], h = g[DS_WH + 1];
+                if (w < 0.0f) w = 0.0f;
+                if (h < 0.0f) h = 0.0f;
+                if (jb.dec.norm2d) {
+                    w = __fmul_rn(w, (float)jb.dec.out_w);
+                    h = __fmul_rn(h, (float)jb.dec.out_h);
+                }
+                const float hw2 = __fdiv_rn(w, 2.0f), hh2 = __fdiv_rn(h, 2.0f);
+                *reinterpret_cast<float4*>(o.bboxes + 4 * ok) =
+                    make_float4(__fsub_rn(xs, hw2), __fsub_rn(ys, hh2), __fadd_rn(xs, hw2), __fadd_rn(ys, hh2));
             }
-            const float hw2 = __fdiv_rn(w, 2.0f), hh2 = __fdiv_rn(h, 2.0f);
-            o.bboxes[4 * ok + 0] = __fsub_rn(xs, hw2);
-            o.bboxes[4 * ok + 1] = __fsub_rn(ys, hh2);
-            o.bboxes[4 * ok + 2] = __fadd_rn(xs, hw2);
-            o.bboxes[4 * ok + 3] = __fadd_rn(ys, hh2);
-        }
-        if (hd.amodal) {  // :165 de-normalise
-            float ax = g[DS_AMODAL], ay = g[DS_AMODAL + 1];
-            if (jb.dec.norm2d) {
-                ax = __fmul_rn(ax, (float)jb.dec.out_w);
-                ay = __fmul_rn(ay, (float)jb.dec.out_h);
+        } else if (j == 2) {
+            if (hd.amodal) {  // :165 de-normalise
+                float ax = g[DS_AMODAL], ay = g[DS_AMODAL + 1];
+                if (jb.dec.norm2d) {
+                    ax = __fmul_rn(ax, (float)jb.dec.out_w);
+                    ay = __fmul_rn(ay, (float)jb.dec.out_h);
+                }
+                o.amodal[2 * ok + 0] = ax;
+                o.amodal[2 * ok + 1] = ay;
             }
-            o.amodal[2 * ok + 0] = ax;
-            o.amodal[2 * ok + 1] = ay;
+            if (hd.depth) o.depth[ok] = g[DS_DEPTH];
         }
-        if (hd.depth) o.depth[ok] = g[DS_DEPTH];
-        if (o.inds) o.inds[ok] = ind;
     }
 }
 
@@ -454,60 +430,93 @@ __device__ __forceinline__ void copy_head(const float* head, float* out, int nch
     }
 }
 
-// the tail of the jobs for this CTA's detections (k = first + kl * stride, kl < n_local), in batches of GB detections:
-// gathers of all jobs, then their epilogues.  gath holds n_jobs * GB * GATH_STRIDE floats.
+// epilogue of a TOPK job for detections kl0 .. kl0+nb (thread group (tid, T))
+__device__ __forceinline__ void epilogue_topk(const MergeParams& p, const MergeJob& jb, int b, const unsigned long long* comps,
+                                              int first, int stride, int kl0, int nb, int tid, int T) {
+    const int K = p.K, HWi = p.H * p.W;
+    for (int q = tid; q < nb; q += T) {
+        const int k = first + (kl0 + q) * stride;
+        const unsigned long long c = comps[k];
+        const uint32_t gi = comp_gidx(c);
+        const int cls = (int)(gi / (uint32_t)HWi);
+        const int ind = (int)(gi - (uint32_t)cls * (uint32_t)HWi);
+        const int y = ind / p.W, x = ind - y * p.W;
+        const size_t o = (size_t)b * K + k;
+        if (jb.topk.scores) jb.topk.scores[o] = comp_score(p, b, c, cls, ind);
+        if (jb.topk.inds) jb.topk.inds[o] = ind;
+        if (jb.topk.classes) jb.topk.classes[o] = cls;
+        if (jb.topk.ys) jb.topk.ys[o] = y;
+        if (jb.topk.xs) jb.topk.xs[o] = x;
+    }
+}
+
+// epilogues of the DECODE jobs for detections kl0 .. kl0+nb out of their gather buffers (thread group (tid, T)); the
+// caller has waited for the jobs' copies and passed a barrier
+__device__ __forceinline__ void merge_tail_decode(const MergeParams& p, int n_jobs, int b, int first, int stride, int kl0,
+                                                  int nb, const unsigned long long* xs_comp, const float* gath, int GB,
+                                                  int tid, int T) {
+    const int K = p.K;
+    for (int li = 0; li < n_jobs; ++li) {
+        const MergeJob& jb = p.job[li];
+        if (jb.epilogue != EPI_DECODE) continue;
+        const unsigned long long* comps = xs_comp + li * K;
+        const float* g = gath + (size_t)li * GB * GATH_STRIDE;
+        epilogue_decode(p, jb, b, comps, first, stride, kl0, nb, g, tid, T);
+        copy_head(jb.dec.heads.rot, jb.dec.out.rot, 8, DS_ROT, b, K, first, stride, kl0, nb, g, tid, T);
+        copy_head(jb.dec.heads.dim, jb.dec.out.dim, 3, DS_DIM, b, K, first, stride, kl0, nb, g, tid, T);
+        copy_head(jb.dec.heads.nuscenes_att, jb.dec.out.nuscenes_att, 8, DS_ATT, b, K, first, stride, kl0, nb, g, tid, T);
+        copy_head(jb.dec.heads.velocity, jb.dec.out.velocity, 3, DS_VEL, b, K, first, stride, kl0, nb, g, tid, T);
+    }
+}
+
+// The tail of the jobs for this CTA's detections (k = first + kl * stride, kl < n_local), in batches of GB detections.
+// Every head value travels as an asynchronous 4-byte copy straight into the gather buffers (gath holds
+// n_jobs * GB * GATH_STRIDE floats): the frustum job's copies go out first and form their own group, because the
+// association waits for them, the decode job's 29 channels per detection follow -- 140 k scattered sectors per batch hit
+// the DRAM at the same moment from every cluster, and whoever is served last sets the pace of the phase.  The frustum
+// epilogue starts as soon as ITS group has landed.  defer_decode (one batch only): the decode epilogue is left to the
+// caller (merge_tail_decode on the upper half of the CTA while the association's finishing threads wait for their
+// velocity reads), who first has every thread wait for its copies and passes a CTA barrier.
 template <int T>
 __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int b, int first, int stride, int n_local,
-                                           const unsigned long long* xs_comp, float* gath, int GB, DetParam* sdet,
-                                           short4* sroi, const float* cal) {
+                                           const unsigned long long* xs_comp, const int32_t* xs_ind, float* gath, int GB,
+                                           DetParam* sdet, short4* sroi, const float* cal, bool defer_decode) {
     const int K = p.K, HWi = p.H * p.W;
+    const int tid = (int)threadIdx.x;
     for (int kl0 = 0; kl0 < n_local; kl0 += GB) {
         const int nb = min(GB, n_local - kl0);
-        // the two jobs run side by side, each on its own half of the CTA's warps: first the gathers (one round of
-        // scattered loads in flight for both jobs at once), then the epilogues
-        const int half = n_jobs == 2 ? T / 2 : T;
-        const int li = n_jobs == 2 ? (int)threadIdx.x / half : 0;
-        const int gt = (int)threadIdx.x - li * half;
-        {
-            const MergeJob& jb = p.job[li];
-            float* g = gath + (size_t)li * GB * GATH_STRIDE;
-            if (jb.epilogue == EPI_FRUSTUM)
-                gather_local<FS_N>(jb.gt, b, (size_t)HWi, xs_comp + li * K, first, stride, kl0, nb, g, gt, half);
-            else if (jb.epilogue == EPI_DECODE)
-                gather_local<DS_N>(jb.gt, b, (size_t)HWi, xs_comp + li * K, first, stride, kl0, nb, g, gt, half);
+#pragma unroll
+        for (int pass = 0; pass < 2; ++pass) {  // group 0: the frustum job, group 1: the others
+            for (int li = 0; li < n_jobs; ++li) {
+                const MergeJob& jb = p.job[li];
+                const bool isf = jb.epilogue == EPI_FRUSTUM;
+                if ((pass == 0) != isf) continue;
+                float* g = gath + (size_t)li * GB * GATH_STRIDE;
+                if (isf)
+                    gather_issue<FS_N>(jb.gt, b, (size_t)HWi, xs_ind + li * K, first, stride, kl0, nb, g, tid, T);
+                else if (jb.epilogue == EPI_DECODE)
+                    gather_issue<DS_N>(jb.gt, b, (size_t)HWi, xs_ind + li * K, first, stride, kl0, nb, g, tid, T);
+            }
+            cp_async_commit();
         }
+        cp_async_wait<1>();
         __syncthreads();
         CF_MERGE_PROF(3);
-        {
+        for (int li = 0; li < n_jobs; ++li) {
             const MergeJob& jb = p.job[li];
             const unsigned long long* comps = xs_comp + li * K;
-            const float* g = gath + (size_t)li * GB * GATH_STRIDE;
-            if (jb.epilogue == EPI_TOPK) {
-                for (int q = gt; q < nb; q += half) {
-                    const int k = first + (kl0 + q) * stride;
-                    const unsigned long long c = comps[k];
-                    const uint32_t gi = comp_gidx(c);
-                    const int cls = (int)(gi / (uint32_t)HWi);
-                    const int ind = (int)(gi - (uint32_t)cls * (uint32_t)HWi);
-                    const int y = ind / p.W, x = ind - y * p.W;
-                    const size_t o = (size_t)b * K + k;
-                    if (jb.topk.scores) jb.topk.scores[o] = comp_score(p, b, c, cls, ind);
-                    if (jb.topk.inds) jb.topk.inds[o] = ind;
-                    if (jb.topk.classes) jb.topk.classes[o] = cls;
-                    if (jb.topk.ys) jb.topk.ys[o] = y;
-                    if (jb.topk.xs) jb.topk.xs[o] = x;
-                }
-            } else if (jb.epilogue == EPI_FRUSTUM) {
-                epilogue_frustum(p, jb, b, comps, first, stride, kl0, nb, g, sdet, sroi, cal, gt, half);
-            } else if (jb.epilogue == EPI_DECODE) {
-                epilogue_decode(p, jb, b, comps, first, stride, kl0, nb, g, gt, half);
-                copy_head(jb.dec.heads.rot, jb.dec.out.rot, 8, DS_ROT, b, K, first, stride, kl0, nb, g, gt, half);
-                copy_head(jb.dec.heads.dim, jb.dec.out.dim, 3, DS_DIM, b, K, first, stride, kl0, nb, g, gt, half);
-                copy_head(jb.dec.heads.nuscenes_att, jb.dec.out.nuscenes_att, 8, DS_ATT, b, K, first, stride, kl0, nb, g, gt, half);
-                copy_head(jb.dec.heads.velocity, jb.dec.out.velocity, 3, DS_VEL, b, K, first, stride, kl0, nb, g, gt, half);
-            }
+            if (jb.epilogue == EPI_TOPK)
+                epilogue_topk(p, jb, b, comps, first, stride, kl0, nb, tid, T);
+            else if (jb.epilogue == EPI_FRUSTUM)
+                epilogue_frustum(p, jb, b, comps, xs_ind + li * K, first, stride, kl0, nb, gath + (size_t)li * GB * GATH_STRIDE,
+                                 sdet, sroi, cal, tid, T);
         }
         CF_MERGE_PROF(7);
+        if (!defer_decode) {
+            cp_async_wait<0>();
+            __syncthreads();
+            merge_tail_decode(p, n_jobs, b, first, stride, kl0, nb, xs_comp, gath, GB, tid, T);
+        }
         __syncthreads();
         CF_MERGE_PROF(4);
     }

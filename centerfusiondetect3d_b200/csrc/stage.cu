@@ -22,10 +22,9 @@
 //               a CTA-wide work list; B2 tests them side by side, one per thread (threshold, 3x3 suppression) and
 //               appends the survivors to the frame's lists (typically 1.1-3 x K entries; one reservation per CTA).
 //   -- cluster barrier --
-//      select   the CTAs split the rank-by-counting of the two survivor lists; every ranked composite is delivered to
-//               every CTA (st.shared::cluster).  Meanwhile the frame's radar depth plane pc_dep[b,0] lands in the
-//               shared memory the heat-map no longer needs (one bulk copy).
-//   -- cluster barrier --
+//      select   every CTA ranks the two survivor lists itself (the two jobs on the two halves of the CTA, rank by
+//               counting over key buckets): no delivery, no barrier.  Meanwhile the frame's radar depth plane
+//               pc_dep[b,0] lands in the shared memory the heat-map no longer needs (one bulk copy).
 //      tail     detection k belongs to CTA k % CS: head gathers, frustum geometry / decode epilogue (merge.cuh);
 //   D  assoc    one warp per detection: ROI scan of the staged depth plane, warp-shuffle lexicographic (depth, pixel)
 //               minimum (assoc.cuh); the K paint records are broadcast to every CTA.
@@ -59,6 +58,9 @@ constexpr int SNW = ST / 32;     // warps
 constexpr int WL_CAP = 640;      // pass-B work list: candidate pixels a CTA parks before it tests them side by side
 constexpr int WL_CAP_RING = 4096;  // ... when the share streams through a ring of slots (shared memory to spare)
 constexpr int FL_CAP = 256;      // pass-B flagged-group list (resident shares)
+constexpr int HOT_CAP = 192;     // hot list: survivors whose head values are prefetched early (a hint: overflow is dropped)
+constexpr int HOT_DIV = 2;       // raw list: hot = at or above the bound of the K / HOT_DIV largest group maxima (covers nearly
+                                 // all winners at ~1.3 x K entries; the nms'd list has only ~1.3 x K survivors: all are hot)
 constexpr int MAX_SLOTS = 64;
 constexpr int MAX_CS = 16;
 constexpr size_t SMEM_DYN_CAP = 227 * 1024 - 1792;  // leaves room for the kernel's static shared memory
@@ -121,6 +123,14 @@ __device__ long long g_prof[1024 * PROF_PTS];
             g_prof[blockIdx.x * PROF_PTS + 16 + (i)] = t_;                                                \
         }                                                                                                 \
     } while (0)
+#define CF_PROF_SLOT(thr, i, val)                                                                            \
+    do {                                                                                                  \
+        if (p.prof && threadIdx.x == (thr) && blockIdx.x < 1024) {                                        \
+            long long t_;                                                                                 \
+            asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_) : "r"(val) : "memory");                      \
+            g_prof[blockIdx.x * PROF_PTS + (i)] = t_;                                                     \
+        }                                                                                                 \
+    } while (0)
 #define PROF(i)                                                                              \
     do {                                                                                     \
         if (p.prof && tid == 0 && blockIdx.x < 1024) g_prof[blockIdx.x * PROF_PTS + (i)] = clock64(); \
@@ -140,6 +150,7 @@ __device__ long long g_prof[1024 * PROF_PTS];
 #else
 #define CF_MERGE_PROF(i) do { } while (0)
 #define CF_MERGE_PROF_DEP(i, val) do { } while (0)
+#define CF_PROF_SLOT(thr, i, val) do { } while (0)
 #define PROF(i) do { } while (0)
 #define PROF_VAL(i, v) do { } while (0)
 #define PROF_DEP(i, val) do { } while (0)
@@ -162,10 +173,10 @@ struct StageParams {
     int hist_words;    // 32-bit words of this CTA's part of the histogram (both lists)
     int slot_area;     // bytes of the slot area (also hosts the merge scratch, the depth plane and the owner map)
     int dep_off;       // byte offset of the staged depth plane inside the slot area, -1: read it from global memory
-    // byte offsets inside the slot area once the heat-map is done with it: [paint records K | sorted composites 2K |
+    // byte offsets inside the slot area once the heat-map is done with it: [paint records K | sorted composites 2K | their pixels 2K |
     // selection scratch | gather buffers | frustum parameters | matches | depth plane]; the owner map of the paint
     // takes everything behind the records
-    int off_comp, off_msm, off_gath, off_det, off_best, off_par, off_own;
+    int off_comp, off_ind, off_msm, off_gath, off_det, off_best, off_par, off_own;
     int GB;            // detections per gather batch
     int wl_entries;    // words of the pass-B work list
     uint32_t* ctr;
@@ -205,10 +216,14 @@ __device__ __forceinline__ uint32_t hist_read_cluster(uint32_t hist_saddr, int l
 
 // tau of both lists: lower edge of the highest bin b* with count(bins >= b*) >= K, 0 ("everything") when the frame
 // has fewer than K groups.  Scans downwards from the top occupied bin, ST bins per round, both lists side by side.
+// hot[l]: the same for the smaller count Kh (hot[l] >= tau[l]; 0xffffffff when there is none) -- survivors at or above it
+// are almost surely among the K best, and the filter pass starts the L2 prefetch of their head values right away.
 __device__ __forceinline__ void tau_scan_cluster(uint32_t hist_saddr, int list_words, int cs_log2, const uint32_t top_in[2],
-                                                 int K, bool want0, bool want1, uint32_t* s_scan, uint32_t tau[2]) {
+                                                 int K, int Kh, bool want0, bool want1, uint32_t* s_scan, uint32_t tau[2],
+                                                 uint32_t hot[2]) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = SNW;
+    constexpr int STRIDE = NW + 2;  // per list: NW warp totals, [NW] = tau bin found, [NW + 1] = hot bin found
     const bool want[2] = {want0, want1};
     uint32_t top[2], carry[2] = {0u, 0u};
     bool done[2];
@@ -217,7 +232,9 @@ __device__ __forceinline__ void tau_scan_cluster(uint32_t hist_saddr, int list_w
         top[l] = want[l] ? top_in[l] : 0u;
         done[l] = !want[l];
         tau[l] = 0u;
+        hot[l] = 0xffffffffu;
     }
+    if (tid < 2) s_scan[tid * STRIDE + NW + 1] = 0xffffffffu;  // (ordered before the first write by the round's barrier)
     for (int round = 0; !(done[0] && done[1]); ++round) {
         uint32_t c[2], inc[2];
 #pragma unroll
@@ -233,8 +250,8 @@ __device__ __forceinline__ void tau_scan_cluster(uint32_t hist_saddr, int list_w
                 const uint32_t o = __shfl_up_sync(FULL, inc[l], off);
                 if (lane >= off) inc[l] += o;
             }
-            if (lane == 31) s_scan[l * (NW + 1) + warp] = inc[l];
-            if (tid == 0) s_scan[l * (NW + 1) + NW] = 0xffffffffu;
+            if (lane == 31) s_scan[l * STRIDE + warp] = inc[l];
+            if (tid == 0) s_scan[l * STRIDE + NW] = 0xffffffffu;
         }
         __syncthreads();
         uint32_t total[2];
@@ -242,7 +259,7 @@ __device__ __forceinline__ void tau_scan_cluster(uint32_t hist_saddr, int list_w
         for (int l = 0; l < 2; ++l) {
             // prefix over the warps' totals: every warp scans them itself (lanes 0..NW-1), no extra barrier
             static_assert(NW <= 32, "one lane per warp total");
-            const uint32_t wt = lane < NW ? s_scan[l * (NW + 1) + lane] : 0u;
+            const uint32_t wt = lane < NW ? s_scan[l * STRIDE + lane] : 0u;
             uint32_t winc = wt;
 #pragma unroll
             for (int off = 1; off < NW; off <<= 1) {
@@ -254,13 +271,16 @@ __device__ __forceinline__ void tau_scan_cluster(uint32_t hist_saddr, int list_w
             inc[l] += below;
             const int bin = (int)top[l] - (round * ST + tid);
             if (!done[l] && inc[l] >= (uint32_t)K && inc[l] - c[l] < (uint32_t)K)
-                s_scan[l * (NW + 1) + NW] = (uint32_t)bin << HIST_SHIFT;  // exactly one thread
+                s_scan[l * STRIDE + NW] = (uint32_t)bin << HIST_SHIFT;  // exactly one thread
+            if (!done[l] && inc[l] >= (uint32_t)Kh && inc[l] - c[l] < (uint32_t)Kh)
+                s_scan[l * STRIDE + NW + 1] = (uint32_t)bin << HIST_SHIFT;  // exactly one thread, in one round
         }
         __syncthreads();
 #pragma unroll
         for (int l = 0; l < 2; ++l) {
             if (done[l]) continue;
-            const uint32_t found = s_scan[l * (NW + 1) + NW];
+            hot[l] = s_scan[l * STRIDE + NW + 1];
+            const uint32_t found = s_scan[l * STRIDE + NW];
             if (found != 0xffffffffu) {
                 tau[l] = found;
                 done[l] = true;
@@ -279,10 +299,11 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     __shared__ uint64_t full[MAX_SLOTS];
     __shared__ uint64_t dep_bar;
     __shared__ volatile uint32_t s_issued[MAX_SLOTS];  // ring mode: bulk copies started into each slot so far
-    __shared__ uint32_t s_scan[2 * (SNW + 1)];
+    __shared__ uint32_t s_scan[2 * (SNW + 2)];
     __shared__ uint32_t s_tops[2][MAX_CS];
     __shared__ uint32_t s_mytop[2];
     __shared__ uint32_t s_nwl;  // entries of the pass-B work list
+    __shared__ uint32_t s_nhot;  // entries of the hot list (survivors whose head values are prefetched early)
     __shared__ uint32_t s_ctr[2];  // in the cluster's CTA 0: survivors appended to the frame's two lists (a shared-memory
                                    // counter every CTA reaches over DSMEM: a third of the round trip of a global atomic)
     __shared__ float s_cal[2];    // calib[0,0], calib[0,2] of the frame (fetched at frame start)
@@ -326,11 +347,24 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         mbar_init(&dep_bar, 1);
         mbar_fence_init();
     }
-    // programmatic dependent launch (see launch_fusion_stage): let the next kernel of the stream place its CTAs as ours
-    // retire, and do not touch global memory before the kernel ahead of us has completed
+    // Frame-start state of the cluster's FIRST frame: histogram part and counters cleared, and the cluster barrier that
+    // tells the peers so, all of it shared memory only -- done BEFORE the wait for the kernel ahead of us, so that in a
+    // stream of back-to-back calls (programmatic dependent launch, see launch_fusion_stage) it overlaps that kernel's tail
+    // instead of standing between the launch and the first bulk copy.
+    auto frame_reset = [&]() {
+        for (int i = tid; i < p.hist_words; i += ST) hist[i] = 0u;
+        if (tid < 2 * MAX_CS) (&s_tops[0][0])[tid] = 0u;
+        if (tid < 2) s_mytop[tid] = 0u;
+        if (tid == 0) s_nwl = s_nfl = s_nhot = 0u;
+        if (tid < 2) s_ctr[tid] = 0u;  // (cleared before this CTA arrives at the frame's first cluster barrier)
+    };
+    frame_reset();
+    __syncthreads();
+    cl_sync();  // every CTA of the cluster runs and its histogram part is clear: remote reductions may land
+    // programmatic dependent launch: let the next kernel of the stream place its CTAs as ours retire, and do not touch
+    // global memory before the kernel ahead of us has completed
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    __syncthreads();
 
     int it = 0;
     for (int b = cluster_id; b < p.B; b += n_clusters, ++it) {
@@ -387,16 +421,14 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
 
         PROF(0);
         // ---- frame start: clear this CTA's histogram part and counters, start the first S bulk copies ------------
-        for (int i = tid; i < p.hist_words; i += ST) hist[i] = 0u;
-        if (tid < 2 * MAX_CS) (&s_tops[0][0])[tid] = 0u;
-        if (tid < 2) s_mytop[tid] = 0u;
-        if (tid == 0) s_nwl = s_nfl = 0u;
-        if (tid < 2) s_ctr[tid] = 0u;  // (cleared before this CTA arrives at the frame's first cluster barrier)
-        fence_async_smem();  // the previous frame's merge scratch / owner map were generic writes to the slot area
-        __syncthreads();
-        // "this CTA runs and its histogram part is clear": arrive now, wait right before the first remote reduction
-        // (the release fence of the arrival then has nothing outstanding to wait for)
-        cl_arrive();
+        if (it > 0) {  // (the first frame's reset ran in the prologue)
+            frame_reset();
+            fence_async_smem();  // the previous frame's merge scratch / owner map were generic writes to the slot area
+            __syncthreads();
+            // "this CTA's histogram part is clear": arrive now, wait right before the first remote reduction
+            // (the release fence of the arrival then has nothing outstanding to wait for)
+            cl_arrive();
+        }
         if (use_tma && tid < (LPF < S ? LPF : S)) issue_load(tid);
         if (p.do_frustum && tid >= ST - 2)  // (the last warp: it stalls on this DRAM read before its first chunk)
             s_cal[tid - (ST - 2)] = __ldg(p.mp.job[0].fh.calib + 12 * (size_t)b + 2 * (tid - (ST - 2)));
@@ -411,7 +443,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             }
         }
         PROF(15);
-        cl_wait();
+        if (it > 0) cl_wait();
         PROF(1);
 
         // ---- pass A: group maxima -> distributed histogram ------------------------------------------------------
@@ -529,11 +561,17 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             top[0] = max(top[0], s_tops[0][r]);
             top[1] = max(top[1], s_tops[1][r]);
         }
-        tau_scan_cluster(hist_saddr, list_words, p.cs_log2, top, K, want_raw, want_nms, s_scan, tau_key);
+        uint32_t hot_key[2];
+        tau_scan_cluster(hist_saddr, list_words, p.cs_log2, top, K, max(1, K / HOT_DIV), want_raw, want_nms, s_scan, tau_key,
+                         hot_key);
         PROF(4);
         const float INF = CUDART_INF_F;
         float tau_raw = want_raw ? tau_to_float(tau_key[0]) : INF;
         float tau_nms = want_nms ? tau_to_float(tau_key[1]) : INF;
+        // survivors at or above these are almost surely winners: their head values are prefetched into L2 while the
+        // cluster gathers at the barrier behind the filter pass, two phases ahead of the gathers
+        const float hot_raw = (want_raw && hot_key[0] != 0xffffffffu) ? tau_to_float(hot_key[0]) : INF;
+        const float hot_nms = want_nms ? -INF : INF;  // (every survivor of the nms'd list)
         if (want_raw && tau_key[0] == 0u) {
             // fewer than K groups: no useful bound -> the merge selects from the frame itself (list flagged overflowed)
             if (rank == 0 && tid == 0) atomicAdd(&s_ctr[0], (uint32_t)CAND_CAP + 1u);
@@ -590,7 +628,9 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             // park this lane's candidates (bit j of mask: pixel j of float4 item_of(bit)) in the work list from `slot` on;
             // lanes that hold several park one per round, so that a blob's pixels are written side by side
             uint16_t* wl16 = reinterpret_cast<uint16_t*>(wl);
-            const uint32_t wl_cap = resident ? 2u * (uint32_t)p.wl_entries : (uint32_t)p.wl_entries;
+            // (the last HOT_CAP words of the work list hold the hot list)
+            const uint32_t wl_cap = resident ? 2u * (uint32_t)(p.wl_entries - HOT_CAP) : (uint32_t)(p.wl_entries - HOT_CAP);
+            uint32_t* s_hot = wl + (p.wl_entries - HOT_CAP);
             auto park = [&](uint32_t mask, uint32_t slot, int q, auto&& item_of) {
                 for (;;) {
                     const bool mine = mask != 0u;
@@ -763,6 +803,12 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     bool sraw = false, snms = false;
                     if (c0 + (uint32_t)(u * ST) < n_wl) {  // (uniform: trips beyond the list cost nothing)
                         if (c < n_wl) cand_eval(resident ? (uint32_t)wl16[c] : wl[c], v, gi, sraw, snms);
+                        if (((sraw && v >= hot_raw) || (snms && v >= hot_nms)) && gi < 0x40000000u) {  // (rare: about K / HOT_DIV per list and frame)
+                            const uint32_t code = gi | ((sraw && v >= hot_raw) ? 0x40000000u : 0u) |
+                                                  ((snms && v >= hot_nms) ? 0x80000000u : 0u);
+                            const uint32_t hs = atomicAdd(&s_nhot, 1u);
+                            if (hs < (uint32_t)HOT_CAP) s_hot[hs] = code;
+                        }
                         const uint32_t bal0 = __ballot_sync(FULL, sraw), bal1 = __ballot_sync(FULL, snms);
                         off[u] = (tot0 + (uint32_t)__popc(bal0 & lanemask_lt())) |
                                  ((tot1 + (uint32_t)__popc(bal1 & lanemask_lt())) << 16);
@@ -805,55 +851,89 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             }
         }
         PROF(5);
-        cl_sync();  // survivor lists complete
-        PROF(6);
-
-        // ---- select: the CTAs split the ranking of the jobs' survivor lists; sorted composites land everywhere -------
-        unsigned long long* xs_comp = reinterpret_cast<unsigned long long*>(smem + p.off_comp);  // [job][K]
-        int last_li = 0;
-        const MergeParams& mp = *reinterpret_cast<const MergeParams*>(smem + p.off_par);
+        // survivor lists complete -- and while the barrier gathers the cluster, the head values of this CTA's hot
+        // survivors start their way from DRAM into L2: the gathers that want them run two phases from now (140 k
+        // scattered sectors per batch, DRAM random-access bound when every cluster asks for them at the same moment)
+        __syncthreads();  // (the merge parameters just parked in shared memory, by other threads)
+        cl_arrive();
         {
-            MergeSmem& msm = *reinterpret_cast<MergeSmem*>(smem + p.off_msm);
-            const int nj = p.n_jobs;
-            const bool split = (int)cs >= nj;  // else (single-CTA cluster, two jobs): one after the other
-            const int n_sel = split ? 1 : nj;
-            const int cut = (int)cs / 2;
-            for (int jj = 0; jj < n_sel; ++jj) {
-                int li = jj, part = 0, parts = 1;
-                if (split && nj == 2) {
-                    li = (int)rank < cut ? 0 : 1;
-                    part = li ? (int)rank - cut : (int)rank;
-                    parts = li ? (int)cs - cut : cut;
-                } else if (split) {
-                    li = 0, part = (int)rank, parts = (int)cs;
-                }
-                const uint32_t dst = smem_u32(xs_comp + li * K);
-                const uint32_t n_list = cl_ld(mp.list[li] ? ctr_nms : ctr_raw);  // survivors of the job's list
-                merge_select_part<ST>(mp, msm, b, li, part, parts, n_list, [&](int r, unsigned long long c) {
-                    for (uint32_t c2 = 0; c2 < cs; ++c2) {
-                        const uint32_t ra = cl_map(dst + 8u * (uint32_t)r, c2);
-                        cl_st(ra, (uint32_t)c);
-                        cl_st(ra + 4u, (uint32_t)(c >> 32));
+            const MergeParams& mpp = *reinterpret_cast<const MergeParams*>(smem + p.off_par);
+            const uint32_t* s_hot = wl + (p.wl_entries - HOT_CAP);
+            const int n_hot = (int)min(s_nhot, (uint32_t)HOT_CAP);
+            const uint32_t HWu = (uint32_t)HW;
+            // the frustum job's channels first: the association waits for them, the decode outputs are due at the frame's end
+#pragma unroll
+            for (int pass = 0; pass < 2; ++pass) {
+                const int epi = pass ? EPI_DECODE : EPI_FRUSTUM;
+                const int NS = pass ? (int)DS_N : (int)FS_N;
+                for (int li = 0; li < p.n_jobs; ++li) {
+                    const MergeJob& jb = mpp.job[li];
+                    if (jb.epilogue != epi) continue;
+                    const uint32_t flag = mpp.list[li] ? 0x80000000u : 0x40000000u;
+                    for (int t = tid; t < n_hot * NS; t += ST) {
+                        const int e = t / NS, slot = t - e * NS;
+                        const uint32_t code = s_hot[e];
+                        const float* base = jb.gt.base[slot];
+                        if ((code & flag) && base) {
+                            const uint32_t ind = (code & 0x3fffffffu) % HWu;
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(base + ((size_t)b * jb.gt.nch[slot] + jb.gt.ch[slot]) * HWu + ind));
+                        }
                     }
-                });
-                if (jj + 1 < n_sel) prefetch_winner_heads<ST>(mp, msm, b, li);  // (the next job reuses the scratch)
-                last_li = li;
+                }
             }
         }
-        PROF(7);
-        // sorted top-K of every job known to every CTA -- and while the barrier gathers the cluster, the prefetches of
-        // this CTA's winners go out
-        cl_arrive();
-        prefetch_winner_heads<ST>(mp, *reinterpret_cast<MergeSmem*>(smem + p.off_msm), b, last_li);
         cl_wait();
+        PROF(6);
+
+        // ---- select: every CTA ranks the jobs' survivor lists itself; the sorted top-K stays in its own shared memory ----
+        // (ranking twice the entries costs a CTA less than the cluster barrier and the remote deliveries a split
+        // ranking needs; the two jobs run side by side on the two halves of the CTA)
+        unsigned long long* xs_comp = reinterpret_cast<unsigned long long*>(smem + p.off_comp);  // [job][K]
+        int32_t* xs_ind = reinterpret_cast<int32_t*>(smem + p.off_ind);  // [job][K]: pixel of the ranked composite
+        const MergeParams& mp = *reinterpret_cast<const MergeParams*>(smem + p.off_par);
+        {
+            MergeSmem* msm = reinterpret_cast<MergeSmem*>(smem + p.off_msm);  // one scratch per job
+            const int nj = p.n_jobs;
+            const uint32_t n0 = cl_ld(mp.list[0] ? ctr_nms : ctr_raw);  // survivors of the jobs' lists
+            const uint32_t n1 = nj == 2 ? cl_ld(mp.list[1] ? ctr_nms : ctr_raw) : 0u;
+            if (nj == 2 && n0 <= (uint32_t)MERGE_WIN && n1 <= (uint32_t)MERGE_WIN) {
+                const int li = tid < ST / 2 ? 0 : 1;  // job of this half of the CTA (named barrier 1 + li)
+                unsigned long long* dst = xs_comp + li * K;
+                int32_t* dind = xs_ind + li * K;
+                const uint32_t HWu = (uint32_t)HW;
+                merge_select<ST / 2, false>(mp, msm[li], b, li, tid - li * (ST / 2), 1 + li, li ? n1 : n0,
+                                            [&](int r, unsigned long long c) {
+                                                dst[r] = c;
+                                                dind[r] = (int32_t)(comp_gidx(c) % HWu);
+                                            });
+            } else {  // one job, or a list that needs the exact block-level selection first: the whole CTA, job by job
+                for (int li = 0; li < nj; ++li) {
+                    unsigned long long* dst = xs_comp + li * K;
+                    int32_t* dind = xs_ind + li * K;
+                    const uint32_t HWu = (uint32_t)HW;
+                    merge_select<ST, true>(mp, msm[0], b, li, tid, 0, li ? n1 : n0, [&](int r, unsigned long long c) {
+                        dst[r] = c;
+                        dind[r] = (int32_t)(comp_gidx(c) % HWu);
+                    });
+                }
+            }
+            __syncthreads();
+        }
+        PROF(7);
+        // (no tail reads the peers' shared memory; without the frustum tail there is no later cluster barrier either, and
+        // CTA 0, which holds the lists' counters, must not run ahead into its next frame or leave)
+        if (!p.do_frustum) cl_sync();
         PROF(8);
 
         // ---- tail: detection k belongs to CTA k % CS: gathers, frustum geometry / decode outputs ----------------------
         const int n_local = (K - (int)rank + (int)cs - 1) / (int)cs;
         DetParam* sdet = reinterpret_cast<DetParam*>(smem + p.off_det);
-        merge_tail<ST>(mp, p.n_jobs, b, (int)rank, (int)cs, n_local, xs_comp, reinterpret_cast<float*>(smem + p.off_gath),
+        // (one batch and a frustum job: the decode epilogue waits until the association's finishing threads leave the upper
+        // half of the CTA idle -- its 29 channels per detection have landed long before)
+        const bool defer_decode = p.do_frustum && p.n_jobs == 2 && n_local <= p.GB && n_local <= ST / 2;
+        merge_tail<ST>(mp, p.n_jobs, b, (int)rank, (int)cs, n_local, xs_comp, xs_ind, reinterpret_cast<float*>(smem + p.off_gath),
                        p.GB, sdet, p.do_frustum ? reinterpret_cast<short4*>(smem + p.off_best) : nullptr,
-                       p.do_frustum ? s_cal : nullptr);
+                       p.do_frustum ? s_cal : nullptr, defer_decode);
         PROF(24);
         if (!p.do_frustum) continue;
 
@@ -910,8 +990,15 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 }
             }
             PROF(25);
+            if (defer_decode) cp_async_wait<0>();  // (this thread's decode copies: issued two phases ago)
             __syncthreads();
             PROF(26);
+            if (defer_decode && tid >= ST / 2) {
+                CF_PROF_SLOT(ST / 2, 35, 0);
+                merge_tail_decode(mp, p.n_jobs, b, (int)rank, (int)cs, 0, n_local, xs_comp,
+                                  reinterpret_cast<const float*>(smem + p.off_gath), p.GB, tid - ST / 2, ST / 2);
+                CF_PROF_SLOT(ST / 2, 36, 0);
+            }
             // paint records: the velocity reads of all matches go out together; every CTA of the cluster gets a copy
             // of every record in its shared memory (st.shared::cluster), in detection order
             for (int kl = tid; kl < n_local; kl += ST) {
@@ -978,7 +1065,7 @@ static size_t align_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct StagePlan {
     int cs, cs_log2, R, S, slot_floats, hist_words, slot_area, dep_off, n_clusters;
-    int off_comp, off_msm, off_gath, off_det, off_best, off_par, off_own, GB, wl_entries;
+    int off_comp, off_ind, off_msm, off_gath, off_det, off_best, off_par, off_own, GB, wl_entries;
     bool resident;
     size_t smem;
 };
@@ -1027,8 +1114,9 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
     const int n_local_max = (K + cs - 1) / cs;
     const int GB = n_local_max < 256 ? n_local_max : 256;
     const size_t off_comp = align_up_sz((size_t)K * sizeof(PaintRec), 128);
-    const size_t off_msm = align_up_sz(off_comp + 2 * (size_t)K * 8, 128);
-    const size_t off_gath = align_up_sz(off_msm + sizeof(MergeSmem), 128);
+    const size_t off_ind = align_up_sz(off_comp + 2 * (size_t)K * 8, 128);
+    const size_t off_msm = align_up_sz(off_ind + 2 * (size_t)K * 4, 128);
+    const size_t off_gath = align_up_sz(off_msm + 2 * sizeof(MergeSmem), 128);
     const size_t off_det = align_up_sz(off_gath + 2 * (size_t)GB * GATH_STRIDE * 4, 128);
     const size_t off_best = align_up_sz(off_det + (size_t)n_local_max * sizeof(DetParam), 128);
     const size_t off_par = align_up_sz(off_best + (size_t)n_local_max * 8, 128);
@@ -1056,6 +1144,7 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
     pl->slot_area = (int)area;
     pl->dep_off = dep_off;
     pl->off_comp = (int)off_comp;
+    pl->off_ind = (int)off_ind;
     pl->off_msm = (int)off_msm;
     pl->off_gath = (int)off_gath;
     pl->off_det = (int)off_det;
@@ -1198,6 +1287,7 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     p.slot_area = best.slot_area;
     p.dep_off = best.dep_off;
     p.off_comp = best.off_comp;
+    p.off_ind = best.off_ind;
     p.off_msm = best.off_msm;
     p.off_gath = best.off_gath;
     p.off_det = best.off_det;

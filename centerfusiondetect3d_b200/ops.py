@@ -340,22 +340,37 @@ def frustum_targets(pc_dep: torch.Tensor, bboxes: torch.Tensor, depth: torch.Ten
     """Row f4 -- the training-target form of the frustum association (dataset/generic_dataset.py:673-687): for every
     frame, cvtPcDepthToHeatmap of annotation 0, 1, ... in list order on a zero pc_hm.  pc_dep (B,3,H,W); bboxes (B,N,4)
     in output-map pixels; depth, distanceThreshold (B,N); counts (B) int32 annotations per frame (None = N).
-    Returns pc_hm (B,3,H,W) [, assoc (B,N) int32]."""
+    Returns pc_hm (B,3,H,W) [, assoc (B,N) int32].
+
+    All-float32 arguments follow the torch branch of cvtPcDepthToHeatmap (cf_frustum_boxes).  If any of bboxes / depth /
+    distanceThreshold is float64 the call follows the NumPy branch the reference's DataLoader runs (cf_frustum_boxes_f64,
+    NumPy >= 2 promotion): `depth` stands for the annotation's Python float (pass it as float64), and the dtypes of
+    `bboxes` and `distanceThreshold` select float32 or float64 arithmetic exactly as they do in NumPy."""
     pcd = _map(pc_dep, "pc_dep")
     B, _, H, W = pcd.shape
-    bb = _map(bboxes, "bboxes", ndim=3)
-    N = bb.shape[1]
-    if bb.shape != (B, N, 4):
+    for t, nm in ((bboxes, "bboxes"), (depth, "depth"), (distanceThreshold, "distanceThreshold")):
+        if not (isinstance(t, torch.Tensor) and t.is_cuda and t.dtype in (torch.float32, torch.float64)):
+            raise ValueError("%s must be a float32 / float64 CUDA tensor: the fusion stage has no CPU path" % nm)
+    np_branch = any(t.dtype == torch.float64 for t in (bboxes, depth, distanceThreshold))
+    dt = torch.float64 if np_branch else torch.float32
+    if bboxes.dim() != 3 or bboxes.shape[0] != B or bboxes.shape[2] != 4:
         raise ValueError("bboxes must be (B,N,4)")
-    dp = _map(depth, "depth", ndim=None).reshape(B, N)
-    th = _map(distanceThreshold, "distanceThreshold", ndim=None).reshape(B, N)
+    N = bboxes.shape[1]
+    flags = (1 if bboxes.dtype == torch.float32 else 0) | (2 if distanceThreshold.dtype == torch.float32 else 0)
+    bb = bboxes.to(dt).contiguous()
+    dp = depth.to(dt).reshape(B, N).contiguous()
+    th = distanceThreshold.to(dt).reshape(B, N).contiguous()
     cn = _map(counts, "counts", ndim=1, dtype=torch.int32) if counts is not None else None
+    _same_device(pcd, bb, dp, th, cn)
     pc_hm = torch.empty_like(pcd)
     assoc = torch.empty((B, N), dtype=torch.int32, device=pcd.device) if return_assoc else None
     ws = _workspace(pcd.device, B * N * 32 + 256)
-    _call(pcd.device, "cf_frustum_boxes", pcd.data_ptr(), bb.data_ptr(), dp.data_ptr(), th.data_ptr(), _ptr(cn), B, N, H, W,
-                                           float(max_pc_dist), pc_hm.data_ptr(), _ptr(assoc), ws.data_ptr(), ws.numel(),
-                                           _stream(pcd))
+    if np_branch:
+        _call(pcd.device, "cf_frustum_boxes_f64", pcd.data_ptr(), bb.data_ptr(), dp.data_ptr(), th.data_ptr(), _ptr(cn), B, N,
+              H, W, float(max_pc_dist), flags, pc_hm.data_ptr(), _ptr(assoc), ws.data_ptr(), ws.numel(), _stream(pcd))
+    else:
+        _call(pcd.device, "cf_frustum_boxes", pcd.data_ptr(), bb.data_ptr(), dp.data_ptr(), th.data_ptr(), _ptr(cn), B, N,
+              H, W, float(max_pc_dist), pc_hm.data_ptr(), _ptr(assoc), ws.data_ptr(), ws.numel(), _stream(pcd))
     return (pc_hm, assoc) if return_assoc else pc_hm
 
 

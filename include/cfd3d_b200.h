@@ -106,7 +106,7 @@ typedef struct {
     float* scores;       /* (B,K)   required */
     float* class_ids;    /* (B,K)   required, class id as fp32 like the reference */
     float* centers;      /* (B,K,2) required, normalised [x/W, y/H] */
-    float* bboxes;       /* (B,K,4) iff heads.wh */
+    float* bboxes;       /* (B,K,4) iff heads.wh; 16-byte aligned (written one box per store) */
     float* depth;        /* (B,K,1) iff heads.depth */
     float* rot;          /* (B,K,8) iff heads.rot */
     float* dim;          /* (B,K,3) iff heads.dim */
@@ -184,6 +184,21 @@ CF_API int cf_radar_sort(const double* points, const int32_t* counts, int B, int
 CF_API int cf_frustum_boxes(const float* pc_dep, const float* bboxes, const float* depth, const float* thr,
                             const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, float* pc_hm,
                             int32_t* assoc, void* ws, size_t ws_bytes, void* stream);
+
+/* The same loop for callers that hold NumPy arguments, as the reference's DataLoader does: the NumPy branch of
+ * cvtPcDepthToHeatmap (src/lib/utils/pointcloud.py:411-481 with lib = np) under NumPy >= 2 promotion rules.  bboxes,
+ * depth and thr are float64 (the exact container of a float32 or float64 value); flags state the dtypes the caller's
+ * arrays had, which select the arithmetic:
+ *   CF_BOX_F32  the box was float32 (transformBbox, src/lib/dataset/generic_dataset.py:507-526): centre, 0.3 * w and the
+ *               int() of the paint window are float32 operations; without it the centre is rounded to float32
+ *               (dtype=np.float32, :424-426) and w, 0.3 * w, centre -+ interval / 2 are float64;
+ *   CF_THR_F32  the threshold was np.float32 (what getDistanceThresh's NumPy branch returns): depth +- thr and the two
+ *               strict compares are float32 (the Python-float depth is weak); without it they are float64.
+ * CF_BOX_F32 | CF_THR_F32 is the DataLoader's arrangement and equals cf_frustum_boxes on the float32-rounded values. */
+enum { CF_BOX_F32 = 1, CF_THR_F32 = 2 };
+CF_API int cf_frustum_boxes_f64(const float* pc_dep, const double* bboxes, const double* depth, const double* thr,
+                                const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, int flags,
+                                float* pc_hm, int32_t* assoc, void* ws, size_t ws_bytes, void* stream);
 
 /* ---- f1  postProcess(y, center, scale, height, width, calibs, isGt)   src/lib/utils/postProcess.py:13-85 ----
  * Decoded detections (the cf_fusion_decode outputs) -> image-space boxes, camera-frame locations, yaw, velocity

@@ -38,6 +38,7 @@ def lib():
         _lib.cfo_get_alpha.restype = C.c_float
         _lib.cfo_dist_thresh_one.restype = C.c_float
         _lib.cfo_pc_dep_to_hm.restype = C.c_int32
+        _lib.cfo_pc_dep_to_hm_np.restype = C.c_int32
     return _lib
 
 
@@ -122,6 +123,20 @@ def pc_dep_to_hm(pc_hm, pc_dep, depth, bbox, thr, max_pc_dist):
     _, H, W = pc_hm.shape
     return int(lib().cfo_pc_dep_to_hm(_p(pc_hm, _f32p), _p(pc_dep, _f32p), H, W, C.c_float(float(depth)),
                                       _p(bbox, _f32p), C.c_float(float(thr)), C.c_float(float(max_pc_dist))))
+
+
+def pc_dep_to_hm_np(pc_hm, pc_dep, depth, bbox, thr, max_pc_dist):
+    """The NumPy branch as the DataLoader calls it (generic_dataset.py:673-687): depth a Python float, thr np.float32 or
+    np.float64, bbox float32 or float64 (the dtypes select the arithmetic, NumPy >= 2 promotion).  In place on pc_hm; returns the matched pixel or -1."""
+    assert pc_hm.dtype == np.float32 and pc_hm.flags.c_contiguous
+    pc_dep = _f32(pc_dep)
+    bbox = np.asarray(bbox)
+    f32 = 1 if bbox.dtype == np.float32 else 0
+    bb = _f64(bbox)
+    t32 = 1 if isinstance(thr, np.float32) or getattr(thr, "dtype", None) == np.float32 else 0
+    _, H, W = pc_hm.shape
+    return int(lib().cfo_pc_dep_to_hm_np(_p(pc_hm, _f32p), _p(pc_dep, _f32p), H, W, C.c_double(float(depth)),
+                                         _p(bb, _f64p), C.c_double(float(thr)), C.c_float(float(max_pc_dist)), f32, t32))
 
 
 def frustum_pc_hm(heat, wh, depth, dim, rot, pc_dep, calib, K, max_pc_dist):

@@ -312,6 +312,82 @@ CFO_API int32_t cfo_pc_dep_to_hm(float* pc_hm /*3,H,W in place*/, const float* p
     return (int32_t)mp;
 }
 
+/* f4: the NumPy branch of cvtPcDepthToHeatmap as the DataLoader calls it (dataset/generic_dataset.py:673-687;
+ * utils/pointcloud.py:411-481 with lib = np), under NumPy >= 2 promotion rules (NEP 50; the container has 2.3):
+ *   - pc_dep / pc_hm are float32 maps; depth is a Python float (weak).  getDistanceThresh's NumPy branch returns
+ *     np.float32 (its rotation matrix and corner arrays are float32, pointcloud.py:268-295), so in the DataLoader
+ *     depth +- thr is float32 arithmetic and the compares are float32 (thr_f32 != 0); a float64 threshold
+ *     (thr_f32 == 0) makes them float64 on the exactly widened pixel;
+ *   - bbox is float32 in the DataLoader (transformBbox, generic_dataset.py:507-526, builds it from float32 scalars):
+ *     centre, 0.3 * w and the int() of the paint window are float32 arithmetic (Python floats are weak), exactly the
+ *     torch branch (bbox_f32 != 0);  a float64 bbox (bbox_f32 == 0) keeps the centre in float32 (dtype=np.float32)
+ *     but computes w, 0.3 * w and centre - interval / 2 in float64;
+ *   - dist /= max_pc_dist stays a float32 division.
+ * Returns the matched flat pixel or -1. */
+CFO_API int32_t cfo_pc_dep_to_hm_np(float* pc_hm, const float* pc_dep, int H, int W, double depth,
+                                    const double* bbox /*x1,y1,x2,y2*/, double thr, float max_pc_dist, int bbox_f32, int thr_f32) {
+    size_t HW = (size_t)H * W;
+    double x1 = bbox[0], y1 = bbox[1], x2 = bbox[2], y2 = bbox[3];
+    float cx, cy;
+    if (bbox_f32) {
+        cx = ((float)x1 + (float)x2) / 2.0f;
+        cy = ((float)y1 + (float)y2) / 2.0f;
+    } else {
+        cx = (float)((x1 + x2) / 2.0);
+        cy = (float)((y1 + y2) / 2.0);
+    }
+    long bx0 = (long)floor(x1), by0 = (long)floor(y1), bx1 = (long)ceil(x2), by1 = (long)ceil(y2);
+    long ya, yb, xa, xb;
+    pyslice(by0, by1 + 1, H, &ya, &yb);
+    pyslice(bx0, bx1 + 1, W, &xa, &xb);
+    double hi = depth + thr;
+    double lo = depth - thr;
+    if (thr_f32) { /* Python float (weak) +- np.float32 -> float32 arithmetic, float32 compares */
+        hi = (double)((float)depth + (float)thr);
+        lo = (double)((float)depth - (float)thr);
+    }
+    if (!(lo > 0.0)) lo = 0.0; /* python max(0, t) */
+    int found = 0;
+    float best = 0.f;
+    long byy = 0, bxx = 0;
+    for (long yy = ya; yy < yb; ++yy)
+        for (long xx = xa; xx < xb; ++xx) {
+            float v = pc_dep[(size_t)yy * W + xx];
+            if (v != 0.0f && (double)v < hi && (double)v > lo && (!found || v < best)) {
+                found = 1;
+                best = v;
+                byy = yy;
+                bxx = xx;
+            }
+        }
+    if (!found) return -1;
+    size_t mp = (size_t)byy * W + bxx;
+    float dist = best / max_pc_dist;
+    float vx = pc_dep[HW + mp], vz = pc_dep[2 * HW + mp];
+    long wmin, wmax, hmin, hmax;
+    if (bbox_f32) {
+        float w = (float)x2 - (float)x1, h = (float)y2 - (float)y1;
+        float hw_ = (0.3f * w) / 2.0f, hh_ = (0.3f * h) / 2.0f;
+        wmin = (long)(cx - hw_), wmax = (long)(cx + hw_);
+        hmin = (long)(cy - hh_), hmax = (long)(cy + hh_);
+    } else {
+        double hw_ = (0.3 * (x2 - x1)) / 2.0, hh_ = (0.3 * (y2 - y1)) / 2.0;
+        wmin = (long)((double)cx - hw_), wmax = (long)((double)cx + hw_);
+        hmin = (long)((double)cy - hh_), hmax = (long)((double)cy + hh_);
+    }
+    long ra, rb, ca, cb;
+    pyslice(hmin, hmax + 1, H, &ra, &rb);
+    pyslice(wmin, wmax + 2, W, &ca, &cb);
+    for (long yy = ra; yy < rb; ++yy)
+        for (long xx = ca; xx < cb; ++xx) {
+            size_t p = (size_t)yy * W + xx;
+            pc_hm[p] = dist;
+            pc_hm[HW + p] = vx;
+            pc_hm[2 * HW + p] = vz;
+        }
+    return (int32_t)mp;
+}
+
 /* ------------------------------------------------------------------------------------------
  * a7  getPcFrustumHeatmap       utils/pointcloud.py:331-394
  * topk on the RAW heat-map (no nms, :347), gathers (:353-371), boxes (:359-367), alpha, centre,

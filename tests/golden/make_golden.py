@@ -308,6 +308,75 @@ def gen_cfg1_model():
     save("cfg1_model", **arrs)
 
 
+def gen_gt_assoc():
+    """Row f4 on the reference's REAL branch: the DataLoader's per-annotation loop (dataset/generic_dataset.py:673-687)
+    calls getDistanceThresh and cvtPcDepthToHeatmap with NumPy arguments (the `lib = np` branch of
+    utils/pointcloud.py:411-481): pc_dep / pc_hm float32 maps, depth a Python float, distanceThreshold np.float32 (what
+    the NumPy branch of getDistanceThresh returns), bbox float32 (transformBbox, generic_dataset.py:507-526).  Two frames x 128 annotations in that arrangement (boxes
+    clipped to the map like transformBbox does), plus one frame of float64 boxes crossing every border with float64 thresholds (what any
+    other NumPy caller of the function may pass: float64 compares and paint-window arithmetic under NumPy >= 2).  Stored: inputs, the reference's thresholds, pc_hm after the whole loop and
+    the matched pixel of every annotation (index trick of SURVEY.md 8c)."""
+    H, W, N = 112, 200, 128
+    cfg = refimport.make_config(K=100, out_hw=(H, W))
+    rng = np.random.default_rng(77)
+    frames = []
+    for f in range(3):
+        pts, _ = syn.make_radar(rng, 1, 300)
+        calib64 = syn.make_calib(rng, 1)
+        pc_dep = ref_pc_dep_from_points(ns, pts[0], calib64[0], syn.output_affine(H, W), (1600, 900), cfg)
+        calib = calib64[0].astype(np.float32)
+        cx, cy = rng.uniform(-8, W + 8, N), rng.uniform(-8, H + 8, N)
+        w, h = rng.uniform(0.5, 70, N), rng.uniform(0.5, 45, N)
+        bb = np.stack([cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2], -1)
+        f32 = f < 2
+        if f32:  # transformBbox: float32, clipped into the map
+            bb = bb.astype(np.float32)
+            bb[:, [0, 2]] = np.clip(bb[:, [0, 2]], 0, W - 1)
+            bb[:, [1, 3]] = np.clip(bb[:, [1, 3]], 0, H - 1)
+        dvals = np.unique(pc_dep[0][pc_dep[0] != 0]).astype(np.float64)
+        depth = dvals[rng.integers(0, len(dvals), N)] + rng.normal(0, 2.5, N)  # near real pillar depths: many matches
+        depth = np.maximum(depth, 0.5)
+        dim = np.stack([rng.uniform(1.2, 3.5, N), rng.uniform(0.5, 2.6, N), rng.uniform(0.6, 11, N)], -1)
+        alpha = rng.uniform(-np.pi, np.pi, N)
+        thr = np.zeros(N, np.float64)
+        assoc = np.full(N, -1, np.int32)
+        pc_hm = np.zeros((3, H, W), np.float32)
+        idxmap = pc_dep.copy()
+        idxmap[1] = np.arange(H * W, dtype=np.float32).reshape(H, W)
+        for i in range(N):
+            bbox = bb[i]
+            center = np.array([(bbox[0] + bbox[2]) / 2, (bbox[1] + bbox[3]) / 2], dtype=np.float32)  # :545-547
+            t_ = ns.getDistanceThresh(calib.reshape(1, 3, 4), center.reshape(1, 1, 2), np.array(list(dim[i])).reshape(1, 1, 3),
+                                      np.array(float(alpha[i])).reshape(1, 1, 1))[0, 0]
+            t_ = t_.reshape(-1)[0]
+            assert isinstance(t_, np.float32)  # the NumPy branch of get3DCorners works in float32 arrays
+            if not f32:
+                t_ = np.float64(t_)  # the generic caller: a float64 threshold (float64 compares)
+            thr[i] = t_
+            # keep the strict compares clear of every pillar depth (thr is an INPUT of the op here, so only the
+            # decimal -> binary of the stored values matters; a margin keeps the fixture robust all the same)
+            for bound in (float(depth[i]) + float(t_), max(0.0, float(depth[i]) - float(t_))):
+                if np.abs(dvals - bound).min() < 1e-4:
+                    depth[i] += 3e-3
+            ns.cvtPcDepthToHeatmap(pc_hm, pc_dep, float(depth[i]), bbox, t_, 60.0)
+            probe = np.zeros((3, H, W), np.float32)
+            ns.cvtPcDepthToHeatmap(probe, idxmap, float(depth[i]), bbox, t_, 60.0)
+            wr = probe[0] != 0
+            if wr.any():
+                assoc[i] = int(probe[1][wr][0])
+            else:
+                assoc[i] = -2  # no match, or a match whose paint window is empty: undecidable from the outside
+        print("gt_assoc frame", f, "float32 boxes" if f32 else "float64 boxes", "matched", int((assoc >= 0).sum()), "of", N)
+        frames.append(dict(pc_dep=pc_dep, bbox=bb.astype(np.float64), bbox_f32=np.bool_(f32), depth=depth, thr=thr,  # (f32 frames: thr holds float32 values)
+                           pc_hm=pc_hm, assoc=assoc))
+    arrs = {}
+    for f, fr in enumerate(frames):
+        arrs.update({"in_pc_dep_%d" % f: fr["pc_dep"], "in_bbox_%d" % f: fr["bbox"], "in_bbox_f32_%d" % f: fr["bbox_f32"],
+                     "in_depth_%d" % f: fr["depth"], "in_thr_%d" % f: fr["thr"], "out_pc_hm_%d" % f: fr["pc_hm"],
+                     "out_assoc_%d" % f: fr["assoc"]})
+    save("gt_assoc", in_max_pc_dist=np.float32(60.0), in_frames=np.int64(len(frames)), **arrs)
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1:  # python tests/golden/make_golden.py gen_cfg1_model
         for name in sys.argv[1:]:
@@ -320,3 +389,4 @@ if __name__ == "__main__":
     gen_frustum_and_decode()
     gen_post_process()
     gen_cfg1_model()
+    gen_gt_assoc()

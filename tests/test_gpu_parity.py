@@ -394,6 +394,22 @@ def test_frustum_targets(ops, oracle):
     assert (assoc_o >= 0).sum() >= 5
 
 
+def test_golden_gt_association_numpy_branch(ops):
+    """f4 on the reference's real branch: fixture generated by the NumPy form of cvtPcDepthToHeatmap under the
+    DataLoader's loop (generic_dataset.py:673-687) -- float32 boxes + np.float32 thresholds + Python-float depths (its
+    own arrangement) and float64 boxes / thresholds crossing every border (generic NumPy caller)."""
+    from test_oracle_golden import gt_assoc_frames
+    for f, f32, pc_dep, bb, depth, thr, hm_ref, assoc_ref, mx in gt_assoc_frames():
+        hm, assoc = ops.frustum_targets(cu(pc_dep[None]), cu(bb[None]), cu(depth[None]), cu(thr[None]), None, mx,
+                                        return_assoc=True)
+        known = assoc_ref != -2
+        assert np.array_equal(npy(assoc)[0][known], assoc_ref[known]), f
+        eq(npy(hm)[0], hm_ref, "pc_hm frame %d" % f)
+        if f32:  # all-float32 arguments (depth rounded like NumPy's weak Python float): the torch-branch kernel agrees
+            hm2 = ops.frustum_targets(cu(pc_dep[None]), cu(bb[None]), cu(depth.astype(np.float32)[None]), cu(thr[None]), None, mx)
+            eq(npy(hm2)[0], hm_ref, "pc_hm frame %d, fp32 entry point" % f)
+
+
 def test_post_process(ops, oracle):
     """f1 postProcess: the kernel against the oracle (bit-exact apart from the fp64-rounded trigonometry, 1e-6) and
     against the reference's own outputs (golden fixture, 1e-5 relative: north_star's bar for decoded boxes)."""

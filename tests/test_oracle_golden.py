@@ -164,3 +164,33 @@ def test_cfg1_whole_model_fixture(oracle):
     post = oracle.post_process({k: g["out_dec_" + k].copy() for k in ref_keys}, g["in_trans"], (H, W), g["in_calib"], False)
     for k in (k[len("out_post_"):] for k in g if k.startswith("out_post_")):
         np.testing.assert_allclose(post[k], g["out_post_" + k], rtol=1e-5, atol=1e-5, err_msg=k)
+
+
+def gt_assoc_frames():
+    g = load_golden("gt_assoc")
+    for f in range(int(g["in_frames"])):
+        f32 = bool(g["in_bbox_f32_%d" % f])
+        bb = g["in_bbox_%d" % f].astype(np.float32) if f32 else g["in_bbox_%d" % f]
+        thr = g["in_thr_%d" % f].astype(np.float32) if f32 else g["in_thr_%d" % f]
+        yield f, f32, g["in_pc_dep_%d" % f], bb, g["in_depth_%d" % f], thr, g["out_pc_hm_%d" % f], g["out_assoc_%d" % f], \
+            float(g["in_max_pc_dist"])
+
+
+def test_gt_association_numpy_branch(oracle):
+    """f4: the DataLoader's NumPy branch of cvtPcDepthToHeatmap (generic_dataset.py:673-687) -- fixture generated by
+    the reference with float32 boxes / thresholds (its own arrangement) and with float64 ones (generic caller)."""
+    total = 0
+    for f, f32, pc_dep, bb, depth, thr, hm_ref, assoc_ref, mx in gt_assoc_frames():
+        hm = np.zeros_like(pc_dep)
+        assoc = np.array([oracle.pc_dep_to_hm_np(hm, pc_dep, float(depth[i]), bb[i], thr[i], mx) for i in range(len(bb))])
+        known = assoc_ref != -2
+        assert np.array_equal(assoc[known], assoc_ref[known]), f
+        assert (assoc[~known] == -1).sum() + (assoc[~known] >= 0).sum() == (~known).sum()
+        assert np.array_equal(hm.view(np.uint32), hm_ref.view(np.uint32)), f
+        total += int((assoc_ref >= 0).sum())
+        if f32:  # the all-float32 arrangement is the torch branch's arithmetic: the fp32 restatement agrees
+            hm2 = np.zeros_like(pc_dep)
+            for i in range(len(bb)):
+                oracle.pc_dep_to_hm(hm2, pc_dep, np.float32(depth[i]), bb[i], thr[i], mx)
+            assert np.array_equal(hm2.view(np.uint32), hm_ref.view(np.uint32))
+    assert total >= 80
