@@ -885,6 +885,16 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         cl_wait();
         PROF(6);
 
+        // Several frames per cluster, shares resident: this CTA's share of the NEXT frame's heat-map starts its way from HBM
+        // into L2 now, under the once-per-frame phases that leave the memory system idle (one bulk prefetch; a round's
+        // shares together are a fraction of the L2).  Pass A of the next frame then streams from L2.
+        if (resident && b + n_clusters < p.B && tid == 64) {
+            const char* nf = reinterpret_cast<const char*>(p.heat + (size_t)(b + n_clusters) * CH * W + (size_t)row_begin * W);
+            const uint32_t nbytes = (uint32_t)((size_t)(row_end - row_begin) * W * 4) & ~15u;
+            if (nbytes && ((reinterpret_cast<uintptr_t>(nf) & 15u) == 0))
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(nf), "r"(nbytes) : "memory");
+        }
+
         // ---- select: every CTA ranks the jobs' survivor lists itself; the sorted top-K stays in its own shared memory ----
         // (ranking twice the entries costs a CTA less than the cluster barrier and the remote deliveries a split
         // ranking needs; the two jobs run side by side on the two halves of the CTA)
