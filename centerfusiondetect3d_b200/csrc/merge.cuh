@@ -475,8 +475,8 @@ __device__ __forceinline__ void merge_tail_decode(const MergeParams& p, int n_jo
 // association waits for them, the decode job's 29 channels per detection follow -- 140 k scattered sectors per batch hit
 // the DRAM at the same moment from every cluster, and whoever is served last sets the pace of the phase.  The frustum
 // epilogue starts as soon as ITS group has landed.  defer_decode (one batch only): the decode epilogue is left to the
-// caller (merge_tail_decode on the upper half of the CTA while the association's finishing threads wait for their
-// velocity reads), who first has every thread wait for its copies and passes a CTA barrier.
+// caller (merge_tail_decode on a few warps beside the association's ROI scans); the closing barrier here comes after
+// every thread has waited for its decode copies.
 template <int T>
 __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int b, int first, int stride, int n_local,
                                            const unsigned long long* xs_comp, const int32_t* xs_ind, float* gath, int GB,
@@ -512,8 +512,8 @@ __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int
                                  sdet, sroi, cal, tid, T);
         }
         CF_MERGE_PROF(7);
+        cp_async_wait<0>();  // (this thread's decode copies: prefetched into L2 long ago, issued a phase ago)
         if (!defer_decode) {
-            cp_async_wait<0>();
             __syncthreads();
             merge_tail_decode(p, n_jobs, b, first, stride, kl0, nb, xs_comp, gath, GB, tid, T);
         }

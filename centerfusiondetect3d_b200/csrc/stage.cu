@@ -960,10 +960,34 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             PROF(32);
             // (the ROI bounds of detection kl wait in sbest[kl], left there by the epilogue's idle warps: this loop runs
             // once per detection on one warp and is priced by its instruction count)
-            if (p.dep_off >= 0) {
-                for (int kl = warp;; kl = SNW) {
-                    if (kl >= SNW) {  // first detection by warp index, the rest from the shared counter (big ROIs wait less)
-                        if (lane == 0) kl = SNW + (int)atomicAdd(&s_nfl, 1u);
+            // (deferred decode epilogue: the last DW warps run it now, beside the scans of the others -- its copies landed
+            // before the tail's closing barrier)
+            constexpr int DW = 3;
+            const int nsw = defer_decode ? SNW - DW : SNW;  // scanning warps
+            // The two velocity values of a match are LOADED by the warp that found it (lanes 0, 1) and parked in the
+            // detection's parameters one scan later (the box corners there are dead by now): the finishing threads below
+            // then wait for no memory at all.
+            float vpend = 0.0f;
+            int klpend = -1;
+            auto park_vel = [&]() {
+                if (klpend >= 0 && lane < 2) reinterpret_cast<float*>(&sdet[klpend])[lane] = vpend;
+            };
+            auto load_vel = [&](int kl, unsigned long long best) {
+                park_vel();
+                klpend = kl;
+                vpend = 0.0f;
+                if (lane < 2 && best != ~0ull)
+                    vpend = __ldg(p.pc_vel + (size_t)b * 3 * HW + (size_t)(lane + 1) * HW + (uint32_t)best);
+            };
+            if (warp >= nsw) {
+                CF_PROF_SLOT(ST - DW * 32, 35, 0);
+                merge_tail_decode(mp, p.n_jobs, b, (int)rank, (int)cs, 0, n_local, xs_comp,
+                                  reinterpret_cast<const float*>(smem + p.off_gath), p.GB, tid - (ST - DW * 32), DW * 32);
+                CF_PROF_SLOT(ST - DW * 32, 36, 0);
+            } else if (p.dep_off >= 0) {
+                for (int kl = warp;; kl = nsw) {
+                    if (kl >= nsw) {  // first detection by warp index, the rest from the shared counter (big ROIs wait less)
+                        if (lane == 0) kl = nsw + (int)atomicAdd(&s_nfl, 1u);
                         kl = __shfl_sync(FULL, kl, 0);
                     }
                     if (kl >= n_local) break;
@@ -973,12 +997,10 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     const unsigned long long best =
                         warp_min_key(roi_scan_box<8, true>(dep0, W, roi.x, roi.y, roi.z, roi.w, dt.x, dt.y, lane, 32));
                     if (lane == 0) sbest[kl] = best;
-                    if (lane < 2 && best != ~0ull) {  // the match's two velocity values: on their way into L1 for the record
-                        const float* v = p.pc_vel + (size_t)b * 3 * HW + (size_t)(lane + 1) * HW + (uint32_t)best;
-                        asm volatile("prefetch.global.L1 [%0];" ::"l"(v));
-                    }
+                    load_vel(kl, best);
                     if (kl == 0) PROF_DEP(33, (uint32_t)best);
                 }
+                park_vel();
             } else {
                 // A plane too big to stage is read from L2: float4 row loads (fewer, wider requests; the staged plane
                 // is bound by its per-pixel tests, and the narrow ROIs of the reference sizes fill a warp better pixel
@@ -997,24 +1019,19 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                         quads ? roi_scan_box4<8>(dep0, W, roi.x, roi.y, roi.z, roi.w, dt.x, dt.y, lane)
                               : roi_scan_box<24, true>(dep0, W, roi.x, roi.y, roi.z, roi.w, dt.x, dt.y, lane, 32));
                     if (lane == 0) sbest[kl] = best;
+                    load_vel(kl, best);
                 }
+                park_vel();
             }
             PROF(25);
-            if (defer_decode) cp_async_wait<0>();  // (this thread's decode copies: issued two phases ago)
             __syncthreads();
             PROF(26);
-            if (defer_decode && tid >= ST / 2) {
-                CF_PROF_SLOT(ST / 2, 35, 0);
-                merge_tail_decode(mp, p.n_jobs, b, (int)rank, (int)cs, 0, n_local, xs_comp,
-                                  reinterpret_cast<const float*>(smem + p.off_gath), p.GB, tid - ST / 2, ST / 2);
-                CF_PROF_SLOT(ST / 2, 36, 0);
-            }
             // paint records: the velocity reads of all matches go out together; every CTA of the cluster gets a copy
             // of every record in its shared memory (st.shared::cluster), in detection order
             for (int kl = tid; kl < n_local; kl += ST) {
                 const int k = (int)rank + kl * (int)cs;
                 const size_t o = (size_t)b * K + k;
-                const PaintRec r = assoc_finalize(sbest[kl], p.pc_vel + (size_t)b * 3 * HW, H, W, sdet[kl], p.max_pc_dist, p.assoc ? p.assoc + o : nullptr);
+                const PaintRec r = assoc_record(sbest[kl], sdet[kl].x1, sdet[kl].y1, sdet[kl], p.max_pc_dist, p.assoc ? p.assoc + o : nullptr);
                 const uint32_t* rw = reinterpret_cast<const uint32_t*>(&r);
                 PROF_DEP(34, rw[0] ^ rw[1] ^ rw[2] ^ rw[3] ^ rw[4]);
                 const uint32_t dst = smem_u32(srecs + k);
@@ -1054,12 +1071,13 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
 // Development switches, read from the environment ONCE per process (never on the launch path).
 struct StageEnv {
     bool verbose, no_pdl;
-    int prof;
+    int prof, force_cs;
     long long chunk_bytes;
     StageEnv() {
         verbose = getenv("CFD3D_VERBOSE") != nullptr;
         no_pdl = getenv("CFD3D_NO_PDL") != nullptr;
         prof = getenv("CFD3D_PROF") ? atoi(getenv("CFD3D_PROF")) : 0;
+        force_cs = getenv("CFD3D_FORCE_CS") ? atoi(getenv("CFD3D_FORCE_CS")) : 0;  // plan exploration (tools/plan_sweep.sh)
         chunk_bytes = 8192;
         if (const char* e = getenv("CFD3D_CHUNK_BYTES")) {
             if (atoll(e) >= 256) chunk_bytes = atoll(e);
@@ -1094,9 +1112,22 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
     if (R > share) R = share;
     // 16-bit histogram counters: a frame must not have more than 65535 lane groups
     while (((share + R - 1) / R) * 32 * cs > 65535) ++R;
-    const size_t slot_bytes = align_up_sz((size_t)R * Wp * 4, 16);
     const int hist_words = 2 * (HIST_BINS / cs) / 2;
     size_t fixed = (size_t)hist_words * 4 + (size_t)WL_CAP * sizeof(uint32_t);
+    // A share that fits the shared memory as a whole but not as a whole number of default-sized chunks (full-resolution
+    // maps on clusters of 16: 141 rows of 1600 bytes) stays resident with smaller chunks: a resident share is read from
+    // HBM once and filtered out of shared memory, a streamed one is fetched twice.
+    if (use_tma && (size_t)share * Wp * 4 + fixed <= SMEM_DYN_CAP) {
+        for (long long r = R; r >= 1; --r) {
+            const long long nn = (share + r - 1) / r;
+            if (nn > MAX_SLOTS || nn * 32 * cs > 65535) break;
+            if ((size_t)nn * align_up_sz((size_t)r * Wp * 4, 16) + fixed <= SMEM_DYN_CAP) {
+                R = r;
+                break;
+            }
+        }
+    }
+    const size_t slot_bytes = align_up_sz((size_t)R * Wp * 4, 16);
     if (fixed + slot_bytes > SMEM_DYN_CAP) return false;
     const long long n = (share + R - 1) / R;
     long long S = (long long)((SMEM_DYN_CAP - fixed) / slot_bytes);
@@ -1228,7 +1259,7 @@ static bool choose_plan(int dev, int B, int C, int H, int W, int K, bool use_tma
     typedef std::tuple<int, int, int, int, int, int, int, int, int> Key;
     static std::mutex mu;
     static std::map<Key, std::pair<bool, StagePlan>> cache;
-    const int force_cs = g_force_cs.load(), force_cap = g_force_cap.load();
+    const int force_cs = g_force_cs.load() ? g_force_cs.load() : stage_env().force_cs, force_cap = g_force_cap.load();
     const Key key(dev, B, C, H, W, K, (use_tma ? 1 : 0) | (stage_dep ? 2 : 0), force_cs, force_cap);
     {
         std::lock_guard<std::mutex> g(mu);
@@ -1240,7 +1271,7 @@ static bool choose_plan(int dev, int B, int C, int H, int W, int K, bool use_tma
     }
     StagePlan best;
     memset(&best, 0, sizeof(best));
-    long long best_rounds = -1;
+    long long best_rounds = -1, best_num = 0, best_den = 1;
     for (int cs = MAX_CS; cs >= 1; cs >>= 1) {
         if (force_cs && cs != force_cs) continue;
         StagePlan pl;
@@ -1250,11 +1281,19 @@ static bool choose_plan(int dev, int B, int C, int H, int W, int K, bool use_tma
         if (stage_env().verbose) fprintf(stderr, "[cfd3d]   cs=%d: %d co-resident clusters (smem %zu)\n", cs, cap, pl.smem);
         if (cap < 1) continue;
         pl.n_clusters = B < cap ? B : cap;
-        // a round over a resident share costs about a third of one that streams its share twice (measured, README)
-        const long long rounds = (((long long)B + pl.n_clusters - 1) / pl.n_clusters) * (pl.resident ? 1 : 3);
-        if (best_rounds < 0 || rounds < best_rounds) {
+        // Cost of a plan = rounds x the weight of one round.  A round over a resident share weighs 1; a round that streams
+        // its share twice weighs 1 + 2 / cs (measured on B200, tools/plan_sweep.sh: 3 for single-CTA clusters, whose CTA
+        // also runs the whole tail of its frame alone, 2 for pairs, 1.25 for clusters of 8).  Ties go to the plan with
+        // fewer rounds, then to the larger cluster.
+        const long long rounds = ((long long)B + pl.n_clusters - 1) / pl.n_clusters;
+        const long long num = rounds * (cs + (pl.resident ? 0 : 2)), den = cs;
+        const bool better = best_rounds < 0 || num * best_den < best_num * den ||
+                            (num * best_den == best_num * den && rounds < best_rounds);
+        if (better) {
             best = pl;
             best_rounds = rounds;
+            best_num = num;
+            best_den = den;
         }
     }
     std::lock_guard<std::mutex> g(mu);

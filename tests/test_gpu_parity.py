@@ -249,8 +249,8 @@ def test_oracle_stage_forced_plans(ops, oracle, cfg_name, B, cs):
 # the plans bench.py runs (no forcing): workload, frames per GPU, expected (cluster size, resident share, staged plane)
 BENCH_PLANS = [("cfg2", 32, dict(cluster_size=4, n_clusters=32, rounds=1, resident=1, depth_plane_staged=1)),
                ("cfg3", 256, None),
-               ("cfg4", 64, dict(cluster_size=4, resident=1, depth_plane_staged=1, rounds=2)),
-               ("cfg5", 8, dict(n_clusters=8, rounds=1))]
+               ("cfg4", 64, dict(cluster_size=2, n_clusters=64, resident=0, rounds=1)),
+               ("cfg5", 8, dict(cluster_size=8, n_clusters=8, rounds=1))]
 
 
 @pytest.mark.parametrize("cfg_name,B,expect", BENCH_PLANS)

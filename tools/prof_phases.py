@@ -63,7 +63,7 @@ for rep in range(6):
     tl = np.diff(buf[:, [8, 19, 20]], axis=1) / 1.965e3
     for r in range(min(CS, 4)):
         print("   rank %d: select load %.2f  rank %.2f | tail gather %.2f  epilogue %.2f" % ((r,) + tuple(mg[r::CS].mean(axis=0)) + tuple(tl[r::CS].mean(axis=0))))
-    print("   deferred decode epilogue (thread 256): start after scans' barrier %.2f  duration %.2f" % tuple((np.diff(buf[:, [26, 35, 36]], axis=1) / 1.965e3).mean(axis=0)))
+    print("   deferred decode epilogue (first thread of the decode warps): start after the tail %.2f  duration %.2f" % tuple((np.diff(buf[:, [24, 35, 36]], axis=1) / 1.965e3).mean(axis=0)))
     print("   passB: loop %.2f  sync %.2f  atomics+sync %.2f  copy %.2f" % tuple((np.diff(ex[1], axis=1) / 1.965e3).mean(axis=0)))
     print("   passB loop per CTA (warp 0):", " ".join("%.0f" % x for x in (buf[:, 12] - buf[:, 4]) / 1.965e3))
     print("   passB: barrier waits %.2f flags %.2f sync %.2f" % tuple((np.diff(buf[:, [4, 30, 31, 29]], axis=1) / 1.965e3).mean(axis=0)))
