@@ -58,6 +58,7 @@ constexpr int SNW = ST / 32;     // warps
 constexpr int WL_CAP = 640;      // pass-B work list: candidate pixels a CTA parks before it tests them side by side
 constexpr int WL_CAP_RING = 4096;  // ... when the share streams through a ring of slots (shared memory to spare)
 constexpr int FL_CAP = 256;      // pass-B flagged-group list (resident shares)
+constexpr int FL_CAP_STREAM = 2048;  // ... of a streamed share (a CTA of a small cluster holds several times the rows)
 constexpr int HOT_CAP = 192;     // hot list: survivors whose head values are prefetched early (a hint: overflow is dropped)
 constexpr int HOT_DIV = 2;       // raw list: hot = at or above the bound of the K / HOT_DIV largest group maxima (covers nearly
                                  // all winners at ~1.3 x K entries; the nms'd list has only ~1.3 x K survivors: all are hot)
@@ -179,6 +180,8 @@ struct StageParams {
     int off_comp, off_ind, off_msm, off_gath, off_det, off_best, off_par, off_own;
     int GB;            // detections per gather batch
     int wl_entries;    // words of the pass-B work list
+    int gmax_off;      // streamed shares: byte offset (from the histogram) of the per-(chunk, lane) group maxima, then the flagged list
+    int fl_cap;        // capacity of the flagged-group list
     uint32_t* ctr;
     unsigned long long* cand;
     MergeParams mp;
@@ -329,10 +332,13 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     // this CTA's rows of the frame matrix, in chunks of R rows
     const int row_begin = (int)((long long)CH * rank / cs), row_end = (int)((long long)CH * (rank + 1) / cs);
     const int n = (row_end - row_begin + R - 1) / R;   // chunks
-    const int n_res = n < S ? n : S;                   // chunks still resident when pass B starts
-    const int n_ref = n - n_res;                       // chunks pass B fetches again
-    const int LPF = n + n_ref;                         // bulk copies per frame
-    const bool resident = use_tma && n_ref == 0;
+    const int LPF = n;                                 // bulk copies per frame: every chunk once
+    const bool resident = use_tma && n <= S;           // the share stays in shared memory between the two looks
+    const bool stream1 = use_tma && !resident;         // streamed through the slot ring once; the filter pass reads the
+                                                       // flagged groups again from global memory (L2)
+    // streamed shares: group maximum per (chunk, lane), then the long flagged-group list
+    float* s_gm = reinterpret_cast<float*>(smem + p.slot_area + p.gmax_off);
+    uint16_t* fl_list = stream1 ? reinterpret_cast<uint16_t*>(s_gm + (size_t)n * 32) : s_fl;
 
     // The merge parameters (two jobs with their head tables) are indexed at run time (job of this half of the CTA, head
     // channel of this thread).  Out of the kernel's parameter space such a read costs microseconds the first time, so
@@ -526,7 +532,9 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 if (want_nms) hist_add_cluster(hist_saddr, list_words, 1, knms, p.cs_log2);
                 tkraw = max(tkraw, kraw);
                 tknms = max(tknms, knms);
-                {
+                if (stream1) {
+                    s_gm[q * 32 + lane] = best;
+                } else {
                     const int ci = q / SNW;
                     if (ci == 0) gmax[0] = best;
                     else if (ci == 1) gmax[1] = best;
@@ -534,7 +542,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     else if (ci == 3) gmax[3] = best;
                 }
                 // a chunk that will not stay resident frees its slot: this warp starts the copy that reuses it
-                if (use_tma && q < n - n_res) {
+                if (use_tma && q + S < n) {
                     __syncwarp();
                     if (lane == 0 && q + S < LPF) issue_load(q + S);
                 }
@@ -631,7 +639,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             // (the last HOT_CAP words of the work list hold the hot list)
             const uint32_t wl_cap = resident ? 2u * (uint32_t)(p.wl_entries - HOT_CAP) : (uint32_t)(p.wl_entries - HOT_CAP);
             uint32_t* s_hot = wl + (p.wl_entries - HOT_CAP);
-            auto park = [&](uint32_t mask, uint32_t slot, int q, auto&& item_of) {
+            auto park = [&](uint32_t mask, uint32_t slot, auto&& code_of) {  // code_of(bit): (chunk << 16) | 4 * item of bit's float4
                 for (;;) {
                     const bool mine = mask != 0u;
                     const uint32_t bal = __ballot_sync(FULL, mine);
@@ -641,7 +649,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     if (!mine) continue;
                     const int bit = __ffs(mask) - 1;
                     mask &= mask - 1;
-                    const uint32_t code = ((uint32_t)q << 16) | (uint32_t)(item_of(bit) * 4 + (bit & 3));
+                    const uint32_t code = (uint32_t)code_of(bit) + (uint32_t)(bit & 3);
                     if (my < wl_cap) {
                         if (resident) wl16[my] = (uint16_t)code;  // q == 0: the pixel index alone, and it fits 16 bits
                         else wl[my] = code;
@@ -661,82 +669,95 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     }
                 }
             };
-            // Resident share, fast path: pass A left every lane the maximum of each of its groups, so the groups that
-            // hold a candidate are known without touching the share again.  They go to a CTA-wide list, and half-warps
-            // rescan just those (a group = 1/32 of a chunk), whichever warp found them.
+            // Fast path: pass A left the maximum of every group (a group = the 1/32 of a chunk one lane took) -- in
+            // registers when the share is resident, in shared memory when it streamed through the ring -- so the groups
+            // that hold a candidate are known without touching the share again.  They go to a CTA-wide list, and half-warps
+            // rescan just those, whichever warp found them: out of shared memory (resident), or out of global memory, where
+            // the chunks have just passed through L2 (streamed: a few hundred groups of 16 sectors instead of a second
+            // pass over the whole share).
             bool scanned = false;
-            if (resident) {
-                // (every chunk's copy was awaited by the warp that took the chunk in pass A; the CTA barrier below
-                // orders those observations before the reads of all the other warps)
+            if (resident || stream1) {
+                // (resident: every chunk's copy was awaited by the warp that took the chunk in pass A; the CTA barrier
+                // below orders those observations before the reads of all the other warps)
                 PROF(30);
-#pragma unroll
-                for (int ci = 0; ci < 4; ++ci) {
+                const int n_ci = (n + SNW - 1) / SNW;
+                for (int ci = 0; ci < n_ci; ++ci) {
                     const int q = warp + ci * SNW;
-                    const bool flag = q < n && gmax[ci] >= tau_min;
+                    float gm = -INF;
+                    if (stream1) {
+                        if (q < n) gm = s_gm[q * 32 + lane];
+                    } else {
+                        gm = ci == 0 ? gmax[0] : (ci == 1 ? gmax[1] : (ci == 2 ? gmax[2] : gmax[3]));
+                    }
+                    const bool flag = q < n && gm >= tau_min;
                     const uint32_t bal = __ballot_sync(FULL, flag);
                     if (bal) {
                         uint32_t base = 0u;
                         if (lane == 0) base = atomicAdd(&s_nfl, (uint32_t)__popc(bal));
                         base = __shfl_sync(FULL, base, 0) + (uint32_t)__popc(bal & lanemask_lt());
-                        if (flag && base < (uint32_t)FL_CAP) s_fl[base] = (uint16_t)((q << 5) | lane);
+                        if (flag && base < (uint32_t)p.fl_cap) fl_list[base] = (uint16_t)((q << 5) | lane);
                     }
                 }
                 PROF(31);
                 __syncthreads();
                 const int nfl = (int)s_nfl;
                 PROF(29);
-                scanned = nfl <= FL_CAP;  // else (dense frame): the block scan below
+                scanned = nfl <= p.fl_cap;  // else (dense frame): the block scan below
                 if (scanned) {
-                    // every half-warp takes up to FL_CAP/32 groups; a lane collects the candidate bits of all of them in
+                    // every half-warp takes up to 8 groups per round; a lane collects the candidate bits of all of them in
                     // one register first (loads back to back), so that the reservation and the parking happen once
                     const int hw = tid >> 4, hl = tid & 15;
                     const int chunk_items = R * W4, t_max = (chunk_items + 31) >> 5;
-                    const float4* c4p = reinterpret_cast<const float4*>(slots);
-                    for (int t0 = 0; t0 < t_max; t0 += 16) {
-                        uint32_t mask = 0u;
+                    const float4* c4p = resident ? reinterpret_cast<const float4*>(slots)
+                                                 : reinterpret_cast<const float4*>(frame + (size_t)row_begin * W);
+                    for (int f0 = 0; f0 < nfl; f0 += 8 * (ST / 16)) {
+                        for (int t0 = 0; t0 < t_max; t0 += 16) {
+                            uint32_t mask = 0u;
 #pragma unroll
-                        for (int u = 0; u < FL_CAP / 32; ++u) {
-                            const int f = u * 32 + hw;
-                            if (f < nfl) {
-                                const int code = (int)s_fl[f];
-                                const int q = code >> 5, i = (code & 31) + 32 * (t0 + hl);
-                                if (i < min(R, row_end - (row_begin + q * R)) * W4) {
-                                    const float4 v = c4p[q * chunk_items + i];  // the slots of a resident share are contiguous
-                                    const uint32_t m4 = (v.x >= tau_min ? 1u : 0u) | (v.y >= tau_min ? 2u : 0u) |
-                                                        (v.z >= tau_min ? 4u : 0u) | (v.w >= tau_min ? 8u : 0u);
-                                    mask |= m4 << (4 * u);
+                            for (int u = 0; u < 8; ++u) {
+                                const int f = f0 + u * (ST / 16) + hw;
+                                if (f < nfl) {
+                                    const int code = (int)fl_list[f];
+                                    const int q = code >> 5, i = (code & 31) + 32 * (t0 + hl);
+                                    if (i < min(R, row_end - (row_begin + q * R)) * W4) {
+                                        const float4 v = c4p[q * chunk_items + i];  // (chunks are contiguous in both memories)
+                                        const uint32_t m4 = (v.x >= tau_min ? 1u : 0u) | (v.y >= tau_min ? 2u : 0u) |
+                                                            (v.z >= tau_min ? 4u : 0u) | (v.w >= tau_min ? 8u : 0u);
+                                        mask |= m4 << (4 * u);
+                                    }
                                 }
                             }
+                            const uint32_t total = __reduce_add_sync(FULL, (uint32_t)__popc(mask));
+                            if (!total) continue;
+                            uint32_t slot = 0u;
+                            if (lane == 0) slot = atomicAdd(&s_nwl, total);
+                            slot = __shfl_sync(FULL, slot, 0);
+                            park(mask, slot, [&](int bit) {
+                                const int code = (int)fl_list[f0 + (bit >> 2) * (ST / 16) + hw];
+                                const int q = code >> 5, i = (code & 31) + 32 * (t0 + hl);
+                                // resident: one contiguous tile, the pixel index alone (16 bits); streamed: (chunk, pixel)
+                                return resident ? (q * chunk_items + i) * 4 : ((q << 16) | (i * 4));
+                            });
                         }
-                        const uint32_t total = __reduce_add_sync(FULL, (uint32_t)__popc(mask));
-                        if (!total) continue;
-                        uint32_t slot = 0u;
-                        if (lane == 0) slot = atomicAdd(&s_nwl, total);
-                        slot = __shfl_sync(FULL, slot, 0);
-                        park(mask, slot, 0, [&](int bit) {
-                            const int code = (int)s_fl[(bit >> 2) * 32 + hw];
-                            return (code >> 5) * chunk_items + (code & 31) + 32 * (t0 + hl);
-                        });
                     }
                 }
             }
-            // Block scan.  Visits: resident -> ONE visit, the whole share as one contiguous tile, 128-item blocks
-            // interleaved over the warps; ring / manual -> one visit per chunk per warp.
+            // Block scan (dense frames whose flagged groups overflow the list, and inputs the TMA cannot take).  Visits:
+            // resident -> ONE visit, the whole share as one contiguous tile, 128-item blocks interleaved over the warps;
+            // streamed / manual -> one visit per chunk per warp, straight from global memory / staged by the warp.
             const int n_vis = scanned ? 0 : (resident ? 1 : n);
             for (int vb = resident ? 0 : warp; vb < n_vis; vb += SNW) {
-                int L = 0, q = 0, nr = row_end - row_begin;
+                int q = 0, nr = row_end - row_begin;
                 const float* tile = slots;
                 if (resident) {
                     for (int c = lane; c < n; c += 32) mbar_wait(&full[c], (uint32_t)it & 1u);  // every copy, seen by this warp
                     __syncwarp();
                 } else {
-                    L = vb < n_res ? n - n_res + vb : n + (vb - n_res);
-                    q = L < n ? L : L - n;
+                    q = vb;
                     const int rr = row_begin + q * R;
                     nr = min(R, row_end - rr);
                     if (use_tma) {
-                        wait_load(L);
-                        tile = slots + (size_t)(L % S) * p.slot_floats;
+                        tile = frame + (size_t)rr * W;  // (streamed share, flagged-group list overflowed: the chunk from L2)
                     } else {
                         float* mt = slots + (size_t)warp * p.slot_floats;
                         manual_fill(mt, rr, nr);
@@ -771,12 +792,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     uint32_t slot = 0u;
                     if (lane == 0) slot = atomicAdd(&s_nwl, total);
                     slot = __shfl_sync(FULL, slot, 0);
-                    park(mask, slot, q, [&](int bit) { return item0 + (bit >> 2) * 32 + lane; });
-                }
-                // this visit was the last use of the slot's contents: start the re-fetch that reuses it, if any
-                if (use_tma && !resident) {
-                    __syncwarp();
-                    if (lane == 0 && L + S < LPF) issue_load(L + S);
+                    park(mask, slot, [&](int bit) { return (q << 16) | ((item0 + (bit >> 2) * 32 + lane) * 4); });
                 }
             }
             PROF(12);
@@ -1093,7 +1109,7 @@ static size_t align_up_sz(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 struct StagePlan {
     int cs, cs_log2, R, S, slot_floats, hist_words, slot_area, dep_off, n_clusters;
-    int off_comp, off_ind, off_msm, off_gath, off_det, off_best, off_par, off_own, GB, wl_entries;
+    int off_comp, off_ind, off_msm, off_gath, off_det, off_best, off_par, off_own, GB, wl_entries, gmax_off, fl_cap;
     bool resident;
     size_t smem;
 };
@@ -1127,21 +1143,40 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
             }
         }
     }
+    {  // a streamed share keeps one group maximum per (chunk, lane) in shared memory, and the flagged-group list packs
+       // the chunk index into 11 bits: bound the number of chunks (bigger chunks: a weaker bound, still a bound)
+        const bool res = use_tma && (share + R - 1) / R <= MAX_SLOTS &&
+                         (size_t)((share + R - 1) / R) * align_up_sz((size_t)R * Wp * 4, 16) + fixed <= SMEM_DYN_CAP;
+        if (use_tma && !res)
+            while ((share + R - 1) / R > 256) ++R;
+    }
     const size_t slot_bytes = align_up_sz((size_t)R * Wp * 4, 16);
     if (fixed + slot_bytes > SMEM_DYN_CAP) return false;
+    if (R * Wp > 65535) return false;  // (work-list codes keep the pixel of a chunk in 16 bits)
     const long long n = (share + R - 1) / R;
     long long S = (long long)((SMEM_DYN_CAP - fixed) / slot_bytes);
     if (S > MAX_SLOTS) S = MAX_SLOTS;
     int wl_entries = WL_CAP;
+    int gmax_off = 0, fl_cap = FL_CAP;
     if (S < n || !use_tma) {
         // the share does not stay resident: its CTA sees more candidates (bigger share) and a ring of a few slots less
-        // streams just as well -> room for a long work list
-        const size_t fixed_long = (size_t)hist_words * 4 + (size_t)WL_CAP_RING * sizeof(uint32_t);
+        // streams just as well -> room for a long work list, and (bulk copies) for the group maxima of every chunk plus a
+        // long flagged-group list: the filter pass then re-reads only the flagged groups, from L2, instead of streaming
+        // the share a second time
+        size_t extra = 0;
+        if (use_tma) {
+            gmax_off = (int)((size_t)hist_words * 4 + (size_t)WL_CAP_RING * sizeof(uint32_t));
+            fl_cap = FL_CAP_STREAM;
+            extra = (size_t)n * 32 * sizeof(float) + (size_t)FL_CAP_STREAM * sizeof(uint16_t);
+        }
+        const size_t fixed_long = (size_t)hist_words * 4 + (size_t)WL_CAP_RING * sizeof(uint32_t) + extra;
         const long long S_long = fixed_long + slot_bytes <= SMEM_DYN_CAP ? (long long)((SMEM_DYN_CAP - fixed_long) / slot_bytes) : 0;
         if (S_long >= (use_tma ? 4 : SNW)) {
             wl_entries = WL_CAP_RING;
             fixed = fixed_long;
             S = S_long < MAX_SLOTS ? S_long : MAX_SLOTS;
+        } else if (use_tma) {
+            return false;  // (rows too wide for four slots beside the lists: another cluster size, or no plan at all)
         }
     }
     if (use_tma) {
@@ -1151,17 +1186,23 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
         if ((size_t)S * slot_bytes + fixed > SMEM_DYN_CAP) return false;
     }
     if (S < 1) return false;
-    // layout of the slot area once the heat-map is done with it (StageParams)
+    // layout of the slot area once the heat-map is done with it (StageParams).  The gather buffers take GB detections at
+    // a time: as many as the CTA owns when they fit, else the tail runs in batches
     const int n_local_max = (K + cs - 1) / cs;
-    const int GB = n_local_max < 256 ? n_local_max : 256;
-    const size_t off_comp = align_up_sz((size_t)K * sizeof(PaintRec), 128);
-    const size_t off_ind = align_up_sz(off_comp + 2 * (size_t)K * 8, 128);
-    const size_t off_msm = align_up_sz(off_ind + 2 * (size_t)K * 4, 128);
-    const size_t off_gath = align_up_sz(off_msm + 2 * sizeof(MergeSmem), 128);
-    const size_t off_det = align_up_sz(off_gath + 2 * (size_t)GB * GATH_STRIDE * 4, 128);
-    const size_t off_best = align_up_sz(off_det + (size_t)n_local_max * sizeof(DetParam), 128);
-    const size_t off_par = align_up_sz(off_best + (size_t)n_local_max * 8, 128);
-    const size_t tail_end = align_up_sz(off_par + sizeof(MergeParams), 128);
+    int GB = n_local_max < 256 ? n_local_max : 256;
+    size_t off_comp, off_ind, off_msm, off_gath, off_det, off_best, off_par, tail_end;
+    for (;;) {
+        off_comp = align_up_sz((size_t)K * sizeof(PaintRec), 128);
+        off_ind = align_up_sz(off_comp + 2 * (size_t)K * 8, 128);
+        off_msm = align_up_sz(off_ind + 2 * (size_t)K * 4, 128);
+        off_gath = align_up_sz(off_msm + 2 * sizeof(MergeSmem), 128);
+        off_det = align_up_sz(off_gath + 2 * (size_t)GB * GATH_STRIDE * 4, 128);
+        off_best = align_up_sz(off_det + (size_t)n_local_max * sizeof(DetParam), 128);
+        off_par = align_up_sz(off_best + (size_t)n_local_max * 8, 128);
+        tail_end = align_up_sz(off_par + sizeof(MergeParams), 128);
+        if (tail_end + fixed <= SMEM_DYN_CAP || GB <= 16) break;
+        GB = (GB + 1) / 2;
+    }
     const size_t off_own = align_up_sz((size_t)K * sizeof(PaintRec), 16);
     size_t area = (size_t)S * slot_bytes;
     if (area < tail_end) area = tail_end;
@@ -1194,6 +1235,8 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
     pl->off_own = (int)off_own;
     pl->GB = GB;
     pl->wl_entries = wl_entries;
+    pl->gmax_off = gmax_off;
+    pl->fl_cap = fl_cap;
     pl->resident = use_tma && S >= n;
     pl->smem = area + fixed;
     return true;
@@ -1345,6 +1388,8 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     p.off_own = best.off_own;
     p.GB = best.GB;
     p.wl_entries = best.wl_entries;
+    p.gmax_off = best.gmax_off;
+    p.fl_cap = best.fl_cap;
     p.ctr = ws.ctr;
     p.cand = ws.cand;
     p.mp.heat = heat;
