@@ -603,6 +603,19 @@ def main() -> int:
     for i in range(3):
         e2e_step(i)
     barrier()
+    # the link's own rate on this host, measured the same minute: the heat-map buffer copied pinned -> device, alone
+    # (every rank at the same time: at N > 1 they share the host's memory and PCIe root)
+    big_k = max(e_keys, key=lambda k: pinned[k].numel())
+    n_bw = 5
+    b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(s_in):
+        dbuf[0][big_k].copy_(pinned[big_k], non_blocking=True)
+        b0.record(s_in)
+        for _ in range(n_bw):
+            dbuf[0][big_k].copy_(pinned[big_k], non_blocking=True)
+        b1.record(s_in)
+    barrier()
+    h2d_link_gbs = n_bw * pinned[big_k].numel() * pinned[big_k].element_size() / (b0.elapsed_time(b1) * 1e-3) / 1e9
     t0 = time.perf_counter()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(s_in)
@@ -627,6 +640,14 @@ def main() -> int:
     # achieved host -> device rate of every rank over its own e2e region (copied bytes only): at N > 1 the ranks share
     # the host's memory and PCIe root, which is what bounds this leg
     h2d_gbs_per_rank = [h2d_copied * e2e_steps / (m * 1e-3) / 1e9 for m in e2e_rank_ms]
+    link = torch.tensor([h2d_link_gbs], dtype=torch.float64, device=dev)
+    link_all = [h2d_link_gbs]
+    if world > 1:
+        ll = [torch.zeros_like(link) for _ in range(world)]
+        dist.all_gather(ll, link)
+        link_all = [float(x.item()) for x in ll]
+    # time the step's host -> device bytes (copies + in-place gathers) would take on the link alone: the floor of this leg
+    e2e_link_floor_ms = h2d / (min(link_all) * 1e9) * 1e3
 
     # -- reporting only: the detections of all ranks gathered over NCCL (shard.gather_detections replaces the reference's
     #    all_gather of the whole head-output dict, model/progressBar.py:85-91); untimed by the bench metric ------------
@@ -703,6 +724,8 @@ def main() -> int:
                     "steps": e2e_steps, "ms_per_step": e2e_ms_max / e2e_steps, "wall_ms_per_step": float(t[1].item()) / e2e_steps,
                     "h2d_copied_bytes_per_step": h2d_copied, "heads_read_in_place": zero_keys,
                     "per_rank_ms_per_step": [m / e2e_steps for m in e2e_rank_ms], "h2d_gbs_per_rank": h2d_gbs_per_rank,
+                    "h2d_link_gbs_per_rank": link_all, "link_floor_ms_per_step": e2e_link_floor_ms,
+                    "frac_of_link_floor": e2e_link_floor_ms / (e2e_ms_max / e2e_steps),
                     "how": "ops.fusion_stage from pinned host buffers; 3-deep pipeline over copy-in / compute / "
                            "copy-out streams; every step copies the fully-read inputs (heat-map, depth plane of pc_dep / radar "
                            "points, calib) H2D and pc_hm + detections D2H; the gather-only heads and the velocity planes "

@@ -25,6 +25,16 @@ KEEP = [
     "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
     "launch__occupancy_limit_shared_mem",
     "launch__waves_per_multiprocessor",
+    "sm__issue_active.avg.pct_of_peak_sustained_elapsed",
+    "sm__icc_request_hit_rate.pct",
+    "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_membar_per_issue_active.ratio",
+    "smsp__average_warps_issue_stalled_branch_resolving_per_issue_active.ratio",
+    "smsp__average_warps_active_per_inst_executed.ratio",
 ]
 
 
