@@ -452,13 +452,14 @@ __device__ __forceinline__ void epilogue_topk(const MergeParams& p, const MergeJ
 
 // epilogues of the DECODE jobs for detections kl0 .. kl0+nb out of their gather buffers (thread group (tid, T)); the
 // caller has waited for the jobs' copies and passed a barrier
+template <bool FUSED>  // FUSED: the fused stage -- job 0 is the frustum job, job 1 the decode job (compile time)
 __device__ __forceinline__ void merge_tail_decode(const MergeParams& p, int n_jobs, int b, int first, int stride, int kl0,
                                                   int nb, const unsigned long long* xs_comp, const float* gath, int GB,
                                                   int tid, int T) {
     const int K = p.K;
-    for (int li = 0; li < n_jobs; ++li) {
+    for (int li = FUSED ? 1 : 0; li < (FUSED ? 2 : n_jobs); ++li) {
         const MergeJob& jb = p.job[li];
-        if (jb.epilogue != EPI_DECODE) continue;
+        if (!FUSED && jb.epilogue != EPI_DECODE) continue;
         const unsigned long long* comps = xs_comp + li * K;
         const float* g = gath + (size_t)li * GB * GATH_STRIDE;
         epilogue_decode(p, jb, b, comps, first, stride, kl0, nb, g, tid, T);
@@ -477,7 +478,7 @@ __device__ __forceinline__ void merge_tail_decode(const MergeParams& p, int n_jo
 // epilogue starts as soon as ITS group has landed.  defer_decode (one batch only): the decode epilogue is left to the
 // caller (merge_tail_decode on a few warps beside the association's ROI scans); the closing barrier here comes after
 // every thread has waited for its decode copies.
-template <int T>
+template <int T, bool FUSED>
 __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int b, int first, int stride, int n_local,
                                            const unsigned long long* xs_comp, const int32_t* xs_ind, float* gath, int GB,
                                            DetParam* sdet, short4* sroi, const float* cal, bool defer_decode) {
@@ -485,37 +486,49 @@ __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int
     const int tid = (int)threadIdx.x;
     for (int kl0 = 0; kl0 < n_local; kl0 += GB) {
         const int nb = min(GB, n_local - kl0);
-#pragma unroll
-        for (int pass = 0; pass < 2; ++pass) {  // group 0: the frustum job, group 1: the others
-            for (int li = 0; li < n_jobs; ++li) {
-                const MergeJob& jb = p.job[li];
-                const bool isf = jb.epilogue == EPI_FRUSTUM;
-                if ((pass == 0) != isf) continue;
-                float* g = gath + (size_t)li * GB * GATH_STRIDE;
-                if (isf)
-                    gather_issue<FS_N>(jb.gt, b, (size_t)HWi, xs_ind + li * K, first, stride, kl0, nb, g, tid, T);
-                else if (jb.epilogue == EPI_DECODE)
-                    gather_issue<DS_N>(jb.gt, b, (size_t)HWi, xs_ind + li * K, first, stride, kl0, nb, g, tid, T);
-            }
+        if (FUSED) {  // group 0: the frustum job (job 0), group 1: the decode job (job 1)
+            gather_issue<FS_N>(p.job[0].gt, b, (size_t)HWi, xs_ind, first, stride, kl0, nb, gath, tid, T);
             cp_async_commit();
+            gather_issue<DS_N>(p.job[1].gt, b, (size_t)HWi, xs_ind + K, first, stride, kl0, nb,
+                               gath + (size_t)GB * GATH_STRIDE, tid, T);
+            cp_async_commit();
+        } else {
+#pragma unroll
+            for (int pass = 0; pass < 2; ++pass) {  // group 0: the frustum job, group 1: the others
+                for (int li = 0; li < n_jobs; ++li) {
+                    const MergeJob& jb = p.job[li];
+                    const bool isf = jb.epilogue == EPI_FRUSTUM;
+                    if ((pass == 0) != isf) continue;
+                    float* g = gath + (size_t)li * GB * GATH_STRIDE;
+                    if (isf)
+                        gather_issue<FS_N>(jb.gt, b, (size_t)HWi, xs_ind + li * K, first, stride, kl0, nb, g, tid, T);
+                    else if (jb.epilogue == EPI_DECODE)
+                        gather_issue<DS_N>(jb.gt, b, (size_t)HWi, xs_ind + li * K, first, stride, kl0, nb, g, tid, T);
+                }
+                cp_async_commit();
+            }
         }
         cp_async_wait<1>();
         __syncthreads();
         CF_MERGE_PROF(3);
-        for (int li = 0; li < n_jobs; ++li) {
-            const MergeJob& jb = p.job[li];
-            const unsigned long long* comps = xs_comp + li * K;
-            if (jb.epilogue == EPI_TOPK)
-                epilogue_topk(p, jb, b, comps, first, stride, kl0, nb, tid, T);
-            else if (jb.epilogue == EPI_FRUSTUM)
-                epilogue_frustum(p, jb, b, comps, xs_ind + li * K, first, stride, kl0, nb, gath + (size_t)li * GB * GATH_STRIDE,
-                                 sdet, sroi, cal, tid, T);
+        if (FUSED) {
+            epilogue_frustum(p, p.job[0], b, xs_comp, xs_ind, first, stride, kl0, nb, gath, sdet, sroi, cal, tid, T);
+        } else {
+            for (int li = 0; li < n_jobs; ++li) {
+                const MergeJob& jb = p.job[li];
+                const unsigned long long* comps = xs_comp + li * K;
+                if (jb.epilogue == EPI_TOPK)
+                    epilogue_topk(p, jb, b, comps, first, stride, kl0, nb, tid, T);
+                else if (jb.epilogue == EPI_FRUSTUM)
+                    epilogue_frustum(p, jb, b, comps, xs_ind + li * K, first, stride, kl0, nb,
+                                     gath + (size_t)li * GB * GATH_STRIDE, sdet, sroi, cal, tid, T);
+            }
         }
         CF_MERGE_PROF(7);
         cp_async_wait<0>();  // (this thread's decode copies: prefetched into L2 long ago, issued a phase ago)
         if (!defer_decode) {
             __syncthreads();
-            merge_tail_decode(p, n_jobs, b, first, stride, kl0, nb, xs_comp, gath, GB, tid, T);
+            merge_tail_decode<FUSED>(p, n_jobs, b, first, stride, kl0, nb, xs_comp, gath, GB, tid, T);
         }
         __syncthreads();
         CF_MERGE_PROF(4);

@@ -297,6 +297,14 @@ __device__ __forceinline__ void tau_scan_cluster(uint32_t hist_saddr, int list_w
     }
 }
 
+// MODE (compile-time: a launch carries only the code of its own plan -- the once-per-frame path is bound by instruction
+// supply): 0 = share resident in shared memory, 1 = share streamed through the slot ring once, 2 = chunks staged by the
+// consuming warp (inputs the TMA cannot take)
+enum { MODE_RESIDENT = 0, MODE_STREAM = 1, MODE_MANUAL = 2 };
+// SPEC: 0 = any job mix (read from the parameters); 1 = the fused stage -- raw list -> frustum job, nms'd list -> decode
+// job, association and paint -- with the depth plane staged in shared memory; 2 = the same, plane scanned from L2
+enum { SPEC_ANY = 0, SPEC_STAGE_STAGED = 1, SPEC_STAGE_L2 = 2 };
+template <int MODE, int SPEC>
 __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_constant__ StageParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ uint64_t full[MAX_SLOTS];
@@ -320,8 +328,12 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     const int C = p.C, H = p.H, W = p.W, Wp = p.Wp, R = p.R, S = p.S, K = p.K;
     const int CH = C * H, W4 = Wp >> 2;
     const size_t HW = (size_t)H * W;
-    const bool want_raw = (p.lists & LIST_RAW) != 0, want_nms = (p.lists & LIST_NMS) != 0;
-    const bool use_tma = p.use_tma != 0;
+    constexpr bool FUSED = SPEC != SPEC_ANY;  // (not `FULL`: that is the full-warp mask of common.cuh)
+    const bool want_raw = FUSED || (p.lists & LIST_RAW) != 0, want_nms = FUSED || (p.lists & LIST_NMS) != 0;
+    const bool do_frustum = FUSED || p.do_frustum != 0;
+    const int n_jobs = FUSED ? 2 : p.n_jobs;
+    const bool dep_staged = SPEC == SPEC_STAGE_STAGED || (SPEC == SPEC_ANY && p.dep_off >= 0);
+    constexpr bool use_tma = MODE != MODE_MANUAL;
 
     float* slots = reinterpret_cast<float*>(smem);
     uint32_t* hist = reinterpret_cast<uint32_t*>(smem + p.slot_area);
@@ -333,8 +345,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     const int row_begin = (int)((long long)CH * rank / cs), row_end = (int)((long long)CH * (rank + 1) / cs);
     const int n = (row_end - row_begin + R - 1) / R;   // chunks
     const int LPF = n;                                 // bulk copies per frame: every chunk once
-    const bool resident = use_tma && n <= S;           // the share stays in shared memory between the two looks
-    const bool stream1 = use_tma && !resident;         // streamed through the slot ring once; the filter pass reads the
+    constexpr bool resident = MODE == MODE_RESIDENT;   // the share stays in shared memory between the two looks (n <= S)
+    constexpr bool stream1 = MODE == MODE_STREAM;      // streamed through the slot ring once; the filter pass reads the
                                                        // flagged groups again from global memory (L2)
     // streamed shares: group maximum per (chunk, lane), then the long flagged-group list
     float* s_gm = reinterpret_cast<float*>(smem + p.slot_area + p.gmax_off);
@@ -436,9 +448,9 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             cl_arrive();
         }
         if (use_tma && tid < (LPF < S ? LPF : S)) issue_load(tid);
-        if (p.do_frustum && tid >= ST - 2)  // (the last warp: it stalls on this DRAM read before its first chunk)
+        if (do_frustum && tid >= ST - 2)  // (the last warp: it stalls on this DRAM read before its first chunk)
             s_cal[tid - (ST - 2)] = __ldg(p.mp.job[0].fh.calib + 12 * (size_t)b + 2 * (tid - (ST - 2)));
-        if (p.do_frustum && tid == 0) {  // the association's radar maps: into L2 while the heat-map streams
+        if (do_frustum && tid == 0) {  // the association's radar maps: into L2 while the heat-map streams
             const size_t total = (p.pc_vel == p.pc_dep ? 3 : 1) * HW * 4, per = ((total + cs - 1) / cs + 15) & ~(size_t)15;
             const size_t off = per * rank;
             if (off < total) {
@@ -860,7 +872,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             // the slot area is free from here on: the merge parameters move in (visible after the cluster barrier)
             if (tid < (int)(sizeof(MergeParams) / 4)) reinterpret_cast<uint32_t*>(smem + p.off_par)[tid] = par_word;
             // Stage the radar depth plane for the association.
-            if (p.do_frustum && p.dep_off >= 0 && tid == 0) {
+            if (do_frustum && dep_staged && tid == 0) {
                 const uint32_t bytes = (uint32_t)(HW * 4);
                 mbar_expect_tx(&dep_bar, bytes);
                 tma_bulk_g2s(smem + p.dep_off, p.pc_dep + (size_t)b * 3 * HW, bytes, &dep_bar);
@@ -882,10 +894,10 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             for (int pass = 0; pass < 2; ++pass) {
                 const int epi = pass ? EPI_DECODE : EPI_FRUSTUM;
                 const int NS = pass ? (int)DS_N : (int)FS_N;
-                for (int li = 0; li < p.n_jobs; ++li) {
+                for (int li = FUSED ? pass : 0; li < (FUSED ? pass + 1 : n_jobs); ++li) {
                     const MergeJob& jb = mpp.job[li];
-                    if (jb.epilogue != epi) continue;
-                    const uint32_t flag = mpp.list[li] ? 0x80000000u : 0x40000000u;
+                    if (!FUSED && jb.epilogue != epi) continue;
+                    const uint32_t flag = (FUSED ? li != 0 : mpp.list[li] != 0) ? 0x80000000u : 0x40000000u;
                     for (int t = tid; t < n_hot * NS; t += ST) {
                         const int e = t / NS, slot = t - e * NS;
                         const uint32_t code = s_hot[e];
@@ -919,7 +931,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         const MergeParams& mp = *reinterpret_cast<const MergeParams*>(smem + p.off_par);
         {
             MergeSmem* msm = reinterpret_cast<MergeSmem*>(smem + p.off_msm);  // one scratch per job
-            const int nj = p.n_jobs;
+            const int nj = n_jobs;
             const uint32_t n0 = cl_ld(mp.list[0] ? ctr_nms : ctr_raw);  // survivors of the jobs' lists
             const uint32_t n1 = nj == 2 ? cl_ld(mp.list[1] ? ctr_nms : ctr_raw) : 0u;
             if (nj == 2 && n0 <= (uint32_t)MERGE_WIN && n1 <= (uint32_t)MERGE_WIN) {
@@ -948,7 +960,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         PROF(7);
         // (no tail reads the peers' shared memory; without the frustum tail there is no later cluster barrier either, and
         // CTA 0, which holds the lists' counters, must not run ahead into its next frame or leave)
-        if (!p.do_frustum) cl_sync();
+        if (!do_frustum) cl_sync();
         PROF(8);
 
         // ---- tail: detection k belongs to CTA k % CS: gathers, frustum geometry / decode outputs ----------------------
@@ -956,12 +968,12 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         DetParam* sdet = reinterpret_cast<DetParam*>(smem + p.off_det);
         // (one batch and a frustum job: the decode epilogue waits until the association's finishing threads leave the upper
         // half of the CTA idle -- its 29 channels per detection have landed long before)
-        const bool defer_decode = p.do_frustum && p.n_jobs == 2 && n_local <= p.GB && n_local <= ST / 2;
-        merge_tail<ST>(mp, p.n_jobs, b, (int)rank, (int)cs, n_local, xs_comp, xs_ind, reinterpret_cast<float*>(smem + p.off_gath),
-                       p.GB, sdet, p.do_frustum ? reinterpret_cast<short4*>(smem + p.off_best) : nullptr,
-                       p.do_frustum ? s_cal : nullptr, defer_decode);
+        const bool defer_decode = do_frustum && n_jobs == 2 && n_local <= p.GB && n_local <= ST / 2;
+        merge_tail<ST, FUSED>(mp, n_jobs, b, (int)rank, (int)cs, n_local, xs_comp, xs_ind, reinterpret_cast<float*>(smem + p.off_gath),
+                       p.GB, sdet, do_frustum ? reinterpret_cast<short4*>(smem + p.off_best) : nullptr,
+                       do_frustum ? s_cal : nullptr, defer_decode);
         PROF(24);
-        if (!p.do_frustum) continue;
+        if (!do_frustum) continue;
 
         // ---- association: one warp per detection, ROI scan of the staged depth plane ---------------------------------
         PaintRec* srecs = reinterpret_cast<PaintRec*>(smem);  // all K records, in detection order, in every CTA
@@ -969,7 +981,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             unsigned long long* sbest = reinterpret_cast<unsigned long long*>(smem + p.off_best);
             const float* dep = p.pc_dep + (size_t)b * 3 * HW;
             const float* dep0 = dep;
-            if (p.dep_off >= 0) {
+            if (dep_staged) {
                 mbar_wait(&dep_bar, (uint32_t)it & 1u);
                 dep0 = reinterpret_cast<const float*>(smem + p.dep_off);
             }
@@ -997,10 +1009,10 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             };
             if (warp >= nsw) {
                 CF_PROF_SLOT(ST - DW * 32, 35, 0);
-                merge_tail_decode(mp, p.n_jobs, b, (int)rank, (int)cs, 0, n_local, xs_comp,
+                merge_tail_decode<FUSED>(mp, n_jobs, b, (int)rank, (int)cs, 0, n_local, xs_comp,
                                   reinterpret_cast<const float*>(smem + p.off_gath), p.GB, tid - (ST - DW * 32), DW * 32);
                 CF_PROF_SLOT(ST - DW * 32, 36, 0);
-            } else if (p.dep_off >= 0) {
+            } else if (dep_staged) {
                 for (int kl = warp;; kl = nsw) {
                     if (kl >= nsw) {  // first detection by warp index, the rest from the shared counter (big ROIs wait less)
                         if (lane == 0) kl = nsw + (int)atomicAdd(&s_nfl, 1u);
@@ -1111,6 +1123,7 @@ struct StagePlan {
     int cs, cs_log2, R, S, slot_floats, hist_words, slot_area, dep_off, n_clusters;
     int off_comp, off_ind, off_msm, off_gath, off_det, off_best, off_par, off_own, GB, wl_entries, gmax_off, fl_cap;
     bool resident;
+    int mode;  // MODE_*
     size_t smem;
 };
 
@@ -1238,6 +1251,7 @@ static bool plan_for_cs(int cs, int C, int H, int W, int K, bool use_tma, bool s
     pl->gmax_off = gmax_off;
     pl->fl_cap = fl_cap;
     pl->resident = use_tma && S >= n;
+    pl->mode = !use_tma ? MODE_MANUAL : (pl->resident ? MODE_RESIDENT : MODE_STREAM);
     pl->smem = area + fixed;
     return true;
 }
@@ -1266,6 +1280,18 @@ void debug_set_plan(int force_cs, int max_clusters) {
 static thread_local cf_plan_info_t g_last_plan = {0, 0, 0, 0, 0, 0, 0, 0};
 void last_plan(cf_plan_info_t* out) { *out = g_last_plan; }
 
+typedef void (*StageKernel)(const StageParams);
+static StageKernel stage_kernel_of(int mode, int spec) {
+    static const StageKernel table[3][3] = {
+        {fusion_stage_kernel<MODE_RESIDENT, SPEC_ANY>, fusion_stage_kernel<MODE_RESIDENT, SPEC_STAGE_STAGED>,
+         fusion_stage_kernel<MODE_RESIDENT, SPEC_STAGE_L2>},
+        {fusion_stage_kernel<MODE_STREAM, SPEC_ANY>, fusion_stage_kernel<MODE_STREAM, SPEC_STAGE_STAGED>,
+         fusion_stage_kernel<MODE_STREAM, SPEC_STAGE_L2>},
+        {fusion_stage_kernel<MODE_MANUAL, SPEC_ANY>, fusion_stage_kernel<MODE_MANUAL, SPEC_STAGE_STAGED>,
+         fusion_stage_kernel<MODE_MANUAL, SPEC_STAGE_L2>}};
+    return table[mode][spec];
+}
+
 // The kernel's function attributes are process-wide state of the CUDA runtime: they are set ONCE per device, to the
 // largest values any plan uses, so that concurrent host threads with different shapes never race on them.
 static cudaError_t device_setup(int dev) {
@@ -1274,10 +1300,12 @@ static cudaError_t device_setup(int dev) {
     std::lock_guard<std::mutex> g(mu);
     auto f = done.find(dev);
     if (f != done.end()) return f->second;
-    cudaError_t e = cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_DYN_CAP);
-    if (e == cudaSuccess) {
+    cudaError_t e = cudaSuccess;
+    for (int m = 0; m < 9 && e == cudaSuccess; ++m) {
+        const StageKernel k = stage_kernel_of(m / 3, m % 3);
+        e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_DYN_CAP);
         // clusters of 16 are an opt-in; a device that refuses just never gets such a plan (occupancy query says 0)
-        if (cudaFuncSetAttribute(fusion_stage_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
+        if (e == cudaSuccess && cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
             cudaGetLastError();
     }
     done[dev] = e;
@@ -1291,7 +1319,7 @@ static int max_clusters(const StagePlan& pl) {
     cudaLaunchAttribute attr[1];
     memset(&cfg, 0, sizeof(cfg));
     launch_cfg(pl, pl.cs, nullptr, &cfg, attr);
-    if (cudaOccupancyMaxActiveClusters(&n, fusion_stage_kernel, &cfg) != cudaSuccess) n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, stage_kernel_of(pl.mode, SPEC_ANY), &cfg) != cudaSuccess) n = 0;
     cudaGetLastError();  // a refused cluster size is not an error of the call
     return n;
 }
@@ -1451,7 +1479,11 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     g_last_plan.chunk_rows = best.R;
     g_last_plan.slots = best.S;
     g_last_plan.smem_bytes = (int)best.smem;
-    e = cudaLaunchKernelEx(&cfg, fusion_stage_kernel, p);
+    // the fused stage (both lists, frustum + decode jobs, association) runs the kernel specialised for it
+    const int spec = (do_frustum && raw_job && nms_job && nms_job->epilogue == EPI_DECODE)
+                         ? (best.dep_off >= 0 ? SPEC_STAGE_STAGED : SPEC_STAGE_L2)
+                         : SPEC_ANY;
+    e = cudaLaunchKernelEx(&cfg, stage_kernel_of(best.mode, spec), p);
     if (e == cudaSuccess) ++*launches;
     return e;
 }
