@@ -46,6 +46,11 @@ class PostOut(C.Structure):
 
 # every symbol include/cfd3d_b200.h declares: name -> (restype, argtypes)
 _I, _F, _D, _Z, _L = C.c_int, C.c_float, C.c_double, C.c_size_t, C.c_int64
+class PostFuse(C.Structure):  # cf_post_fuse_t
+    _fields_ = [("trans_host", C.POINTER(C.c_float)), ("calib", C.c_void_p), ("height", C.c_int), ("width", C.c_int),
+                ("is_gt", C.c_int), ("out", PostOut)]
+
+
 SYMBOLS = {
     "cf_version": (_I, []),
     "cf_last_error": (C.c_char_p, []),
@@ -70,6 +75,11 @@ SYMBOLS = {
                                                                                         C.POINTER(DecodeOut), _vp, _Z, _vp]),
     "cf_fusion_stage_split": (_I, [_vp] * 8 + [_I] * 5 + [_F] + [_vp, _L] + [_vp] * 3 + [C.POINTER(DecodeHeads), _I, _I, _I,
                                                                                       C.POINTER(DecodeOut), _vp, _Z, _vp]),
+    "cf_fusion_decode_post": (_I, [C.POINTER(DecodeHeads), _I, _I, _I, _I, _I, _I, _I, _I, C.POINTER(DecodeOut),
+                                   C.POINTER(PostFuse), _vp, _Z, _vp]),
+    "cf_fusion_stage_post": (_I, [_vp] * 8 + [_I] * 5 + [_F] + [_vp, _L] + [_vp] * 3 + [C.POINTER(DecodeHeads), _I, _I, _I,
+                                                                                     C.POINTER(DecodeOut),
+                                                                                     C.POINTER(PostFuse), _vp, _Z, _vp]),
     "cf_stage_depth_plane": (_I, [_vp, _vp, _I, _I, _I, _vp]),
     "cf_radar_sort": (_I, [_vp, _vp, _I, _I, _vp, _vp, _vp]),
     "cf_frustum_boxes": (_I, [_vp] * 5 + [_I] * 4 + [_F, _vp, _vp, _vp, _Z, _vp]),

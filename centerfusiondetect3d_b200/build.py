@@ -19,7 +19,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcfd3d_b200.so")
 SOURCES = ["api.cu", "peak_ops.cu", "frustum.cu", "stage.cu", "post.cu"]
-HEADERS = ["common.cuh", "select.cuh", "geometry.cuh", "kernels.cuh", "merge.cuh", "assoc.cuh", "paint.cuh", os.path.join("..", "..", "include", "cfd3d_b200.h")]
+HEADERS = ["common.cuh", "select.cuh", "geometry.cuh", "kernels.cuh", "merge.cuh", "assoc.cuh", "paint.cuh", "post.cuh", os.path.join("..", "..", "include", "cfd3d_b200.h")]
 
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",

@@ -225,8 +225,36 @@ int cf_frustum_pc_hm(const float* heat, const float* wh, const float* depth, con
                            inds, nullptr, 0, 0, 0, nullptr, ws, ws_bytes, stream);
 }
 
+// postProcess fused into a decode job (row f1): argument checks + the device-side arguments
+static int set_post_fuse(const cf_post_fuse_t* post, const cf_decode_heads_t* heads, PostFuse* pf) {
+    memset(pf, 0, sizeof(*pf));
+    if (!post) return 0;
+    if (!post->trans_host) return fail(CF_E_NULL, "post: trans_host is NULL");
+    if (post->height < 1 || post->width < 1) return fail(CF_E_SHAPE, "post: bad height / width");
+    const cf_post_out_t& o = post->out;
+    const bool has3d = heads->rot && heads->depth && heads->dim;
+    if (!o.centers) return fail(CF_E_NULL, "post: centers output is NULL");
+    if ((heads->wh && !o.bboxes) || (heads->rot && !o.alpha) ||
+        (has3d && (!o.locations || !o.yaws || !o.bboxes3d || !post->calib)))
+        return fail(CF_E_NULL, "post: a head is present but its post output (or calib) is NULL");
+    pf->enabled = 1;
+    pf->height = post->height;
+    pf->width = post->width;
+    pf->is_gt = post->is_gt;
+    for (int j = 0; j < 6; ++j) pf->t[j] = post->trans_host[j];
+    pf->calib = post->calib;
+    pf->out = o;
+    return 0;
+}
+
 int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W, int K, int out_h, int out_w,
                      int norm2d, const cf_decode_out_t* out, void* ws, size_t ws_bytes, void* stream) {
+    return cf_fusion_decode_post(heads, B, C, H, W, K, out_h, out_w, norm2d, out, nullptr, ws, ws_bytes, stream);
+}
+
+int cf_fusion_decode_post(const cf_decode_heads_t* heads, int B, int C, int H, int W, int K, int out_h, int out_w,
+                          int norm2d, const cf_decode_out_t* out, const cf_post_fuse_t* post, void* ws, size_t ws_bytes,
+                          void* stream) {
     g_launches = 0;
     if (B == 0) return 0;
     if (int rc = check_decode_args(heads, out)) return rc;
@@ -246,6 +274,7 @@ int cf_fusion_decode(const cf_decode_heads_t* heads, int B, int C, int H, int W,
     job.dec.out_h = out_h;
     job.dec.out_w = out_w;
     job.dec.norm2d = norm2d;
+    if (int rc = set_post_fuse(post, heads, &job.dec.post)) return rc;
     if (int rc = run_peak_passes(heads->heatmap, B, C, H, W, K, nullptr, &job, w, st, &n)) return rc;
     g_launches = n;
     return 0;
@@ -276,6 +305,17 @@ int cf_fusion_stage_split(const float* heat, const float* wh, const float* depth
                           int K, float max_pc_dist, float* pc_hm, int64_t pc_hm_batch_stride, int32_t* assoc, float* thr,
                           int64_t* inds, const cf_decode_heads_t* dec_heads, int out_h, int out_w, int norm2d,
                           const cf_decode_out_t* dec_out, void* ws, size_t ws_bytes, void* stream) {
+    return cf_fusion_stage_post(heat, wh, depth, dim, rot, pc_dep, pc_dep_vel, calib, B, C, H, W, K, max_pc_dist, pc_hm,
+                                pc_hm_batch_stride, assoc, thr, inds, dec_heads, out_h, out_w, norm2d, dec_out, nullptr, ws,
+                                ws_bytes, stream);
+}
+
+int cf_fusion_stage_post(const float* heat, const float* wh, const float* depth, const float* dim, const float* rot,
+                         const float* pc_dep, const float* pc_dep_vel, const float* calib, int B, int C, int H, int W,
+                         int K, float max_pc_dist, float* pc_hm, int64_t pc_hm_batch_stride, int32_t* assoc, float* thr,
+                         int64_t* inds, const cf_decode_heads_t* dec_heads, int out_h, int out_w, int norm2d,
+                         const cf_decode_out_t* dec_out, const cf_post_fuse_t* post, void* ws, size_t ws_bytes,
+                         void* stream) {
     if (pc_hm_batch_stride < 3ll * H * W) return fail(CF_E_SHAPE, "cf_fusion_stage: pc_hm batch stride < 3*H*W");
     g_launches = 0;
     if (B == 0) return 0;
@@ -285,6 +325,8 @@ int cf_fusion_stage_split(const float* heat, const float* wh, const float* depth
         if (int rc = check_decode_args(dec_heads, dec_out)) return rc;
         if (dec_heads->heatmap != heat)
             return fail(CF_E_NULL, "cf_fusion_stage: decode heatmap must be the frustum heatmap");
+    } else if (post) {
+        return fail(CF_E_NULL, "cf_fusion_stage_post: post needs the decode heads");
     }
     if (int rc = check_dims(B, C, H, W)) return rc;
     if (int rc = check_k(K, H, W)) return rc;
@@ -307,6 +349,7 @@ int cf_fusion_stage_split(const float* heat, const float* wh, const float* depth
         dj.dec.out_h = out_h;
         dj.dec.out_w = out_w;
         dj.dec.norm2d = norm2d;
+        if (int rc = set_post_fuse(post, dec_heads, &dj.dec.post)) return rc;
     }
     finish_job(&fj);
     if (with_decode) finish_job(&dj);

@@ -53,10 +53,18 @@ struct TopkOut {
     int64_t* ys;
     int64_t* xs;
 };
+// postProcess fused into a decode epilogue (row f1, post.cuh): absent when enabled == 0
+struct PostFuse {
+    int enabled, height, width, is_gt;
+    float t[6];          // inverse output affine (2x3)
+    const float* calib;  // (B,3,4) device
+    cf_post_out_t out;
+};
 struct DecodeArgs {
     cf_decode_heads_t heads;
     cf_decode_out_t out;
     int out_h, out_w, norm2d;
+    PostFuse post;
 };
 
 // head channels a merge job gathers at the K peak pixels: slot s reads base[s][(b*nch[s] + ch[s])*H*W + ind]

@@ -18,6 +18,7 @@
 #include "assoc.cuh"
 #include "geometry.cuh"
 #include "kernels.cuh"
+#include "post.cuh"
 #include "select.cuh"
 
 #ifndef CF_MERGE_PROF
@@ -354,16 +355,77 @@ __device__ __forceinline__ float comp_score(const MergeParams& p, int b, unsigne
     return score;
 }
 
+// the 2-D box of a decoded detection (decode.py:132-150) out of its gathered channels
+__device__ __forceinline__ float4 decode_bbox(const DecodeArgs& da, const float* g, float xn, float yn) {
+    float xs = __fmul_rn(xn, (float)da.out_w), ys = __fmul_rn(yn, (float)da.out_h);
+    if (da.heads.reg) {
+        xs = __fadd_rn(xs, g[DS_REG]);
+        ys = __fadd_rn(ys, g[DS_REG + 1]);
+    } else {
+        xs = __fadd_rn(xs, 0.5f);
+        ys = __fadd_rn(ys, 0.5f);
+    }
+    float w = g[DS_WH], h = g[DS_WH + 1];
+    if (w < 0.0f) w = 0.0f;
+    if (h < 0.0f) h = 0.0f;
+    if (da.norm2d) {
+        w = __fmul_rn(w, (float)da.out_w);
+        h = __fmul_rn(h, (float)da.out_h);
+    }
+    const float hw2 = __fdiv_rn(w, 2.0f), hh2 = __fdiv_rn(h, 2.0f);
+    return make_float4(__fsub_rn(xs, hw2), __fsub_rn(ys, hh2), __fadd_rn(xs, hw2), __fadd_rn(ys, hh2));
+}
+// its amodal offset (decode.py:165 de-normalise)
+__device__ __forceinline__ float2 decode_amodal(const DecodeArgs& da, const float* g) {
+    float ax = g[DS_AMODAL], ay = g[DS_AMODAL + 1];
+    if (da.norm2d) {
+        ax = __fmul_rn(ax, (float)da.out_w);
+        ay = __fmul_rn(ay, (float)da.out_h);
+    }
+    return make_float2(ax, ay);
+}
+
+// postProcess of one decoded detection from its gathered channels (lane 3 of the detection's quad; out of line: the
+// epilogues' common path carries a call, not the code)
+static __device__ __noinline__ void epilogue_post(const DecodeArgs& da, const float* g, float xn, float yn, int b, size_t ok) {
+    const cf_decode_heads_t& hd = da.heads;
+    const cf_decode_out_t& o = da.out;
+    PostDet d;
+    d.has = (hd.wh ? PD_BBOX : 0) | (hd.rot ? PD_ROT : 0) | (hd.depth ? PD_DEPTH : 0) | (hd.dim ? PD_DIM : 0) |
+            (hd.amodal ? PD_AMODAL : 0) | (hd.velocity ? PD_VEL : 0);
+    d.cx = xn;
+    d.cy = yn;
+    const float4 bb = hd.wh ? decode_bbox(da, g, xn, yn) : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    d.bb[0] = bb.x, d.bb[1] = bb.y, d.bb[2] = bb.z, d.bb[3] = bb.w;
+    const float2 am = hd.amodal ? decode_amodal(da, g) : make_float2(0.0f, 0.0f);
+    d.amodal[0] = am.x, d.amodal[1] = am.y;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) d.rot[i] = g[DS_ROT + i];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) d.dim[i] = g[DS_DIM + i];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) d.vel[i] = g[DS_VEL + i];
+    d.depth = g[DS_DEPTH];
+    post_detection(da.post, da.post.calib + 12 * (size_t)b, (long long)ok, d);
+    if (hd.velocity) {  // (the plain copy of this head is skipped: see merge_tail_decode)
+#pragma unroll
+        for (int i = 0; i < 3; ++i) o.velocity[3 * ok + i] = d.vel[i];
+    }
+}
+
 // reference src/lib/model/decode.py:38-41, :80-85, :132-165
 // Four lanes per detection, each with its own part of the outputs (this code runs once per frame on a few threads: its
 // cost is the length of the longest thread's instruction sequence): lane 0 score / class / centre / index, lane 1 the
-// 2-D box, lane 2 amodal offset and depth.
+// 2-D box, lane 2 amodal offset and depth, lane 3 -- when the caller asked for it -- the detection's postProcess
+// (post.cuh; row f1) from the same gathered channels: class id + 1 and the re-oriented velocity land where the
+// reference updates them in place, the rest in the post outputs.
 __device__ __forceinline__ void epilogue_decode(const MergeParams& p, const MergeJob& jb, int b,
                                                 const unsigned long long* comps, int first, int stride, int kl0, int nb,
                                                 const float* gath, int tid, int T) {
     const int K = p.K, HWi = p.H * p.W;
     const cf_decode_heads_t& hd = jb.dec.heads;
     const cf_decode_out_t& o = jb.dec.out;
+    const bool post = jb.dec.post.enabled != 0;
     const int j = tid & 3;
     for (int q = tid >> 2; q < nb; q += T >> 2) {
         const int k = first + (kl0 + q) * stride;
@@ -379,42 +441,21 @@ __device__ __forceinline__ void epilogue_decode(const MergeParams& p, const Merg
             float score = comp_score(p, b, c, cls, ind);
             if (hd.uncertainty) score = __fmul_rn(score, expf(-expf(g[DS_UNC])));
             o.scores[ok] = score;
-            o.class_ids[ok] = (float)cls;
+            o.class_ids[ok] = post ? __fadd_rn((float)cls, 1.0f) : (float)cls;  // (postProcess.py:34)
             o.centers[2 * ok + 0] = xn;
             o.centers[2 * ok + 1] = yn;
             if (o.inds) o.inds[ok] = ind;
         } else if (j == 1) {
-            if (hd.wh) {
-                float xs = __fmul_rn(xn, (float)jb.dec.out_w), ys = __fmul_rn(yn, (float)jb.dec.out_h);
-                if (hd.reg) {
-                    xs = __fadd_rn(xs, g[DS_REG]);
-                    ys = __fadd_rn(ys, g[DS_REG + 1]);
-                } else {
-                    xs = __fadd_rn(xs, 0.5f);
-                    ys = __fadd_rn(ys, 0.5f);
-                }
-                float w = g[DS_WH], h = g[DS_WH + 1];
-                if (w < 0.0f) w = 0.0f;
-                if (h < 0.0f) h = 0.0f;
-                if (jb.dec.norm2d) {
-                    w = __fmul_rn(w, (float)jb.dec.out_w);
-                    h = __fmul_rn(h, (float)jb.dec.out_h);
-                }
-                const float hw2 = __fdiv_rn(w, 2.0f), hh2 = __fdiv_rn(h, 2.0f);
-                *reinterpret_cast<float4*>(o.bboxes + 4 * ok) =
-                    make_float4(__fsub_rn(xs, hw2), __fsub_rn(ys, hh2), __fadd_rn(xs, hw2), __fadd_rn(ys, hh2));
-            }
+            if (hd.wh) *reinterpret_cast<float4*>(o.bboxes + 4 * ok) = decode_bbox(jb.dec, g, xn, yn);
         } else if (j == 2) {
-            if (hd.amodal) {  // :165 de-normalise
-                float ax = g[DS_AMODAL], ay = g[DS_AMODAL + 1];
-                if (jb.dec.norm2d) {
-                    ax = __fmul_rn(ax, (float)jb.dec.out_w);
-                    ay = __fmul_rn(ay, (float)jb.dec.out_h);
-                }
-                o.amodal[2 * ok + 0] = ax;
-                o.amodal[2 * ok + 1] = ay;
+            if (hd.amodal) {
+                const float2 a = decode_amodal(jb.dec, g);
+                o.amodal[2 * ok + 0] = a.x;
+                o.amodal[2 * ok + 1] = a.y;
             }
             if (hd.depth) o.depth[ok] = g[DS_DEPTH];
+        } else if (post) {
+            epilogue_post(jb.dec, g, xn, yn, b, ok);
         }
     }
 }
@@ -466,7 +507,8 @@ __device__ __forceinline__ void merge_tail_decode(const MergeParams& p, int n_jo
         copy_head(jb.dec.heads.rot, jb.dec.out.rot, 8, DS_ROT, b, K, first, stride, kl0, nb, g, tid, T);
         copy_head(jb.dec.heads.dim, jb.dec.out.dim, 3, DS_DIM, b, K, first, stride, kl0, nb, g, tid, T);
         copy_head(jb.dec.heads.nuscenes_att, jb.dec.out.nuscenes_att, 8, DS_ATT, b, K, first, stride, kl0, nb, g, tid, T);
-        copy_head(jb.dec.heads.velocity, jb.dec.out.velocity, 3, DS_VEL, b, K, first, stride, kl0, nb, g, tid, T);
+        if (!jb.dec.post.enabled)  // (with postProcess fused the velocity is written by the detection's post lane)
+            copy_head(jb.dec.heads.velocity, jb.dec.out.velocity, 3, DS_VEL, b, K, first, stride, kl0, nb, g, tid, T);
     }
 }
 

@@ -297,6 +297,21 @@ __device__ __forceinline__ void tau_scan_cluster(uint32_t hist_saddr, int list_w
     }
 }
 
+// The whole CTA ranks the jobs' lists one after the other (single-job calls, and lists that need the exact block-level
+// selection first).  Out of line: on the fused stage's common path this is cold code.
+__device__ __noinline__ void select_sequential(const MergeParams& mp, MergeSmem& msm, int b, int nj, uint32_t n0, uint32_t n1,
+                                               unsigned long long* xs_comp, int32_t* xs_ind, uint32_t HWu) {
+    const int K = mp.K;
+    for (int li = 0; li < nj; ++li) {
+        unsigned long long* dst = xs_comp + li * K;
+        int32_t* dind = xs_ind + li * K;
+        merge_select<ST, true>(mp, msm, b, li, (int)threadIdx.x, 0, li ? n1 : n0, [&](int r, unsigned long long c) {
+            dst[r] = c;
+            dind[r] = (int32_t)(comp_gidx(c) % HWu);
+        });
+    }
+}
+
 // MODE (compile-time: a launch carries only the code of its own plan -- the once-per-frame path is bound by instruction
 // supply): 0 = share resident in shared memory, 1 = share streamed through the slot ring once, 2 = chunks staged by the
 // consuming warp (inputs the TMA cannot take)
@@ -945,15 +960,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                                                 dind[r] = (int32_t)(comp_gidx(c) % HWu);
                                             });
             } else {  // one job, or a list that needs the exact block-level selection first: the whole CTA, job by job
-                for (int li = 0; li < nj; ++li) {
-                    unsigned long long* dst = xs_comp + li * K;
-                    int32_t* dind = xs_ind + li * K;
-                    const uint32_t HWu = (uint32_t)HW;
-                    merge_select<ST, true>(mp, msm[0], b, li, tid, 0, li ? n1 : n0, [&](int r, unsigned long long c) {
-                        dst[r] = c;
-                        dind[r] = (int32_t)(comp_gidx(c) % HWu);
-                    });
-                }
+                select_sequential(mp, msm[0], b, nj, n0, n1, xs_comp, xs_ind, (uint32_t)HW);  // (out of line: cold)
             }
             __syncthreads();
         }

@@ -21,7 +21,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import DecodeHeads, DecodeOut, PostIn, PostOut
+from ._lib import DecodeHeads, DecodeOut, PostFuse, PostIn, PostOut
 
 __all__ = [
     "nms", "topk", "getFeature", "transposeAndGetFeature", "get_alpha", "getDistanceThresh",
@@ -427,8 +427,52 @@ def _decode_structs(output: dict, K: int, keep: list):
     return heads, out, ret, (B, Cc, H, W), heat
 
 
-def fusionDecode(outputs, outputSize=(112, 200), K=100, norm2d=False) -> dict:
-    """decode.py:10-174 -- drop-in.  Single pyramid layer (all the reference's networks emit one, dla.py:579)."""
+def _post_fuse(ret: dict, post: dict, keep: list):
+    """cf_post_fuse_t for a decode whose result dict is `ret`: `post` = postProcess's remaining arguments
+    {center, scale, height, width, calibs[, isGt]} (postProcess.py:13).  Returns (struct, finish) -- finish(ret) turns
+    the decode's dict into what postProcess returns (centers / bboxes replaced, rotation -> alpha, new 3-D keys)."""
+    B, K = ret["scores"].shape
+    dev = ret["scores"].device
+    height, width = int(post["height"]), int(post["width"])
+    trans = inverse_output_affine(post["center"], post["scale"], width, height)
+    has3d = all(k in ret for k in ("rotation", "depth", "dimension"))
+    cal = None
+    if has3d:
+        cal = _map(post["calibs"], "calibs", ndim=None).reshape(-1, 3, 4)
+        if cal.shape[0] != B:
+            cal = cal.expand(B, 3, 4).contiguous()
+    new = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)  # noqa: E731
+    o_cen = new(B, K, 2)
+    o_bb = new(B, K, 4) if "bboxes" in ret else None
+    o_alpha = new(B, K) if "rotation" in ret else None
+    o_loc, o_yaw, o_b3 = (new(B, K, 3), new(B, K), new(B, K, 8, 3)) if has3d else (None, None, None)
+    tarr = (C.c_float * 6)(*[float(v) for v in trans.reshape(-1)])
+    pf = PostFuse(C.cast(tarr, C.POINTER(C.c_float)), _ptr(cal), height, width, int(bool(post.get("isGt", False))),
+                  PostOut(_ptr(o_cen), _ptr(o_bb), _ptr(o_alpha), _ptr(o_loc), _ptr(o_yaw), _ptr(o_b3)))
+    keep.extend([tarr, cal])
+
+    def finish(r: dict) -> dict:
+        r["centers"] = o_cen
+        if o_bb is not None:
+            r["bboxes"] = o_bb
+        if "depth" in r:
+            r["depth"] = r["depth"].reshape(B, K)
+        if o_alpha is not None:
+            r.pop("rotation")
+            r["alpha"] = o_alpha
+        if has3d:
+            r["locations"], r["yaws"], r["bboxes3d"] = o_loc, o_yaw, o_b3
+        return r
+
+    return pf, finish
+
+
+def fusionDecode(outputs, outputSize=(112, 200), K=100, norm2d=False, post: dict | None = None) -> dict:
+    """decode.py:10-174 -- drop-in.  Single pyramid layer (all the reference's networks emit one, dla.py:579).
+
+    post = {center, scale, height, width, calibs[, isGt]}: postProcess (postProcess.py:13-85) runs inside the decode's
+    own launch (row f1, cf_fusion_decode_post) and the returned dict is what `postProcess(fusionDecode(...), **post)`
+    returns -- bit for bit, one launch fewer."""
     assert isinstance(outputs, list), "output must be a list of dictionaries"
     layers = [o for o in outputs if "heatmap" in o]
     if not layers:
@@ -441,9 +485,11 @@ def fusionDecode(outputs, outputSize=(112, 200), K=100, norm2d=False) -> dict:
     heads, out, ret, (B, Cc, H, W), heat = _decode_structs(layers[0], K, keep)
     _same_device(*keep)
     ws, wsn = _stage_ws(heat.device, B, Cc, H, W, K)
-    _call(heat.device, "cf_fusion_decode", C.byref(heads), B, Cc, H, W, K, int(outputSize[0]), int(outputSize[1]),
-                                           int(bool(norm2d)), C.byref(out), ws.data_ptr(), wsn, _stream(heat))
-    return ret
+    pf, finish = _post_fuse(ret, post, keep) if post is not None else (None, None)
+    _call(heat.device, "cf_fusion_decode_post", C.byref(heads), B, Cc, H, W, K, int(outputSize[0]), int(outputSize[1]),
+                                                int(bool(norm2d)), C.byref(out), C.byref(pf) if pf else None,
+                                                ws.data_ptr(), wsn, _stream(heat))
+    return finish(ret) if finish else ret
 
 
 def stage_depth_plane(pc_dep_dev: torch.Tensor, pc_dep_host: torch.Tensor) -> None:
@@ -459,8 +505,11 @@ def stage_depth_plane(pc_dep_dev: torch.Tensor, pc_dep_host: torch.Tensor) -> No
 
 def fusion_stage(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config, outputSize=None, norm2d=False,
                  decode_output: dict | None = None, sec_feats: torch.Tensor | None = None,
-                 pc_vel: torch.Tensor | None = None):
+                 pc_vel: torch.Tensor | None = None, post: dict | None = None):
     """getPcFrustumHeatmap + fusionDecode with ONE pass over the heat-map (cf_fusion_stage).
+
+    post = {center, scale, height, width, calibs[, isGt]}: postProcess runs in the decode epilogue of the same launch
+    (row f1); `ret` is then what postProcess returns (see fusionDecode).
 
     `output` holds the first-stage heads (heatmap, widthHeight, depth, dimension, rotation); `decode_output` the dict
     fusionDecode would receive (defaults to `output`, which then typically also carries reg, depth2, rotation2, ...).
@@ -520,12 +569,14 @@ def fusion_stage(output: dict, pc_dep: torch.Tensor, calib: torch.Tensor, config
         pc_hm = sec_feats[:, sec_feats.shape[1] - 3:]
         stride = sec_feats.shape[1] * H * W
     ws, wsn = _stage_ws(heat.device, B, Cc, H, W, K)
-    _call(heat.device, "cf_fusion_stage_split", heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
-                                                rot.data_ptr(), pcd.data_ptr(), _ptr(pcd_vel), cal.data_ptr(), B, Cc, H, W,
-                                                K, max_pc_dist, pc_hm.data_ptr(), stride, None, None, None,
-                                                C.byref(heads), int(outputSize[0]), int(outputSize[1]),
-                                                int(bool(norm2d)), C.byref(out), ws.data_ptr(), wsn, _stream(heat))
-    return pc_hm, ret
+    pf, finish = _post_fuse(ret, post, keep) if post is not None else (None, None)
+    _call(heat.device, "cf_fusion_stage_post", heat.data_ptr(), wh.data_ptr(), dep.data_ptr(), dim.data_ptr(),
+                                               rot.data_ptr(), pcd.data_ptr(), _ptr(pcd_vel), cal.data_ptr(), B, Cc, H, W,
+                                               K, max_pc_dist, pc_hm.data_ptr(), stride, None, None, None,
+                                               C.byref(heads), int(outputSize[0]), int(outputSize[1]),
+                                               int(bool(norm2d)), C.byref(out), C.byref(pf) if pf else None,
+                                               ws.data_ptr(), wsn, _stream(heat))
+    return pc_hm, (finish(ret) if finish else ret)
 
 
 # ------------------------------------------------------------------------------------------------------

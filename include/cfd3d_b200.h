@@ -230,6 +230,33 @@ typedef struct {
 CF_API int cf_post_process(const cf_post_in_t* in, int B, int K, int out_h, int out_w, const float* trans_host,
                            const float* calib, int is_gt, const cf_post_out_t* out, void* stream);
 
+/* ---- f1 fused: fusionDecode + postProcess in the decode's own launch --------------------------------------------
+ * The decode callers run postProcess right after fusionDecode (src/lib/detector.py:414-424 + :341,
+ * src/lib/model/progressBar.py:96-104, :190-196).  With `post` the fourth lane of every detection's lane quad in the
+ * decode epilogue computes the detection's postProcess from the channels the decode has gathered anyway: no second
+ * launch, no second pass over the (B,K) records.  dec_out then holds what the reference's dict holds AFTER
+ * postProcess for the keys it updates in place (class_ids + 1, velocity re-oriented) and the plain decode values for
+ * the rest (centers normalised, bboxes in output pixels, rot); post->out receives the replaced / new keys.  Results
+ * equal cf_fusion_decode followed by cf_post_process bit for bit (same arithmetic body).  post == NULL: plain decode.
+ * height / width: postProcess's arguments (the network output size). */
+typedef struct {
+    const float* trans_host; /* 2x3 fp32 inverse output affine, HOST (see cf_post_process) */
+    const float* calib;      /* (B,3,4) device; required when rot, depth and dim heads exist */
+    int height, width, is_gt;
+    cf_post_out_t out;
+} cf_post_fuse_t;
+
+CF_API int cf_fusion_decode_post(const cf_decode_heads_t* heads, int B, int C, int H, int W, int K, int out_h, int out_w,
+                                 int norm2d, const cf_decode_out_t* out, const cf_post_fuse_t* post, void* ws,
+                                 size_t ws_bytes, void* stream);
+/* cf_fusion_stage_split (declared above) with the same option */
+CF_API int cf_fusion_stage_post(const float* heat, const float* wh, const float* depth, const float* dim,
+                                const float* rot, const float* pc_dep, const float* pc_dep_vel, const float* calib, int B,
+                                int C, int H, int W, int K, float max_pc_dist, float* pc_hm, int64_t pc_hm_batch_stride,
+                                int32_t* assoc, float* thr, int64_t* inds, const cf_decode_heads_t* dec_heads, int out_h,
+                                int out_w, int norm2d, const cf_decode_out_t* dec_out, const cf_post_fuse_t* post,
+                                void* ws, size_t ws_bytes, void* stream);
+
 /* ---- a5 + a6  radar pillar expansion -> pc_dep -----------------------------------------------------------
  * loadRadarPointCloud filters      src/lib/dataset/datasets/nuscenes.py:172-205
  * map_pointcloud_to_image          src/lib/utils/pointcloud.py:17-49

@@ -171,6 +171,13 @@ def test_golden_cfg1_whole_model(ops):
     eq(npy(pc_hm2), g["out_pc_hm"], "fused pc_hm")
     for k in ref_keys:
         eq(npy(ret2[k]), g["out_dec_" + k], "fused decode " + k)
+    # ... and with postProcess folded into the same launch (row f1)
+    _, out3 = ops.fusion_stage(dict(y), pc_dep, calib, cfg,
+                               post=dict(center=g["in_center"], scale=float(g["in_scale"]), height=H, width=W, calibs=calib))
+    assert ops.last_launch_count() == 1 and sorted(out3) == post_keys
+    for k in post_keys:
+        np.testing.assert_allclose(npy(out3[k]), g["out_post_" + k], rtol=1e-5, atol=1e-5, err_msg="fused post " + k)
+        eq(npy(out3[k]), npy(out[k]), "fused post == postProcess launch, " + k)
 
 
 def test_get_feature_bnc_form(ops):
@@ -444,6 +451,47 @@ def test_post_process(ops, oracle):
     assert float(out["yaws"].abs().max()) <= np.pi + 1e-6
     dead = (out["dimension"] <= 0).any(dim=2)
     assert not bool(out["bboxes3d"][dead].any())
+
+
+def _same_dict(a: dict, b: dict, what: str):
+    assert sorted(a) == sorted(b), (what, sorted(a), sorted(b))
+    for k in a:
+        eq(npy(a[k]), npy(b[k]), "%s %s" % (what, k))
+
+
+@pytest.mark.parametrize("cfg_name,B,heads_dropped", [("cfg2", 5, ()), ("cfg2", 3, ("amodal_offset",)),
+                                                     ("cfg2", 2, ("amodal_offset", "widthHeight", "reg")),
+                                                     ("cfg2", 2, ("depth2", "depth")), ("cfg5", 2, ())])
+def test_post_process_fused_into_decode(ops, cfg_name, B, heads_dropped):
+    """Row f1, fused: fusionDecode(post=...) and fusion_stage(post=...) run postProcess in the decode epilogue of their
+    one launch; the result is bit for bit what fusionDecode -> postProcess (two launches) returns, for every mix of
+    heads postProcess branches on (postProcess.py:39-64: amodal centre / box centre / plain centre, 3-D keys or not)."""
+    wl = syn.WORKLOADS[cfg_name]
+    inp = make_case(wl, B)
+    cfg = Cfg(wl.K, wl.max_pc_dist)
+    post = dict(center=(800.0, 450.0), scale=1600.0, height=wl.H, width=wl.W, calibs=cu(inp["calib"]))
+    dec_keys = [k for k in DEC_KEYS if k not in heads_dropped]
+    # two launches
+    ret = ops.fusionDecode([to_cuda(inp, dec_keys, DEV)], (wl.H, wl.W), wl.K)
+    n_dec = ops.last_launch_count()
+    want = ops.postProcess(ret, post["center"], post["scale"], wl.H, wl.W, post["calibs"])
+    # one launch: decode alone ...
+    got = ops.fusionDecode([to_cuda(inp, dec_keys, DEV)], (wl.H, wl.W), wl.K, post=post)
+    assert ops.last_launch_count() == n_dec
+    _same_dict(got, want, "decode+post")
+    # ... and the whole stage (frustum heads always complete; the decode dict is the varied one)
+    fwd = to_cuda(inp, FWD_KEYS, DEV)
+    pc_dep, calib = cu(inp["pc_dep"]), cu(inp["calib"])
+    pc_hm0, _ = ops.fusion_stage(dict(fwd), pc_dep, calib, cfg, decode_output=to_cuda(inp, dec_keys, DEV))
+    pc_hm, got2 = ops.fusion_stage(dict(fwd), pc_dep, calib, cfg, decode_output=to_cuda(inp, dec_keys, DEV), post=post)
+    assert ops.last_launch_count() == 1
+    eq(npy(pc_hm), npy(pc_hm0), "pc_hm unchanged by the fused post")
+    _same_dict(got2, want, "stage+post")
+    # ground-truth flavour (isGt: centres stay the plain ones, velocity untouched; postProcess.py:54,71)
+    want_gt = ops.postProcess(ops.fusionDecode([to_cuda(inp, dec_keys, DEV)], (wl.H, wl.W), wl.K), post["center"],
+                              post["scale"], wl.H, wl.W, post["calibs"], isGt=True)
+    got_gt = ops.fusionDecode([to_cuda(inp, dec_keys, DEV)], (wl.H, wl.W), wl.K, post=dict(post, isGt=True))
+    _same_dict(got_gt, want_gt, "decode+post isGt")
 
 
 def test_oracle_dense_radar_with_pillars(ops, oracle):
