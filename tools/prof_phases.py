@@ -20,6 +20,8 @@ B = int(sys.argv[2]) if len(sys.argv) > 2 else min(wl.B, 32)
 CS = int(sys.argv[3]) if len(sys.argv) > 3 else 4
 dev = "cuda:0"
 keys = bench.STAGE_KEYS + ("calib", "pc_dep")
+if wl.with_pillars:
+    keys += ("radar_points", "radar_counts", "cam", "calib64", "A_out")
 # like bench.py: back-to-back launches over rotating input sets (> 2 x L2 together), no other kernel in between --
 # the SM's instruction cache keeps the kernel from launch to launch, the data is cold.  COLD=1: one input set and
 # an L2-evicting read between the launches instead (that also evicts the code: every once-per-frame phase gets slower).
@@ -46,7 +48,9 @@ for rep in range(6):
     bench.run_stage(ops, wl, d, cfg)
     e1.record()
     torch.cuda.synchronize()
-    n_cta = min(B, 148 // CS) * CS
+    plan = ops.last_plan()
+    CS = plan["cluster_size"]
+    n_cta = plan["n_clusters"] * CS
     buf = np.zeros((n_cta, 48), dtype=np.int64)
     L.cf_debug_read_prof(buf.ctypes.data, n_cta)
     dt = np.diff(buf[:, order], axis=1) / 1.965e3  # us at 1965 MHz
