@@ -380,7 +380,21 @@ int cf_radar_sort(const double* points, const int32_t* counts, int B, int Nmax, 
     if (B < 0 || Nmax < 0 || Nmax > 25600) return fail(CF_E_SHAPE, "cf_radar_sort: bad shape (Nmax <= 25600)");
     if (points == sorted) return fail(CF_E_NULL, "cf_radar_sort: sorted must not alias points");
     int n = 0;
-    CF_CUDA(launch_radar_sort(points, counts, B, Nmax, sorted, order, (cudaStream_t)stream, &n), "radar_sort");
+    CF_CUDA(launch_radar_sort(points, counts, B, 0, Nmax, nullptr, 0, sorted, order, (cudaStream_t)stream, &n), "radar_sort");
+    g_launches = n;
+    return 0;
+}
+
+int cf_radar_ingest(const double* raw, const int32_t* counts, int B, int rows, int Nmax, const int32_t* flip,
+                    int descending, double* sorted, int32_t* order, void* stream) {
+    g_launches = 0;
+    if (!counts || !sorted || (Nmax > 0 && !raw)) return fail(CF_E_NULL, "cf_radar_ingest: NULL pointer");
+    if (B < 0 || Nmax < 0 || Nmax > 25600) return fail(CF_E_SHAPE, "cf_radar_ingest: bad shape (Nmax <= 25600)");
+    if (rows != 0 && rows < 10) return fail(CF_E_SHAPE, "cf_radar_ingest: rows must be 0 (packed [X,Y,Z,vx,vz]) or >= 10");
+    if (raw == sorted) return fail(CF_E_NULL, "cf_radar_ingest: sorted must not alias raw");
+    int n = 0;
+    CF_CUDA(launch_radar_sort(raw, counts, B, rows, Nmax, flip, descending ? 1 : 0, sorted, order, (cudaStream_t)stream, &n),
+            "radar_ingest");
     g_launches = n;
     return 0;
 }
@@ -463,6 +477,14 @@ int cf_radar_pillars(const double* points, const int32_t* counts, int B, int Nma
                      const double* calib, const double* A, int img_w, int img_h, int H, int W,
                      const double* pillar_dims_host, double max_dist, double z_offset, float* pc_dep, int32_t* owner,
                      void* ws, size_t ws_bytes, void* stream) {
+    return cf_radar_pillars_flip(points, counts, nullptr, B, Nmax, cam, calib, A, img_w, img_h, H, W, pillar_dims_host,
+                                 max_dist, z_offset, pc_dep, owner, ws, ws_bytes, stream);
+}
+
+int cf_radar_pillars_flip(const double* points, const int32_t* counts, const int32_t* flip, int B, int Nmax,
+                          const double* cam, const double* calib, const double* A, int img_w, int img_h, int H, int W,
+                          const double* pillar_dims_host, double max_dist, double z_offset, float* pc_dep,
+                          int32_t* owner, void* ws, size_t ws_bytes, void* stream) {
     g_launches = 0;
     if (!counts || !cam || !calib || !A || !pillar_dims_host || !pc_dep || (Nmax > 0 && !points))
         return fail(CF_E_NULL, "cf_radar_pillars: NULL pointer");
@@ -475,7 +497,7 @@ int cf_radar_pillars(const double* points, const int32_t* counts, int B, int Nma
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
-    CF_KERNEL(CF_KERNEL_PILLAR_RECTS, st, launch_pillar_rects(points, counts, B, Nmax, cam, calib, A, img_w, img_h, H, W, pillar_dims_host[0],
+    CF_KERNEL(CF_KERNEL_PILLAR_RECTS, st, launch_pillar_rects(points, counts, flip, B, Nmax, cam, calib, A, img_w, img_h, H, W, pillar_dims_host[0],
                                 pillar_dims_host[1], pillar_dims_host[2], max_dist, z_offset, (PaintRec*)ws, st, &n), "pillar_rects");
     CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint((const PaintRec*)ws, Nmax, Nmax, nullptr, B, H, W, pc_dep, owner, st, &n), "paint");
     g_launches = n;

@@ -396,22 +396,35 @@ cudaError_t launch_dist_thresh(const float* calib, const float* center, const fl
 }
 
 // -----------------------------------------------------------------------------------------------------
-// f2: stable depth sort of a frame's radar points on the device (ascending Z, ties by source index).
-// The reference sorts on the host with np.argsort (dataset/datasets/nuscenes.py:195-197, detector.py:281), whose
-// default kind is not stable; the pillar paint is last-writer-wins, so the order is part of the result.  Here the
-// order is fixed: (Z, source index) ascending == np.argsort(kind="stable").  One CTA per frame, rank by counting
-// with the depths in shared memory (N <= a few thousand points).
+// f2: radar ingestion on the device -- the host-side steps of loadRadarPointCloud between the pickle and
+// processPointCloud (dataset/datasets/nuscenes.py:159-205; detector.py:255-283):
+//   * layout: the (rows >= 10, N) float64 array convert_nuScenes.py stores (rows 0-2 x, y, z in the camera frame,
+//     rows 8, 9 the compensated velocities vx, vz) -> [X, Y, Z, vx, vz] rows (rows == 0: the input already has them);
+//   * stable depth sort.  The reference sorts with np.argsort (nuscenes.py:195-197, detector.py:281), whose default
+//     kind is not stable; the pillar paint is last-writer-wins, so the order is part of the result.  Here it is fixed:
+//     (Z, source index) ascending == np.argsort(kind="stable"); `descending` = that order reversed, index[::-1] of
+//     nuscenes.py:196-197 (PC_REVERSE false);
+//   * flip augmentation (nuscenes.py:201-205): X and vx change sign (the projected u is mirrored by the pillar kernel,
+//     which gets the same flags).
+// The distance filter, the z offset and the in-image masks stay in pillar_rects_kernel: they drop points without
+// changing the order of the rest.  One CTA per frame, rank by counting with the depths in shared memory.
 // -----------------------------------------------------------------------------------------------------
 constexpr int RS_T = 1024;
 
 __global__ void __launch_bounds__(RS_T) radar_sort_kernel(const double* __restrict__ points, const int32_t* __restrict__ counts,
-                                                          int Nmax, double* __restrict__ out, int32_t* __restrict__ order) {
+                                                          int rows, int Nmax, const int32_t* __restrict__ flip,
+                                                          int descending, double* __restrict__ out,
+                                                          int32_t* __restrict__ order) {
     extern __shared__ double sz[];
     const int b = blockIdx.x, tid = threadIdx.x;
     const int n = min(Nmax, max(0, counts[b]));
-    const double* fp = points + (size_t)b * Nmax * 5;
+    const bool raw = rows > 0;
+    const double* fp = points + (size_t)b * Nmax * (raw ? rows : 5);
+    // element c in {X, Y, Z, vx, vz} of point i
+    auto at = [&](int i, int c) { return raw ? fp[(size_t)(c < 3 ? c : c + 5) * Nmax + i] : fp[(size_t)i * 5 + c]; };
     double* fo = out + (size_t)b * Nmax * 5;
-    for (int i = tid; i < n; i += RS_T) sz[i] = fp[(size_t)i * 5 + 2];
+    const double sgn = (flip && flip[b]) ? -1.0 : 1.0;
+    for (int i = tid; i < n; i += RS_T) sz[i] = at(i, 2);
     __syncthreads();
     for (int i = tid; i < Nmax; i += RS_T) {
         int rank = i;  // padding rows keep their place
@@ -426,15 +439,20 @@ __global__ void __launch_bounds__(RS_T) radar_sort_kernel(const double* __restri
             }
             if (j < n) r0 += (sz[j] < zi || (sz[j] == zi && j < i)) ? 1 : 0;
             rank = r0 + r1;
+            if (descending) rank = n - 1 - rank;
         }
-#pragma unroll
-        for (int c = 0; c < 5; ++c) fo[(size_t)rank * 5 + c] = fp[(size_t)i * 5 + c];
+        double* q = fo + (size_t)rank * 5;
+        q[0] = i < n ? sgn * at(i, 0) : at(i, 0);
+        q[1] = at(i, 1);
+        q[2] = at(i, 2);
+        q[3] = i < n ? sgn * at(i, 3) : at(i, 3);
+        q[4] = at(i, 4);
         if (order) order[(size_t)b * Nmax + rank] = i;
     }
 }
 
-cudaError_t launch_radar_sort(const double* points, const int32_t* counts, int B, int Nmax, double* out, int32_t* order,
-                              cudaStream_t st, int* launches) {
+cudaError_t launch_radar_sort(const double* points, const int32_t* counts, int B, int rows, int Nmax, const int32_t* flip,
+                              int descending, double* out, int32_t* order, cudaStream_t st, int* launches) {
     if (B == 0 || Nmax == 0) return cudaSuccess;
     const size_t smem = (size_t)Nmax * sizeof(double);
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
@@ -442,7 +460,7 @@ cudaError_t launch_radar_sort(const double* points, const int32_t* counts, int B
         cudaError_t e = cudaFuncSetAttribute(radar_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    radar_sort_kernel<<<B, RS_T, smem, st>>>(points, counts, Nmax, out, order);
+    radar_sort_kernel<<<B, RS_T, smem, st>>>(points, counts, rows, Nmax, flip, descending, out, order);
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) ++*launches;
     return e;
@@ -459,6 +477,7 @@ cudaError_t launch_radar_sort(const double* points, const int32_t* counts, int B
 struct PillarParams {
     const double *points, *cam, *calib, *A;
     const int32_t* counts;
+    const int32_t* flip;  // (B) or NULL: the frame's image is flipped (nuscenes.py:201-205); X, vx arrive negated
     int B, Nmax, img_w, img_h, H, W;
     double ox, oy, oz, max_dist, z_offset;
     PaintRec* recs;
@@ -492,11 +511,17 @@ __global__ void __launch_bounds__(128) pillar_rects_kernel(const PillarParams p)
     const int W = p.W, H = p.H;
     bool ok = !(p.max_dist > 0 && !(Z <= p.max_dist));
     Y = __dsub_rn(Y, p.z_offset);
-    const double uh = dot3(Kc[0], X, Kc[1], Y, Kc[2], Z);
-    const double vh = dot3(Kc[3], X, Kc[4], Y, Kc[5], Z);
-    const double zh = dot3(Kc[6], X, Kc[7], Y, Kc[8], Z);
-    const double u = uh / zh, v = vh / zh;
+    // a flipped frame was projected and masked BEFORE the flip (nuscenes.py:187-191, then :201-203): with the point as
+    // loaded (X back to its sign), and the pixel column mirrored afterwards; the pillar below stands at the flipped X
+    const bool flipped = p.flip && p.flip[b];
+    const double Xp = flipped ? -X : X;
+    const double uh = dot3(Kc[0], Xp, Kc[1], Y, Kc[2], Z);
+    const double vh = dot3(Kc[3], Xp, Kc[4], Y, Kc[5], Z);
+    const double zh = dot3(Kc[6], Xp, Kc[7], Y, Kc[8], Z);
+    double u = uh / zh;
+    const double v = vh / zh;
     ok = ok && (Z > 0 && u > 1 && u < p.img_w - 1 && v > 1 && v < p.img_h - 1);
+    if (flipped) u = __dsub_rn((double)(p.img_w - 1), u);
     const double up = __dadd_rn(__dadd_rn(__dmul_rn(Ab[0], u), __dmul_rn(Ab[1], v)), Ab[2]);
     const double vp = __dadd_rn(__dadd_rn(__dmul_rn(Ab[3], u), __dmul_rn(Ab[4], v)), Ab[5]);
     ok = ok && (up < W && vp < H && 0 < up && 0 < vp);
@@ -542,7 +567,7 @@ __global__ void __launch_bounds__(128) pillar_rects_kernel(const PillarParams p)
     *dst = r;
 }
 
-cudaError_t launch_pillar_rects(const double* points, const int32_t* counts, int B, int Nmax, const double* cam,
+cudaError_t launch_pillar_rects(const double* points, const int32_t* counts, const int32_t* flip, int B, int Nmax, const double* cam,
                                 const double* calib, const double* A, int img_w, int img_h, int H, int W, double ph,
                                 double pw, double pl, double max_dist, double z_offset, PaintRec* recs,
                                 cudaStream_t st, int* launches) {
@@ -552,6 +577,7 @@ cudaError_t launch_pillar_rects(const double* points, const int32_t* counts, int
     p.calib = calib;
     p.A = A;
     p.counts = counts;
+    p.flip = flip;
     p.B = B;
     p.Nmax = Nmax;
     p.img_w = img_w;

@@ -121,8 +121,8 @@ cudaError_t launch_box_assoc(const float* pc_dep, const float* bboxes, const flo
 cudaError_t launch_box_assoc_np(const float* pc_dep, const double* bboxes, const double* depth, const double* thr,
                                 const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, int flags,
                                 PaintRec* recs, int32_t* assoc, cudaStream_t st, int* launches);
-cudaError_t launch_radar_sort(const double* points, const int32_t* counts, int B, int Nmax, double* out, int32_t* order,
-                              cudaStream_t st, int* launches);
+cudaError_t launch_radar_sort(const double* points, const int32_t* counts, int B, int rows, int Nmax, const int32_t* flip,
+                              int descending, double* out, int32_t* order, cudaStream_t st, int* launches);
 int debug_read_prof(long long* out, int n_cta);  // -DCFD3D_PROFILE builds only
 void debug_set_plan(int force_cs, int max_clusters);
 void last_plan(cf_plan_info_t* out);
@@ -137,7 +137,7 @@ cudaError_t launch_dist_thresh(const float* calib, const float* center, const fl
 cudaError_t launch_pc2hm_single(float* pc_hm, const float* pc_dep, int H, int W, const float* depth,
                                 const float* bbox, const float* thr, float max_pc_dist, int32_t* assoc,
                                 cudaStream_t st, int* launches);
-cudaError_t launch_pillar_rects(const double* points, const int32_t* counts, int B, int Nmax, const double* cam,
+cudaError_t launch_pillar_rects(const double* points, const int32_t* counts, const int32_t* flip, int B, int Nmax, const double* cam,
                                 const double* calib, const double* A, int img_w, int img_h, int H, int W, double ph,
                                 double pw, double pl, double max_dist, double z_offset, PaintRec* recs,
                                 cudaStream_t st, int* launches);

@@ -662,12 +662,44 @@ def radar_sort(points: torch.Tensor, counts: torch.Tensor, return_order: bool = 
     return (out, order) if return_order else out
 
 
+def radar_ingest(raw: torch.Tensor, counts: torch.Tensor, flip=None, descending: bool = False,
+                 return_order: bool = False, packed: bool = False):
+    """Row f2, complete -- the host-side steps of loadRadarPointCloud between the pickle and processPointCloud
+    (nuscenes.py:159-205; detector.py:255-283) on the device (cf_radar_ingest).
+
+    raw (B, rows >= 10, Nmax) f64: per frame the stored radar array (rows 0-2 x, y, z; rows 8, 9 vx, vz), padded to Nmax
+    columns -- or, with packed=True, (B, Nmax, 5) [X,Y,Z,vx,vz] rows; counts (B,) i32.  flip (B,) bool / i32 or None: the frame's image
+    is flipped (X, vx change sign; hand the same flags to radar_to_pc_dep).  descending = not DATASET.PC_REVERSE
+    (nuscenes.py:196-197); detector.py:281 sorts ascending.  Returns (B, Nmax, 5) f64 sorted [, order (B, Nmax) i32]."""
+    r = _map(raw, "raw", ndim=3, dtype=torch.float64)
+    B = r.shape[0]
+    if packed:
+        if r.shape[2] != 5:
+            raise ValueError("packed points must be (B, Nmax, 5) [X,Y,Z,vx,vz], got %s" % (tuple(r.shape),))
+        rows, Nmax = 0, r.shape[1]
+    else:
+        if r.shape[1] < 10:
+            raise ValueError("raw must be (B, rows >= 10, Nmax), got %s" % (tuple(r.shape),))
+        rows, Nmax = r.shape[1], r.shape[2]
+    cnt = _map(counts, "counts", ndim=1, dtype=torch.int32)
+    fl = None if flip is None else _map(torch.as_tensor(flip, device=r.device).to(torch.int32), "flip", ndim=1,
+                                        dtype=torch.int32)
+    _same_device(r, cnt, fl)
+    out = torch.empty((B, Nmax, 5), dtype=torch.float64, device=r.device)
+    order = torch.empty((B, Nmax), dtype=torch.int32, device=r.device) if return_order else None
+    _call(r.device, "cf_radar_ingest", _ptr(r) if Nmax else None, cnt.data_ptr(), B, rows, Nmax, _ptr(fl),
+                                          int(bool(descending)), out.data_ptr(), _ptr(order), _stream(r))
+    return (out, order) if return_order else out
+
+
 def radar_to_pc_dep(points: torch.Tensor, counts: torch.Tensor, cam: torch.Tensor, calib: torch.Tensor,
                     A_out: torch.Tensor, out_hw, img_wh=(1600, 900), pillar_dims=(1.5, 0.2, 0.2), max_dist=60.0,
-                    z_offset=0.0, return_owner=False, sort_points=False):
+                    z_offset=0.0, return_owner=False, sort_points=False, flip=None):
     """points (B,Nmax,5) f64 [X,Y,Z,vx,vz] camera frame, each frame sorted ascending by Z (or sort_points=True: sorted
     on the device first, row f2; owner indices then refer to the SORTED order); counts (B,) i32;
-    cam (B,3,3) f64; calib (B,3,4) f64; A_out (B,2,3) f64 -> pc_dep (B,3,H,W) f32 [, owner (B,H,W) i32]."""
+    cam (B,3,3) f64; calib (B,3,4) f64; A_out (B,2,3) f64 -> pc_dep (B,3,H,W) f32 [, owner (B,H,W) i32].
+    flip (B,) or None: frames whose image is flipped (nuscenes.py:201-205); their points carry X and vx negated, as
+    radar_ingest(..., flip=flip) leaves them."""
     pts = _map(points, "points", ndim=3, dtype=torch.float64)
     B, Nmax, five = pts.shape
     if five != 5:
@@ -675,6 +707,8 @@ def radar_to_pc_dep(points: torch.Tensor, counts: torch.Tensor, cam: torch.Tenso
     cnt = _map(counts, "counts", ndim=1, dtype=torch.int32)
     if sort_points and Nmax:
         pts = radar_sort(pts, cnt)
+    fl = None if flip is None else _map(torch.as_tensor(flip, device=pts.device).to(torch.int32), "flip", ndim=1,
+                                        dtype=torch.int32)
     cam = _map(cam, "cam", ndim=None, dtype=torch.float64).view(B, 3, 3)
     cal = _map(calib, "calib", ndim=None, dtype=torch.float64).view(B, 3, 4)
     A = _map(A_out, "A_out", ndim=None, dtype=torch.float64).view(B, 2, 3)
@@ -687,10 +721,10 @@ def radar_to_pc_dep(points: torch.Tensor, counts: torch.Tensor, cam: torch.Tenso
     n = _lib.lib().cf_pillars_workspace_bytes(B, Nmax)
     ws = _workspace(dev, n)
     pd = (C.c_double * 3)(*[float(v) for v in pillar_dims])
-    _call(dev, "cf_radar_pillars", _ptr(pts) if Nmax else None, cnt.data_ptr(), B, Nmax, cam.data_ptr(),
-                                           cal.data_ptr(), A.data_ptr(), int(img_wh[0]), int(img_wh[1]), H, W, pd,
-                                           float(max_dist), float(z_offset), pc_dep.data_ptr(), _ptr(owner),
-                                           ws.data_ptr(), ws.numel(), _stream(pts))
+    _call(dev, "cf_radar_pillars_flip", _ptr(pts) if Nmax else None, cnt.data_ptr(), _ptr(fl), B, Nmax, cam.data_ptr(),
+                                                cal.data_ptr(), A.data_ptr(), int(img_wh[0]), int(img_wh[1]), H, W, pd,
+                                                float(max_dist), float(z_offset), pc_dep.data_ptr(), _ptr(owner),
+                                                ws.data_ptr(), ws.numel(), _stream(pts))
     return (pc_dep, owner) if return_owner else pc_dep
 
 

@@ -175,6 +175,21 @@ CF_API int cf_stage_depth_plane(float* pc_dep_dev, const float* pc_dep_host, int
 CF_API int cf_radar_sort(const double* points, const int32_t* counts, int B, int Nmax, double* sorted, int32_t* order,
                          void* stream);
 
+/* ---- f2, complete: from the stored radar array to sorted points ----------------------------------------------
+ * The host-side steps of loadRadarPointCloud between the pickle and processPointCloud
+ * (src/lib/dataset/datasets/nuscenes.py:159-205; src/lib/detector.py:255-283) in one launch:
+ *   layout   raw (B, rows, Nmax) fp64 = per frame the (rows >= 10, N) array tools/convert_nuScenes.py:205-212,252-253
+ *            stores, padded to Nmax columns: rows 0-2 x, y, z (camera frame), rows 8, 9 the compensated velocities
+ *            vx, vz (what drawPcHeat writes, nuscenes.py:259-261).  rows == 0: raw is already (B,Nmax,5) [X,Y,Z,vx,vz];
+ *   sort     stable by depth as in cf_radar_sort; descending != 0: that order reversed = index[::-1] of
+ *            nuscenes.py:196-197 (DATASET.PC_REVERSE false); 0 = detector.py:281 / PC_REVERSE true;
+ *   flip     (B) i32 or NULL: the frame's image is flipped (nuscenes.py:201-205) -> X and vx change sign; pass the
+ *            same flags to cf_radar_pillars_flip, which mirrors the projected pixel column.
+ * The distance filter, PC_Z_OFFSET and the in-image masks (nuscenes.py:172-191) stay in cf_radar_pillars*: they drop
+ * points without changing the order of the others.  sorted (B,Nmax,5) fp64, order (B,Nmax) i32 optional. */
+CF_API int cf_radar_ingest(const double* raw, const int32_t* counts, int B, int rows, int Nmax, const int32_t* flip,
+                           int descending, double* sorted, int32_t* order, void* stream);
+
 /* ---- f4  frustum association of given boxes (training targets) ---------------------------------------------------
  * The per-annotation loop of src/lib/dataset/generic_dataset.py:673-687: cvtPcDepthToHeatmap
  * (src/lib/utils/pointcloud.py:397-481) for box 0, 1, ... of every frame in list order, later boxes overwriting earlier
@@ -272,6 +287,13 @@ CF_API int cf_radar_pillars(const double* points, const int32_t* counts, int B, 
                             const double* calib, const double* A, int img_w, int img_h, int H, int W,
                             const double* pillar_dims_host, double max_dist, double z_offset, float* pc_dep,
                             int32_t* owner, void* ws, size_t ws_bytes, void* stream);
+/* ... for flipped frames (nuscenes.py:201-205): flip (B) i32 or NULL.  A flipped frame's points arrive with X and vx
+ * negated (cf_radar_ingest); the kernel projects and masks the point as loaded, mirrors the pixel column
+ * (img_w - 1 - u) and sizes the pillar at the flipped X, exactly the reference's order of operations. */
+CF_API int cf_radar_pillars_flip(const double* points, const int32_t* counts, const int32_t* flip, int B, int Nmax,
+                                 const double* cam, const double* calib, const double* A, int img_w, int img_h, int H,
+                                 int W, const double* pillar_dims_host, double max_dist, double z_offset, float* pc_dep,
+                                 int32_t* owner, void* ws, size_t ws_bytes, void* stream);
 
 /* Number of kernels the last successful call on this thread launched (bench.py's gpu_launches). */
 CF_API int cf_last_launch_count(void);

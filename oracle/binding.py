@@ -201,8 +201,34 @@ def fusion_decode(output: dict, out_hw=(112, 200), K=100, norm2d=False):
     return ret
 
 
+def radar_ingest(raw, counts, flip=None, descending=False):
+    """nuscenes.py:159-205 / detector.py:255-283 between the pickle and processPointCloud, restated in NumPy: rows
+    0,1,2,8,9 of the stored (rows, N) array, stable depth sort (descending = the reversed stable order, index[::-1] of
+    nuscenes.py:196-197), flip of X and vx (:203-204).  raw (B, rows, Nmax) f64, counts (B,) -> (B, Nmax, 5) f64 and
+    the order (B, Nmax) i32 (source column of every sorted row).  The filters the reference applies before its sort drop
+    points without changing the order of the others: they live in radar_pillars."""
+    raw = _f64(raw)
+    B, rows, Nmax = raw.shape
+    out = np.empty((B, Nmax, 5), np.float64)
+    order = np.empty((B, Nmax), np.int32)
+    for b in range(B):
+        n = min(Nmax, max(0, int(counts[b])))
+        pts = raw[b][[0, 1, 2, 8, 9], :].T.copy()  # (Nmax, 5)
+        idx = np.argsort(pts[:n, 2], kind="stable")
+        if descending:
+            idx = idx[::-1]
+        idx = np.concatenate([idx, np.arange(n, Nmax)]).astype(np.int64)
+        srt = pts[idx]
+        if flip is not None and flip[b]:
+            srt[:n, 0] *= -1
+            srt[:n, 3] *= -1
+        out[b] = srt
+        order[b] = idx
+    return out, order
+
+
 def radar_pillars(points, counts, cam, calib, A, img_wh, out_hw, pillar_dims=(1.5, 0.2, 0.2), max_dist=60.0,
-                  z_offset=0.0, want_owner=True):
+                  z_offset=0.0, want_owner=True, flip=None):
     points = _f64(points)
     B, Nmax, five = points.shape
     assert five == 5
@@ -214,7 +240,8 @@ def radar_pillars(points, counts, cam, calib, A, img_wh, out_hw, pillar_dims=(1.
     pd = _f64(pillar_dims)
     pc_dep = np.empty((B, 3, H, W), np.float32)
     owner = np.empty((B, H, W), np.int32) if want_owner else None
-    lib().cfo_radar_pillars(_p(points, _f64p), _p(counts, _i32p), B, Nmax, _p(cam, _f64p), _p(calib, _f64p),
+    flip = None if flip is None else np.ascontiguousarray(flip, dtype=np.int32)
+    lib().cfo_radar_pillars(_p(points, _f64p), _p(counts, _i32p), _p(flip, _i32p), B, Nmax, _p(cam, _f64p), _p(calib, _f64p),
                             _p(A, _f64p), int(img_wh[0]), int(img_wh[1]), H, W, _p(pd, _f64p),
                             C.c_double(float(max_dist)), C.c_double(float(z_offset)), _p(pc_dep, _f32p),
                             _p(owner, _i32p))

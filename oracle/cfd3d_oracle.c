@@ -532,9 +532,9 @@ CFO_API int cfo_fusion_decode(const float* heat, const float* reg, const float* 
  * pillar corners; A (B,2,3) output affine.  pc_dep (B,3,H,W) fp32 out.  owner (B,H,W) int32
  * out (optional): index of the surviving point per pixel, or -1.
  * ------------------------------------------------------------------------------------------ */
-CFO_API void cfo_radar_pillars(const double* points, const int32_t* counts, int B, int Nmax, const double* cam,
-                               const double* calib, const double* A, int img_w, int img_h, int H, int W,
-                               const double* pillar_dims /*h,w,l*/, double max_dist, double z_offset,
+CFO_API void cfo_radar_pillars(const double* points, const int32_t* counts, const int32_t* flip /*B or NULL*/, int B,
+                               int Nmax, const double* cam, const double* calib, const double* A, int img_w, int img_h,
+                               int H, int W, const double* pillar_dims /*h,w,l*/, double max_dist, double z_offset,
                                float* pc_dep, int32_t* owner) {
     size_t HW = (size_t)H * W;
     memset(pc_dep, 0, sizeof(float) * 3 * HW * (size_t)B);
@@ -557,13 +557,18 @@ CFO_API void cfo_radar_pillars(const double* points, const int32_t* counts, int 
             double X = pt[0], Y = pt[1], Z = pt[2];
             if (max_dist > 0 && !(Z <= max_dist)) continue; /* nuscenes.py:177-180 */
             Y -= z_offset;                                  /* :183-184 */
+            /* a flipped frame (nuscenes.py:201-205) arrives with X and vx negated; the reference projects and masks
+               the point as loaded (:187-191), THEN mirrors the pixel column (:202) and the 3-D X (:203) */
+            const int flipped = flip && flip[b];
+            const double Xp = flipped ? -X : X;
             /* view_points, normalize=True */
-            double uh = Kc[0] * X + Kc[1] * Y + Kc[2] * Z;
-            double vh = Kc[3] * X + Kc[4] * Y + Kc[5] * Z;
-            double zh = Kc[6] * X + Kc[7] * Y + Kc[8] * Z;
+            double uh = Kc[0] * Xp + Kc[1] * Y + Kc[2] * Z;
+            double vh = Kc[3] * Xp + Kc[4] * Y + Kc[5] * Z;
+            double zh = Kc[6] * Xp + Kc[7] * Y + Kc[8] * Z;
             double u = uh / zh, v = vh / zh;
             /* pointcloud.py:40-45 */
             if (!(Z > 0 && u > 1 && u < img_w - 1 && v > 1 && v < img_h - 1)) continue;
+            if (flipped) u = (double)(img_w - 1) - u; /* img.shape[1] - 1 - pc_2d[0] */
             /* transformPointCloud :853-862 */
             double up = Ab[0] * u + Ab[1] * v + Ab[2];
             double vp = Ab[3] * u + Ab[4] * v + Ab[5];

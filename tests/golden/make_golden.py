@@ -377,6 +377,57 @@ def gen_gt_assoc():
     save("gt_assoc", in_max_pc_dist=np.float32(60.0), in_frames=np.int64(len(frames)), **arrs)
 
 
+def gen_radar_ingest():
+    """Row f2, complete: the reference's OWN loadRadarPointCloud (dataset/datasets/nuscenes.py:131-218) run on pickled
+    (18, N) radar arrays written where it looks for them -- distance filter, z offset, projection + masks, depth sort
+    (+ reversal when PC_REVERSE is false), flip, processPointCloud.  Outputs: pc_dep and the padded, sorted pc_3d."""
+    import pickle
+    import tempfile
+    import types
+
+    GD, NU = ns.generic_dataset.GenericDataset, ns.nuscenes.nuScenes
+    cases = [  # tag, out_hw, N, flipped, PC_REVERSE, PC_Z_OFFSET, seed
+        ("a", (112, 200), 150, False, False, 0, 31),
+        ("b", (112, 200), 150, True, False, 0, 32),
+        ("c", (112, 200), 300, True, True, 0.5, 33),
+        ("d", (225, 400), 300, False, True, 0, 34),
+    ]
+    arrs = {"in_cases": np.array([c[0] for c in cases])}
+    with tempfile.TemporaryDirectory() as tmp:
+        for tag, (H, W), n, flipped, reverse, zoff, seed in cases:
+            cfg = refimport.make_config(K=100, out_hw=(H, W))
+            cfg.DATASET.PC_REVERSE = reverse
+            cfg.DATASET.PC_Z_OFFSET = zoff
+            cfg.DATASET.RADAR_PC = True
+            rng = np.random.default_rng(seed)
+            pts, _ = syn.make_radar(rng, 1, n)
+            pts = pts[0][rng.permutation(n)]  # as stored: NOT sorted
+            raw = rng.normal(size=(18, n))     # the other rows (rcs, raw velocities, ...) are never read on this path
+            raw[0:3] = pts[:, 0:3].T
+            raw[8], raw[9] = pts[:, 3], pts[:, 4]
+            calib = syn.make_calib(rng, 1)[0]
+            A = syn.output_affine(H, W)
+            d = os.path.join(tmp, "annotations", "radar_pc", "CAM_FRONT")
+            os.makedirs(d, exist_ok=True)
+            with open(os.path.join(d, "tok_%s.bin" % tag), "wb") as f:
+                pickle.dump(raw.tolist(), f)
+            self = types.SimpleNamespace(config=cfg, img_dir=tmp, SENSOR_NAME={1: "CAM_FRONT"})
+            for name in ("transformPointCloud", "getPcPillarsSize", "processPointCloud"):
+                setattr(self, name, types.MethodType(getattr(GD, name), self))
+            for name in ("getDepthMap", "drawPcHeat", "loadRadarPointCloud"):
+                setattr(self, name, types.MethodType(getattr(NU, name), self))
+            img_info = {"sensor_id": 1, "sample_token": "tok_%s" % tag, "camera_intrinsic": calib[:, :3].tolist(),
+                        "width": 1600, "height": 900, "calib": calib.tolist()}
+            img = np.zeros((900, 1600, 3), np.uint8)
+            pc_z, pc_N, pc_dep, pc_3dz = self.loadRadarPointCloud(img, img_info, A, A, flipped)
+            print("radar_ingest", tag, "points in", n, "kept", int(pc_N), "painted px", int((pc_dep[0] != 0).sum()))
+            arrs.update({"in_raw_" + tag: raw, "in_calib_" + tag: calib, "in_A_" + tag: A, "in_hw_" + tag: np.array([H, W]),
+                         "in_flip_" + tag: np.bool_(flipped), "in_reverse_" + tag: np.bool_(reverse),
+                         "in_zoff_" + tag: np.float64(zoff), "out_pc_dep_" + tag: pc_dep,
+                         "out_pc_N_" + tag: np.int64(pc_N), "out_pc_3d_" + tag: pc_3dz, "out_pc_2d_" + tag: pc_z})
+    save("radar_ingest", **arrs)
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1:  # python tests/golden/make_golden.py gen_cfg1_model
         for name in sys.argv[1:]:
@@ -390,3 +441,4 @@ if __name__ == "__main__":
     gen_post_process()
     gen_cfg1_model()
     gen_gt_assoc()
+    gen_radar_ingest()

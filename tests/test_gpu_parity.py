@@ -376,6 +376,51 @@ def test_radar_sort_on_device(ops, oracle):
     eq(npy(b_), pc_o, "pc_dep vs oracle")
 
 
+def test_golden_radar_ingest_and_flip(ops, oracle):
+    """Row f2, complete: the stored (18, N) radar array through ops.radar_ingest + ops.radar_to_pc_dep(flip=...) against
+    the reference's own loadRadarPointCloud (fixture gen_radar_ingest) -- pc_dep bit-exact -- and against the oracle's
+    restatement of the ingestion; then all cases as ONE ragged batch (Nmax = the largest, per-frame flip flags)."""
+    from test_oracle_golden import check_sorted_points_against_reference, radar_ingest_cases
+    g = load_golden("radar_ingest")
+    cases = list(radar_ingest_cases(g))
+    for tag, raw, cnt, calib, A, (H, W), flip, desc, zoff in cases:
+        pts, order = ops.radar_ingest(cu(raw), cu(cnt), flip=cu(flip), descending=desc, return_order=True)
+        pts_o, order_o = oracle.radar_ingest(raw, cnt, flip, desc)
+        eq(npy(pts), pts_o, "ingested points " + tag)
+        eq(npy(order), order_o, "order " + tag)
+        check_sorted_points_against_reference(g, tag, npy(pts)[0], zoff)
+        pc_dep = ops.radar_to_pc_dep(pts, cu(cnt), cu(calib[:, :, :3]), cu(calib), cu(A), (H, W), z_offset=zoff,
+                                     flip=cu(flip))
+        eq(npy(pc_dep)[0], g["out_pc_dep_" + tag], "pc_dep " + tag)
+    # one batch of the three 112x200 cases (they differ in N, flip and order direction: direction is per call)
+    for desc in (False, True):
+        sel = [c for c in cases if c[5] == (112, 200) and c[7] == desc and c[8] == 0.0]
+        if not sel:
+            continue
+        Nmax = max(c[1].shape[2] for c in sel)
+        raw = np.zeros((len(sel), 18, Nmax))
+        for i, c in enumerate(sel):
+            raw[i, :, :c[1].shape[2]] = c[1][0]
+        cnt = np.array([c[1].shape[2] for c in sel], np.int32)
+        calib = np.concatenate([c[3] for c in sel])
+        A = np.concatenate([c[4] for c in sel])
+        flip = np.array([bool(c[6][0]) for c in sel])
+        pts = ops.radar_ingest(cu(raw), cu(cnt), flip=cu(flip), descending=desc)
+        pc_dep = ops.radar_to_pc_dep(pts, cu(cnt), cu(calib[:, :, :3]), cu(calib), cu(A), (112, 200), flip=cu(flip))
+        for i, c in enumerate(sel):
+            eq(npy(pc_dep)[i], g["out_pc_dep_" + c[0]], "batched pc_dep " + c[0])
+    # packed [X,Y,Z,vx,vz] input, ties: descending == the reversed stable order
+    rng = np.random.default_rng(5)
+    p5 = rng.normal(size=(2, 40, 5))
+    p5[:, 10:20, 2] = p5[:, 3:4, 2]
+    cnt = np.array([40, 33], np.int32)
+    got = npy(ops.radar_ingest(cu(p5), cu(cnt), descending=True, packed=True))
+    for b in range(2):
+        n = int(cnt[b])
+        eq(got[b, :n], p5[b, :n][np.argsort(p5[b, :n, 2], kind="stable")[::-1]], "descending stable")
+        eq(got[b, n:], p5[b, n:], "padding rows stay")
+
+
 def test_frustum_targets(ops, oracle):
     """f4: association of given (ground-truth style) boxes in list order == the oracle's cvtPcDepthToHeatmap loop
     (pinned on the reference by the quirk fixtures), ragged counts included."""

@@ -71,6 +71,50 @@ def test_pillars_bit_exact(oracle):
         assert (ref[:, 0] != 0).mean() > 0.05
 
 
+def radar_ingest_cases(g):
+    """(tag, raw (1,18,N), counts, calib (1,3,4), A (1,2,3), (H,W), flip (1,), descending, z_offset) per fixture case."""
+    for tag in (str(t) for t in g["in_cases"]):
+        raw = g["in_raw_" + tag][None]
+        yield (tag, raw, np.array([raw.shape[2]], np.int32), g["in_calib_" + tag][None], g["in_A_" + tag][None],
+               tuple(int(v) for v in g["in_hw_" + tag]), np.array([bool(g["in_flip_" + tag])]),
+               not bool(g["in_reverse_" + tag]), float(g["in_zoff_" + tag]))
+
+
+def check_sorted_points_against_reference(g, tag, pts, zoff):
+    """The reference's padded pc_3d (18, MAX_PC) holds the points it kept, in its order: they must appear in the
+    ingested (sorted, flipped) points in the same order, values bit-equal (Y after the z offset)."""
+    n_kept = min(int(g["out_pc_N_" + tag]), g["out_pc_3d_" + tag].shape[1])
+    ref = g["out_pc_3d_" + tag][[0, 1, 2, 8, 9], :n_kept].T
+    mine = pts.copy()
+    mine[:, 1] -= zoff
+    pos = 0
+    for row in ref:
+        while pos < len(mine) and not np.array_equal(mine[pos], row):
+            pos += 1
+        assert pos < len(mine), "%s: a kept point is missing or out of order" % tag
+        pos += 1
+
+
+def test_radar_ingest_and_flip(oracle):
+    """Row f2, complete: stored (18, N) array -> pc_dep, against the reference's own loadRadarPointCloud
+    (nuscenes.py:131-218; fixture gen_radar_ingest): layout, sort order incl. PC_REVERSE, flip, z offset -- bit-exact."""
+    g = load_golden("radar_ingest")
+    flips = 0
+    for tag, raw, cnt, calib, A, (H, W), flip, desc, zoff in radar_ingest_cases(g):
+        pts, order = oracle.radar_ingest(raw, cnt, flip, desc)
+        z = pts[0, :, 2]
+        assert (np.diff(z) <= 0).all() if desc else (np.diff(z) >= 0).all()
+        assert np.array_equal(np.sort(order[0]), np.arange(raw.shape[2]))
+        check_sorted_points_against_reference(g, tag, pts[0], zoff)
+        pc_dep, _ = oracle.radar_pillars(pts, cnt, calib[:, :, :3], calib, A, (1600, 900), (H, W), z_offset=zoff,
+                                         flip=flip)
+        ref = g["out_pc_dep_" + tag]
+        assert np.array_equal(pc_dep[0].view(np.uint32), ref.view(np.uint32)), tag
+        assert (ref[0] != 0).mean() > 0.05
+        flips += int(flip[0])
+    assert flips >= 2
+
+
 def test_frustum_pc_hm(oracle):
     g = load_golden("frustum_decode")
     K = int(g["in_K"])
