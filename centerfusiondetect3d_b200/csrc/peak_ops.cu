@@ -108,7 +108,10 @@ __global__ void __launch_bounds__(256) gather_kernel(const float* __restrict__ f
         const int c = (int)(t % ch);
         const long long bm = t / ch;
         const long long b = bm / M;
-        out[t] = __ldg(feat + ((size_t)b * ch + c) * HW + inds[bm]);
+        // (torch.gather raises a device-side assert on an index outside [0, HW); here the element becomes NaN and
+        // nothing outside the tensor is read)
+        const long long ix = inds[bm];
+        out[t] = (ix >= 0 && ix < HW) ? __ldg(feat + ((size_t)b * ch + c) * HW + ix) : __int_as_float(0x7fc00000);
     }
 }
 

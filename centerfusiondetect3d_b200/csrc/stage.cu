@@ -180,6 +180,8 @@ struct StageParams {
     int off_comp, off_ind, off_msm, off_gath, off_det, off_best, off_par, off_own;
     int GB;            // detections per gather batch
     int wl_entries;    // words of the pass-B work list
+    int g_log2;        // a lane's group in passes A / B = 2^g_log2 float4 items of a chunk (32 << g_log2 >= R * Wp / 4) ...
+    int g_contig;      // ... consecutive ones (1) or every 32nd (0)
     int gmax_off;      // streamed shares: byte offset (from the histogram) of the per-(chunk, lane) group maxima, then the flagged list
     int fl_cap;        // capacity of the flagged-group list
     uint32_t* ctr;
@@ -341,7 +343,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
     const uint32_t rank = cl_rank(), cs = cl_size();
     const int cluster_id = (int)(blockIdx.x >> p.cs_log2), n_clusters = (int)(gridDim.x >> p.cs_log2);
     const int C = p.C, H = p.H, W = p.W, Wp = p.Wp, R = p.R, S = p.S, K = p.K;
-    const int CH = C * H, W4 = Wp >> 2;
+    const int CH = C * H, W4 = Wp >> 2, g_log2 = p.g_log2;
+    const bool g_contig = p.g_contig != 0;
     const size_t HW = (size_t)H * W;
     constexpr bool FUSED = SPEC != SPEC_ANY;  // (not `FULL`: that is the full-warp mask of common.cuh)
     const bool want_raw = FUSED || (p.lists & LIST_RAW) != 0, want_nms = FUSED || (p.lists & LIST_NMS) != 0;
@@ -465,8 +468,10 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         if (use_tma && tid < (LPF < S ? LPF : S)) issue_load(tid);
         if (do_frustum && tid >= ST - 2)  // (the last warp: it stalls on this DRAM read before its first chunk)
             s_cal[tid - (ST - 2)] = __ldg(p.mp.job[0].fh.calib + 12 * (size_t)b + 2 * (tid - (ST - 2)));
-        if (do_frustum && tid == 0) {  // the association's radar maps: into L2 while the heat-map streams
-            const size_t total = (p.pc_vel == p.pc_dep ? 3 : 1) * HW * 4, per = ((total + cs - 1) / cs + 15) & ~(size_t)15;
+        if (do_frustum && tid == 0) {  // the association's depth plane: into L2 while the heat-map streams
+            // (NOT the velocity planes: they are read at <= K matched pixels, and prefetching them whole cost a streamed
+            // frame 2 % -- 179 KB of DRAM reads beside the 896 KB it streams -- and gained the others nothing)
+            const size_t total = HW * 4, per = ((total + cs - 1) / cs + 15) & ~(size_t)15;
             const size_t off = per * rank;
             if (off < total) {
                 const size_t nbytes = (min(per, total - off)) & ~(size_t)15;
@@ -484,6 +489,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         {
             const float inv_w4 = 1.0f / (float)W4;
             uint32_t tkraw = 0u, tknms = 0u;
+            const int G = 1 << g_log2;
             for (int q = warp; q < n; q += SNW) {
                 const int rr = row_begin + q * R, nr = min(R, row_end - rr);
                 float* tile;
@@ -497,19 +503,29 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                 const int n_items = nr * W4;
                 const float4* c4p = reinterpret_cast<const float4*>(tile);
                 float best = -CUDART_INF_F;
-                int bi = lane;
+                // a lane's group = G float4 items.  Consecutive ones (g_contig): the filter pass re-reads a flagged group
+                // as one contiguous run -- whole sectors from L2, conflict-free out of shared memory -- and a blob
+                // flags half as many groups; the visiting order is rotated by the lane index so that the eight lanes
+                // of a quarter-warp hit eight different bank groups.  Or every 32nd item: a blob's pixels spread over
+                // many groups, which makes the bound below tighter (about half the survivors) -- the choice of large K,
+                // where the survivors must still fit their list (launch_fusion_stage).
+                const int gbase = g_contig ? lane << g_log2 : lane;
+                int bi = gbase;
 #pragma unroll 4
-                for (int i = lane; i < n_items; i += 32) {
-                    const float4 v = c4p[i];
-                    const float m = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
-                    if (m > best) {
-                        best = m;
-                        bi = i;
+                for (int t = 0; t < G; ++t) {
+                    const int i = g_contig ? gbase + ((t + lane) & (G - 1)) : lane + 32 * t;
+                    if (i < n_items) {
+                        const float4 v = c4p[i];
+                        const float m = fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w));
+                        if (m > best) {
+                            best = m;
+                            bi = i;
+                        }
                     }
                 }
                 uint32_t kraw = 0u, knms = 0u;
                 int r = 0, x = -1;
-                if (lane < n_items) {
+                if (gbase < n_items) {
                     r = (int)(((float)bi + 0.5f) * inv_w4);  // bi / W4, exact for bi < 2^21
                     int cc = bi - r * W4;
                     if (cc < 0) {
@@ -734,7 +750,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     // every half-warp takes up to 8 groups per round; a lane collects the candidate bits of all of them in
                     // one register first (loads back to back), so that the reservation and the parking happen once
                     const int hw = tid >> 4, hl = tid & 15;
-                    const int chunk_items = R * W4, t_max = (chunk_items + 31) >> 5;
+                    const int chunk_items = R * W4, t_max = 1 << g_log2;
                     const float4* c4p = resident ? reinterpret_cast<const float4*>(slots)
                                                  : reinterpret_cast<const float4*>(frame + (size_t)row_begin * W);
                     for (int f0 = 0; f0 < nfl; f0 += 8 * (ST / 16)) {
@@ -745,8 +761,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                                 const int f = f0 + u * (ST / 16) + hw;
                                 if (f < nfl) {
                                     const int code = (int)fl_list[f];
-                                    const int q = code >> 5, i = (code & 31) + 32 * (t0 + hl);
-                                    if (i < min(R, row_end - (row_begin + q * R)) * W4) {
+                                    const int q = code >> 5, i = g_contig ? ((code & 31) << g_log2) + t0 + hl : (code & 31) + 32 * (t0 + hl);
+                                    if (t0 + hl < t_max && i < min(R, row_end - (row_begin + q * R)) * W4) {
                                         const float4 v = c4p[q * chunk_items + i];  // (chunks are contiguous in both memories)
                                         const uint32_t m4 = (v.x >= tau_min ? 1u : 0u) | (v.y >= tau_min ? 2u : 0u) |
                                                             (v.z >= tau_min ? 4u : 0u) | (v.w >= tau_min ? 8u : 0u);
@@ -761,7 +777,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                             slot = __shfl_sync(FULL, slot, 0);
                             park(mask, slot, [&](int bit) {
                                 const int code = (int)fl_list[f0 + (bit >> 2) * (ST / 16) + hw];
-                                const int q = code >> 5, i = (code & 31) + 32 * (t0 + hl);
+                                const int q = code >> 5, i = g_contig ? ((code & 31) << g_log2) + t0 + hl : (code & 31) + 32 * (t0 + hl);
                                 // resident: one contiguous tile, the pixel index alone (16 bits); streamed: (chunk, pixel)
                                 return resident ? (q * chunk_items + i) * 4 : ((q << 16) | (i * 4));
                             });
@@ -1423,6 +1439,12 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     p.off_own = best.off_own;
     p.GB = best.GB;
     p.wl_entries = best.wl_entries;
+    p.g_log2 = 0;
+    while ((32ll << p.g_log2) < (long long)p.R * (p.Wp / 4)) ++p.g_log2;
+    // consecutive groups roughly double the survivors of the raw list (measured: 2.8 -> 4.7 x K at the reference size,
+    // 2.3 -> 4.5 x K at 225 x 400, K = 500); a list that overflows CAND_CAP falls back to the exact selection from the
+    // frame, which is milliseconds
+    p.g_contig = 8ll * K <= CAND_CAP ? 1 : 0;
     p.gmax_off = best.gmax_off;
     p.fl_cap = best.fl_cap;
     p.ctr = ws.ctr;

@@ -187,6 +187,13 @@ def test_get_feature_bnc_form(ops):
     ind = rng.integers(0, 50, size=(3, 11)).astype(np.int64)
     want = np.take_along_axis(feat, ind[:, :, None].repeat(7, axis=2), axis=1)
     eq(npy(ops.getFeature(cu(feat), cu(ind))), want, "getFeature")
+    # an index outside the tensor reads nothing and yields NaN (torch.gather: device-side assert)
+    ind[1, 4], ind[2, 0] = 50, -1
+    got = npy(ops.getFeature(cu(feat), cu(ind)))
+    assert np.isnan(got[1, 4]).all() and np.isnan(got[2, 0]).all()
+    ok = np.ones((3, 11), bool)
+    ok[1, 4] = ok[2, 0] = False
+    eq(got[ok], want[ok], "getFeature, in-range rows")
 
 
 # ------------------------------------------------------------------------------------------------
