@@ -84,6 +84,7 @@ SYMBOLS = {
     "cf_radar_sort": (_I, [_vp, _vp, _I, _I, _vp, _vp, _vp]),
     "cf_radar_ingest": (_I, [_vp, _vp, _I, _I, _I, _vp, _I, _vp, _vp, _vp]),
     "cf_frustum_boxes": (_I, [_vp] * 5 + [_I] * 4 + [_F, _vp, _vp, _vp, _Z, _vp]),
+    "cf_frustum_boxes_static": (_I, [_vp] * 5 + [_I] * 4 + [_F, _vp, _vp, _vp]),
     "cf_frustum_boxes_f64": (_I, [_vp] * 5 + [_I] * 4 + [_F, _I, _vp, _vp, _vp, _Z, _vp]),
     "cf_post_process": (_I, [C.POINTER(PostIn), _I, _I, _I, _I, C.POINTER(C.c_float), _vp, _I, C.POINTER(PostOut), _vp]),
     "cf_radar_pillars": (_I, [_vp, _vp, _I, _I, _vp, _vp, _vp, _I, _I, _I, _I, C.POINTER(_D), _D, _D, _vp, _vp, _vp,

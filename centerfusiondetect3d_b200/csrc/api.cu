@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 #include "kernels.cuh"
 
@@ -505,3 +506,57 @@ int cf_radar_pillars_flip(const double* points, const int32_t* counts, const int
 }
 
 }  // extern "C"
+
+// -----------------------------------------------------------------------------------------------------
+// cf_frustum_boxes_static: cf_frustum_boxes without a caller-provided workspace -- for callers that cannot allocate
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+// reference.  The paint records box_assoc_kernel hands to paint_kernel
+// live in the file-scope device array below (CF_STATIC_MAX_BOXES records of 32 bytes = 1 MiB, held by every GPU that
+// loads the library until the process exits).  Host code must not pass the array's NAME to a kernel (on the host it is
+// a stand-in, not a device address): its device address is taken once per device with cudaGetSymbolAddress, with that
+// device current, and that pointer goes to the kernels.  Nothing here allocates.
+// -----------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_recs[(size_t)CF_STATIC_MAX_BOXES * sizeof(PaintRec)];
+
+static constexpr int STATIC_MAX_DEV = 64;
+static PaintRec* g_static_ptr[STATIC_MAX_DEV];  // per device: the array's address on THAT device (zero = not asked yet)
+static std::mutex g_static_mu;
+
+// device address of g_static_recs on the current device (set-up: once per device)
+static int static_recs(PaintRec** out) {
+    int dev = -1;
+    CF_CUDA(cudaGetDevice(&dev), "cf_frustum_boxes_static: cudaGetDevice");
+    if (dev < 0 || dev >= STATIC_MAX_DEV) return fail(CF_E_RANGE, "cf_frustum_boxes_static: device ordinal %d >= %d", dev, STATIC_MAX_DEV);
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        void* ptr = nullptr;
+        CF_CUDA(cudaGetSymbolAddress(&ptr, g_static_recs), "cf_frustum_boxes_static: cudaGetSymbolAddress");
+        if (!ptr) return fail(CF_E_NULL, "cf_frustum_boxes_static: cudaGetSymbolAddress returned NULL");
+        g_static_ptr[dev] = reinterpret_cast<PaintRec*>(ptr);
+    }
+    *out = g_static_ptr[dev];
+    return 0;
+}
+
+extern "C" int cf_frustum_boxes_static(const float* pc_dep, const float* bboxes, const float* depth, const float* thr,
+                                       const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, float* pc_hm,
+                                       int32_t* assoc, void* stream) {
+    g_launches = 0;
+    if (!pc_dep || !pc_hm || (N > 0 && (!bboxes || !depth || !thr))) return fail(CF_E_NULL, "cf_frustum_boxes_static: NULL pointer");
+    if (B < 0 || N < 0 || H < 1 || W < 1 || H > 32767 || W > 32767) return fail(CF_E_SHAPE, "cf_frustum_boxes_static: bad shape");
+    if ((long long)B * N > (long long)CF_STATIC_MAX_BOXES)
+        return fail(CF_E_WORKSPACE, "cf_frustum_boxes_static: B*N = %lld boxes exceed the static scratch of %d (use cf_frustum_boxes "
+                                    "with a workspace)", (long long)B * N, CF_STATIC_MAX_BOXES);
+    if (B == 0) return 0;
+    PaintRec* recs = nullptr;
+    if (int rc = static_recs(&recs)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    int n = 0;
+    // (every record [0, B*N) is written by box_assoc_kernel before paint_kernel reads it: nothing has to start at zero,
+    // whatever the last call left in the array)
+    CF_KERNEL(CF_KERNEL_ASSOC, st,
+              launch_box_assoc(pc_dep, bboxes, depth, thr, counts, B, N, H, W, max_pc_dist, recs, assoc, st, &n), "box_assoc");
+    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint(recs, N, N, counts, B, H, W, pc_hm, nullptr, st, &n), "paint");
+    g_launches = n;
+    return 0;
+}

@@ -215,6 +215,22 @@ CF_API int cf_frustum_boxes_f64(const float* pc_dep, const double* bboxes, const
                                 const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, int flags,
                                 float* pc_hm, int32_t* assoc, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- cf_frustum_boxes for callers that cannot allocate ---------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs and
+ * results as cf_frustum_boxes, but no workspace argument: the paint records between its two kernels live in a
+ * file-scope `static __device__` array of the library (csrc/api.cu), CF_STATIC_MAX_BOXES records of 32 bytes = 1 MiB,
+ * held by every GPU that loads the library until the process exits.  B * N > CF_STATIC_MAX_BOXES is refused with
+ * CF_E_WORKSPACE.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine); its one piece
+ * of set-up, once per device, is cudaGetSymbolAddress of the array with that device current.  Every call on a device
+ * shares the array, which keeps the last call's contents -- every record a call reads it has written first, so nothing
+ * needs clearing -- and therefore calls that OVERLAP on one GPU (different streams, parallel graph branches) race:
+ * serialise them, or use cf_frustum_boxes with one workspace each. */
+#define CF_STATIC_MAX_BOXES 32768
+CF_API int cf_frustum_boxes_static(const float* pc_dep, const float* bboxes, const float* depth, const float* thr,
+                                   const int32_t* counts, int B, int N, int H, int W, float max_pc_dist, float* pc_hm,
+                                   int32_t* assoc, void* stream);
+
 /* ---- f1  postProcess(y, center, scale, height, width, calibs, isGt)   src/lib/utils/postProcess.py:13-85 ----
  * Decoded detections (the cf_fusion_decode outputs) -> image-space boxes, camera-frame locations, yaw, velocity
  * re-oriented along the box and the 8 corners of the 3-D box (utils/ddd.py:8-23, :122-199).  One detection per
