@@ -70,13 +70,20 @@ __device__ __forceinline__ unsigned long long roi_scan_box(const float* dep, int
                 const float t_ = dep[(size_t)yc * W + xx];
                 v[u] = yy < yb ? t_ : 0.0f;
             }
+            // (lo >= 0, so `> lo` already excludes the empty pixels, 0 and -0, and NaN; almost every pixel fails the
+            // window: the common path is two compares per pixel, the key is built behind a branch)
+            uint32_t hit = 0u;
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int yy = y0 + u * rows_par;
-                if (v[u] != 0.0f && v[u] < hi && v[u] > lo) {
-                    const unsigned long long key = ((unsigned long long)__float_as_uint(v[u]) << 32) |
-                                                   (unsigned long long)(uint32_t)(yy * W + xx);
-                    best = key < best ? key : best;
+            for (int u = 0; u < U; ++u) hit |= (v[u] > lo && v[u] < hi) ? (1u << u) : 0u;
+            if (hit) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    if (hit >> u & 1u) {
+                        const int yy = y0 + u * rows_par;
+                        const unsigned long long key = ((unsigned long long)__float_as_uint(v[u]) << 32) |
+                                                       (unsigned long long)(uint32_t)(yy * W + xx);
+                        best = key < best ? key : best;
+                    }
                 }
             }
         }
@@ -84,10 +91,12 @@ __device__ __forceinline__ unsigned long long roi_scan_box(const float* dep, int
     return best;
 }
 
-// One warp, four pixels per load: lanes run over column QUADS (float4 loads; W % 4 == 0 and a 16-byte aligned plane
-// required), rows unrolled.  A wide ROI costs a quarter of the load batches of roi_scan_box -- the big boxes set the pace
-// of the association (the cluster waits for the slowest warp of its slowest CTA).  Columns of the first / last quad
-// outside [xa, xb) are masked; the minimum key is the same as roi_scan_box's whatever the visiting order.
+// One warp, four pixels per load (float4; W % 4 == 0 and a 16-byte aligned plane required).  The (row, column quad)
+// pairs of the ROI are dealt to the lanes as ONE flat sequence, U loads per lane in flight: every lane is busy whatever
+// the ROI's width (lanes over columns leave 14 of 32 idle on an 18-quad box), so a scan out of L2 -- which is bound by
+// the number of dependent load batches, one L2 latency each -- needs half the batches.  The big boxes set the pace of
+// the association (the cluster waits for the slowest warp of its slowest CTA).  Columns of the first / last quad outside
+// [xa, xb) are masked; the minimum key is the same as roi_scan_box's whatever the visiting order.
 template <int U>
 __device__ __forceinline__ unsigned long long roi_scan_box4(const float* dep, int W, int ya, int yb, int xa, int xb,
                                                             float depth, float thr, int lane) {
@@ -97,34 +106,43 @@ __device__ __forceinline__ unsigned long long roi_scan_box4(const float* dep, in
     unsigned long long best = ~0ull;
     if (ya >= yb || xa >= xb) return best;
     const int qa = xa >> 2, qb = (xb + 3) >> 2;  // column quads [qa, qb)
-    const int nq = qb - qa;
-    const int cols = nq < 32 ? nq : 32;
-    const float inv = __fdividef(1.0f, (float)cols);  // see roi_scan_box
-    const int rows_par = (int)(32.5f * inv);
-    const int ty = (int)(((float)lane + 0.5f) * inv), tx = lane - ty * cols;
-    if (ty >= rows_par) return best;
-    for (int q = qa + tx; q < qb; q += cols) {
-        const int x0 = 4 * q;
-        uint32_t mask = 0u;  // columns of this quad inside the ROI
+    const int nq = qb - qa, total = nq * (yb - ya);
+    const float inv = 1.0f / (float)nq;
+    for (int j0 = 0; j0 < total; j0 += 32 * U) {
+        float4 v[U];
+        int px[U], x0[U];  // flat pixel index / column of the quad's first pixel; px = -1: no item
 #pragma unroll
-        for (int j = 0; j < 4; ++j) mask |= (x0 + j >= xa && x0 + j < xb) ? (1u << j) : 0u;
-        for (int y0 = ya + ty; y0 < yb; y0 += U * rows_par) {
-            float4 v[U];
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int yy = y0 + u * rows_par;
-                const int yc = yy < yb ? yy : ya;  // clamped: the load is unconditional
-                v[u] = *reinterpret_cast<const float4*>(dep + (size_t)yc * W + x0);
+        for (int u = 0; u < U; ++u) {
+            const int j = j0 + u * 32 + lane;
+            const int jj = j < total ? j : 0;  // (the load is unconditional)
+            int r = (int)(((float)jj + 0.5f) * inv);  // jj / nq; exact after the fix-up below
+            int q = jj - r * nq;
+            if (q < 0) {
+                --r;
+                q += nq;
+            } else if (q >= nq) {
+                ++r;
+                q -= nq;
             }
+            x0[u] = 4 * (qa + q);
+            const int p0 = (ya + r) * W + x0[u];
+            v[u] = *reinterpret_cast<const float4*>(dep + p0);
+            px[u] = j < total ? p0 : -1;
+        }
+        // (lo >= 0, so `> lo` already excludes the empty pixels and NaN; almost every pixel fails the window: the common
+        // path is two compares per pixel, column mask and key are worked out behind a branch)
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int yy = y0 + u * rows_par;
-                const float c4[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+        for (int u = 0; u < U; ++u) {
+            const float c4[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+            uint32_t hit = 0u;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    if (c4[j] != 0.0f && c4[j] < hi && c4[j] > lo && yy < yb && (mask >> j & 1u)) {
-                        const unsigned long long key = ((unsigned long long)__float_as_uint(c4[j]) << 32) |
-                                                       (unsigned long long)(uint32_t)(yy * W + x0 + j);
+            for (int c = 0; c < 4; ++c) hit |= (c4[c] > lo && c4[c] < hi) ? (1u << c) : 0u;
+            if (hit && px[u] >= 0) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    if ((hit >> c & 1u) && x0[u] + c >= xa && x0[u] + c < xb) {
+                        const unsigned long long key = ((unsigned long long)__float_as_uint(c4[c]) << 32) |
+                                                       (unsigned long long)(uint32_t)(px[u] + c);
                         best = key < best ? key : best;
                     }
                 }
