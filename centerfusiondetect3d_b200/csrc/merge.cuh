@@ -123,13 +123,16 @@ __device__ __forceinline__ void merge_select(const MergeParams& p, MergeSmem& sm
                                              Emit&& emit) {
     const int list = p.list[li];
     const int K = p.K;
-    constexpr int U = MERGE_WIN / T;  // list entries per thread
-    static_assert(MERGE_WIN % T == 0 && MERGE_WIN <= CAND_CAP && MERGE_WIN <= SEL_CAP / 2, "rank window");
+    // rank window: a half of the CTA ranks up to MERGE_WIN survivors, the whole CTA a full list (K = 500 on a
+    // 225 x 400 map leaves ~1200: ranking them directly costs a third of the exact selection that would cut them to K)
+    constexpr int WIN = WHOLE ? CAND_CAP : MERGE_WIN;
+    constexpr int U = WIN / T;  // list entries per thread
+    static_assert(WIN % T == 0 && WIN <= CAND_CAP && WIN <= SEL_CAP && 256 * 4 <= MERGE_WIN * 8, "rank window");
     CF_MERGE_PROF(0);
     const unsigned long long* cand = p.cand + ((size_t)b * 2 + list) * CAND_CAP;
     int nw;  // entries of win[] to rank
     unsigned long long me[U];
-    if (n <= (uint32_t)MERGE_WIN) {
+    if (n <= (uint32_t)WIN) {
         nw = (int)n;
 #pragma unroll
         for (int u = 0; u < U; ++u) me[u] = tid + u * T < nw ? __ldcg(cand + tid + u * T) : 0ull;
@@ -145,7 +148,7 @@ __device__ __forceinline__ void merge_select(const MergeParams& p, MergeSmem& sm
     // so the list is first bucketed by key (256 linear buckets over [min key, max key], a counting sort in shared
     // memory): rank = entries of the higher buckets + larger entries of the own bucket.
     unsigned long long* sorted = sm.sc.surv;
-    uint32_t* start = reinterpret_cast<uint32_t*>(sm.sc.surv + MERGE_WIN);
+    uint32_t* start = reinterpret_cast<uint32_t*>(sm.win);  // (win[] is free: its K entries sit in me[] by now)
     const int lane = tid & 31;
     if (tid < 256) sm.sc.hist[tid] = 0u;
     if (tid == 0) {
