@@ -124,9 +124,13 @@ size_t cf_workspace_bytes(int B, int C, int H, int W, int K) {
     return workspace_layout(B, K, nullptr, nullptr) + 256;
 }
 
+static size_t pillar_rects_offset(int B, int Nmax) {
+    return ((size_t)B * (size_t)Nmax * sizeof(PaintRec) + 255) / 256 * 256;
+}
 size_t cf_pillars_workspace_bytes(int B, int Nmax) {
     if (B < 0 || Nmax < 0) return 0;
-    return (size_t)B * (size_t)Nmax * sizeof(PaintRec) + 256;
+    // paint records + the dense copy of their rectangles (8 bytes each, 256-byte aligned behind the records)
+    return pillar_rects_offset(B, Nmax) + (size_t)B * (size_t)Nmax * sizeof(short4) + 256;
 }
 
 int cf_nms(const float* heat, int B, int C, int H, int W, float* out, void* stream) {
@@ -416,7 +420,7 @@ int cf_frustum_boxes(const float* pc_dep, const float* bboxes, const float* dept
     CF_KERNEL(CF_KERNEL_ASSOC, st,
               launch_box_assoc(pc_dep, bboxes, depth, thr, counts, B, N, H, W, max_pc_dist, (PaintRec*)ws, assoc, st, &n),
               "box_assoc");
-    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint((const PaintRec*)ws, N, N, counts, B, H, W, pc_hm, nullptr, st, &n), "paint");
+    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint((const PaintRec*)ws, nullptr, N, N, counts, B, H, W, pc_hm, nullptr, st, &n), "paint");
     g_launches = n;
     return 0;
 }
@@ -438,7 +442,7 @@ int cf_frustum_boxes_f64(const float* pc_dep, const double* bboxes, const double
     CF_KERNEL(CF_KERNEL_ASSOC, st,
               launch_box_assoc_np(pc_dep, bboxes, depth, thr, counts, B, N, H, W, max_pc_dist, flags, (PaintRec*)ws, assoc, st, &n),
               "box_assoc_np");
-    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint((const PaintRec*)ws, N, N, counts, B, H, W, pc_hm, nullptr, st, &n), "paint");
+    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint((const PaintRec*)ws, nullptr, N, N, counts, B, H, W, pc_hm, nullptr, st, &n), "paint");
     g_launches = n;
     return 0;
 }
@@ -498,9 +502,12 @@ int cf_radar_pillars_flip(const double* points, const int32_t* counts, const int
     if (B == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     int n = 0;
+    // (a workspace sized for the records alone still works: the paint then reads the rectangles out of the records)
+    const size_t roff = pillar_rects_offset(B, Nmax);
+    short4* rects = ws_bytes >= roff + (size_t)B * Nmax * sizeof(short4) ? reinterpret_cast<short4*>((char*)ws + roff) : nullptr;
     CF_KERNEL(CF_KERNEL_PILLAR_RECTS, st, launch_pillar_rects(points, counts, flip, B, Nmax, cam, calib, A, img_w, img_h, H, W, pillar_dims_host[0],
-                                pillar_dims_host[1], pillar_dims_host[2], max_dist, z_offset, (PaintRec*)ws, st, &n), "pillar_rects");
-    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint((const PaintRec*)ws, Nmax, Nmax, nullptr, B, H, W, pc_dep, owner, st, &n), "paint");
+                                pillar_dims_host[1], pillar_dims_host[2], max_dist, z_offset, (PaintRec*)ws, rects, st, &n), "pillar_rects");
+    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint((const PaintRec*)ws, rects, Nmax, Nmax, nullptr, B, H, W, pc_dep, owner, st, &n), "paint");
     g_launches = n;
     return 0;
 }
@@ -556,7 +563,7 @@ extern "C" int cf_frustum_boxes_static(const float* pc_dep, const float* bboxes,
     // whatever the last call left in the array)
     CF_KERNEL(CF_KERNEL_ASSOC, st,
               launch_box_assoc(pc_dep, bboxes, depth, thr, counts, B, N, H, W, max_pc_dist, recs, assoc, st, &n), "box_assoc");
-    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint(recs, N, N, counts, B, H, W, pc_hm, nullptr, st, &n), "paint");
+    CF_KERNEL(CF_KERNEL_PAINT, st, launch_paint(recs, nullptr, N, N, counts, B, H, W, pc_hm, nullptr, st, &n), "paint");
     g_launches = n;
     return 0;
 }

@@ -13,6 +13,8 @@
 #include <math_constants.h>
 
 #include <cstring>
+#include <map>
+#include <mutex>
 
 #include "assoc.cuh"
 #include "geometry.cuh"
@@ -27,97 +29,177 @@ namespace cf {
 // Records in global memory: thousands of radar pillars (drawPcHeat under the pillar loop, nuscenes.py:234-263 /
 // generic_dataset.py:798-826) or a few dozen boxes (row f4).  Pillars overlap an order of magnitude deep (2000 pillars
 // cover 87 % of a 112x200 map eleven times over), so visiting every pixel of every rectangle is the wrong amount of work.
-// Here one WARP owns a tile of 32 columns x 32 rows, one lane per column with a 32-bit mask of its rows that already
-// have an owner.  The records are walked from the LARGEST index down, 32 at a time: each lane tests one record against
-// the tile and prepares its row mask, a ballot keeps the few that touch the tile, and for those a lane takes `rows of the
-// rectangle AND NOT filled` -- three shuffles and a handful of bit operations per (record, tile) whatever the
-// rectangle's height.  Every pixel gets its owner exactly once; no atomics; a tile whose pixels are all owned stops early.
+// Here a CTA owns a strip of 32 columns x 128 rows and each of its four WARPS 8 of those columns over all the rows: lane
+// = (group of 32 rows, column), with a 32-bit mask of the lane's rows that already have an owner.  (Pillars are narrow and
+// tall: a warp that is narrow and tall meets a third of the rectangles a 32 x 32 tile does, and no tile row is hotter
+// than another.)  The CTA first stages the frame's rectangles in shared memory -- ONE pass for up to 2048 records, kept
+// in order, only those that touch the strip (a fifth) -- then every warp walks them from the LARGEST index down, 32 at a
+// time: each lane tests one record against the warp's columns, a ballot keeps the few that touch them, and for those,
+// two per trip, every lane takes `rows of the rectangle inside its group AND NOT filled` -- three shuffles and a handful
+// of bit operations per (record, warp) whatever the rectangle's height.  Every pixel gets its owner exactly once; no
+// atomics; a warp whose pixels are all owned stops early.  The kernel is bound by the length of a warp's dependent
+// instruction chain (~8 cycles per instruction with 3-4 warps per scheduler), not by memory: tools/prof_paint.py.
 // (Measured alternatives, all slower on the dense-radar workload: a thread or a warp per rectangle with atomicMax on an
-// owner map, the tile's records split over four warps with a priority merge, and column-binned lists with a sort --
-// they lose to lane divergence on the few very wide near pillars.)
+// owner map, 32 x 32 tiles, their records split over four warps with a priority merge, and column-binned lists with a
+// sort -- they lose to lane divergence on the few very wide near pillars.)
 // -----------------------------------------------------------------------------------------------------
-constexpr int PT = 128;              // threads per CTA: 4 tiles
-constexpr int PAINT_REC_CAP = 1536;  // records staged in shared memory per pass (8 bytes each; static shared memory <= 48 KB)
+#ifdef CFD3D_PROFILE
+__device__ long long g_paint_prof[4096 * 16];
+#define PP(i) do { if (lane == 0 && wid < 4096) g_paint_prof[wid * 16 + (i)] = clock64(); } while (0)
+#define PPV(i, v) do { if (lane == 0 && wid < 4096) g_paint_prof[wid * 16 + (i)] = (v); } while (0)
+#else
+#define PP(i) do { } while (0)
+#define PPV(i, v) do { } while (0)
+#endif
+constexpr int PT = 128;              // threads per CTA: a strip of 32 columns x up to 128 rows
+constexpr int PAINT_LU = 16;         // records a thread examines per pass (2048 per pass: a frame's pillars in one)
+constexpr int PAINT_REC_CAP = PAINT_LU * PT;  // records examined per pass; those that touch the CTA's strip are staged
+                                              // in shared memory (10 bytes each; the pair lists are dynamic shared memory:
+                                              // 53 KB per CTA together, four CTAs per SM)
+constexpr int PAINT_ROWS = 128;      // rows per CTA: 4 lane groups of 32 rows
 
-__global__ void __launch_bounds__(PT) paint_kernel(const PaintRec* __restrict__ recs, int n_max, int rec_stride,
+// rects (optional): the records' rectangles once more as a dense array of 8-byte entries (same indexing as recs).  Every
+// strip of a frame examines ALL the frame's rectangles: out of 32-byte records that is a sector per rectangle and CTA
+// (7 x 64 x 2000 sectors at the dense-radar workload: the L2's request rate sets the pace), out of the dense array a quarter.
+__global__ void __launch_bounds__(PT) paint_kernel(const PaintRec* __restrict__ recs, const short4* __restrict__ rects,
+                                                   int n_max, int rec_stride,
                                                    const int32_t* __restrict__ counts, int H, int W, int tiles_x,
-                                                   int n_tiles, float* __restrict__ out, int32_t* __restrict__ owner_out) {
+                                                   float* __restrict__ out, int32_t* __restrict__ owner_out) {
     __shared__ short4 srect[PAINT_REC_CAP];
-    // per warp and lane: the (record, newly owned rows) pairs of the lane's column, at most 32 (a pair owns >= 1 row)
-    __shared__ int2 spair[PT / 32][32][32];
+    __shared__ uint16_t sidx[PAINT_REC_CAP];  // record index of a staged rectangle, relative to the pass's first
+    static_assert(PAINT_REC_CAP <= 65536, "16-bit pass-relative indices");
+    __shared__ int swsum[PT / 32];
+    // per warp and lane: the (record, newly owned rows) pairs of the lane's 32 pixels, at most 32 (a pair owns >= 1 row)
+    extern __shared__ int2 spair_dyn[];
+    int2 (*spair)[32][32] = reinterpret_cast<int2 (*)[32][32]>(spair_dyn);
     // programmatic dependent launch: placed while the kernel that produces the records drains; the next kernel of the
     // stream (the stage kernel) may be placed as this one retires
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int b = blockIdx.y;
-    const int tile = blockIdx.x * (PT / 32) + warp;
-    const bool live = tile < n_tiles;
-    const int ty = live ? tile / tiles_x : 0, tx = live ? tile - ty * tiles_x : 0;
-    const int x0 = tx * 32, y0 = ty * 32, x = x0 + lane;
+    const int wid = ((int)blockIdx.y * (int)gridDim.x + (int)blockIdx.x) * 4 + warp;
+    (void)wid;
+    long long t_stage = 0, t_walk = 0, t_mark;
+    int n_it = 0;
+    PP(0);
+    { long long gt_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_)); PPV(8, gt_); }
+    // blockIdx.x = (block of 128 rows, strip of 32 columns); a WARP owns 8 columns of the strip over all the rows: lane =
+    // (group of 32 rows, column)
+    const int tx = (int)blockIdx.x % tiles_x, Y0 = ((int)blockIdx.x / tiles_x) * PAINT_ROWS;
+    const int X0 = tx * 32, xw = X0 + 8 * warp;  // the strip's / this warp's first column
+    const int x = xw + (lane & 7), y0 = Y0 + 32 * (lane >> 3);  // this lane's column and first row
     int n = n_max;
     if (counts) n = min(n_max, counts[b]);
     const PaintRec* fr = recs + (size_t)b * rec_stride;
+    const short4* frect = rects ? rects + (size_t)b * rec_stride : nullptr;
     const size_t HW = (size_t)H * W;
-    // rows of the tile beyond the map count as filled
-    uint32_t filled = (y0 + 32 <= H) ? 0u : ~((1u << (H - y0)) - 1u);
-    if (!live || x >= W) filled = ~0u;
+    // rows beyond the map count as filled
+    uint32_t filled = (y0 + 32 <= H) ? 0u : (y0 >= H ? ~0u : ~((1u << (H - y0)) - 1u));
+    if (x >= W) filled = ~0u;
     int np = 0;  // pairs of this lane
     // records from the largest index down, PAINT_REC_CAP at a time through shared memory
     for (int hi = n; hi > 0; hi -= PAINT_REC_CAP) {
-        const int lo = max(0, hi - PAINT_REC_CAP), cnt = hi - lo;
+        const int lo = max(0, hi - PAINT_REC_CAP);
+        int cnt;  // records of this pass that touch the CTA's strip
         __syncthreads();
-        {  // (all of a thread's record loads in flight together: one memory round trip per pass)
-            constexpr int LU = PAINT_REC_CAP / PT;
+        t_mark = clock64();
+        {  // thread t examines records lo + t * LU .. + LU - 1 (all loads in flight together: one memory round trip per
+           // pass), keeps those that touch the strip, and writes them behind those of the threads before it
+            constexpr int LU = PAINT_LU;
             short4 q[LU];
+            uint32_t keep = 0u;
 #pragma unroll
             for (int u = 0; u < LU; ++u) {
-                const int i = tid + u * PT;
-                q[u] = i < cnt ? __ldg(reinterpret_cast<const short4*>(fr + lo + i)) : make_short4(0, 0, 0, 0);
+                const int i = lo + tid * LU + u;
+                q[u] = i < hi ? (frect ? __ldg(frect + i) : __ldg(reinterpret_cast<const short4*>(fr + i)))
+                              : make_short4(0, 0, 0, 0);
+                if (q[u].y > q[u].x && q[u].w > q[u].z && q[u].w > X0 && q[u].z < X0 + 32 && q[u].y > Y0 &&
+                    q[u].x < Y0 + PAINT_ROWS)
+                    keep |= 1u << u;
+            }
+            const int mine = __popc(keep);
+            int incl = mine;  // inclusive scan over the warp, then over the warps
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const int o = __shfl_up_sync(FULL, incl, off);
+                if (lane >= off) incl += o;
+            }
+            if (lane == 31) swsum[warp] = incl;
+            __syncthreads();
+            int pos = incl - mine;
+            cnt = 0;
+#pragma unroll
+            for (int w = 0; w < PT / 32; ++w) {
+                if (w < warp) pos += swsum[w];
+                cnt += swsum[w];
             }
 #pragma unroll
             for (int u = 0; u < LU; ++u) {
-                const int i = tid + u * PT;
-                if (i < cnt) srect[i] = q[u];
+                if (keep >> u & 1u) {
+                    srect[pos] = q[u];
+                    sidx[pos] = (uint16_t)(tid * LU + u);
+                    ++pos;
+                }
             }
         }
         __syncthreads();
+        t_stage += clock64() - t_mark;
+        t_mark = clock64();
         if (__all_sync(FULL, filled == ~0u)) continue;  // (still takes part in the barriers above)
         for (int base = cnt - 1; base >= 0; base -= 32) {
-            // lane-parallel: this lane's record of the step (descending index over the lanes), its relevance to the tile
-            // and its row mask inside the tile
+            // lane-parallel: this lane's record of the step (descending index over the lanes) and whether it touches
+            // the warp's 8 columns
             const int i = base - lane;
             bool rel = false;
-            int ca = 0, cb = 0;
-            uint32_t rmask = 0u;
+            uint32_t rows_ab = 0u, cols_ab = 0u;
+            int ridx = 0;
             if (i >= 0) {
                 const short4 q = srect[i];
-                rel = q.y > q.x && q.w > q.z && q.y > y0 && q.x < y0 + 32 && q.w > x0 && q.z < x0 + 32;
-                const int a = max((int)q.x - y0, 0), e = min((int)q.y - y0, 32);
-                rmask = rel ? ((e >= 32 ? ~0u : ((1u << e) - 1u)) & ~((1u << a) - 1u)) : 0u;
-                ca = q.z;
-                cb = q.w;
+                ridx = lo + (int)sidx[i];
+                rel = q.w > xw && q.z < xw + 8;
+                rows_ab = (uint32_t)(uint16_t)q.x | ((uint32_t)(uint16_t)q.y << 16);
+                cols_ab = (uint32_t)(uint16_t)q.z | ((uint32_t)(uint16_t)q.w << 16);
             }
             uint32_t m = __ballot_sync(FULL, rel);
-            // serial over the step's relevant records, largest index first: three shuffles and a few bit operations each
-            while (m) {
-                const int src = __ffs(m) - 1;
-                m &= m - 1;
-                const int qa = __shfl_sync(FULL, ca, src), qb = __shfl_sync(FULL, cb, src);
-                uint32_t rows = __shfl_sync(FULL, rmask, src);
-                rows = (x >= qa && x < qb) ? rows & ~filled : 0u;
+            // serial over the step's relevant records, largest index first, two per trip (their six shuffles are in
+            // flight together): every lane works out the rectangle's rows inside its own group of 32 and takes those
+            // that have no owner yet
+            auto take = [&](uint32_t rab, uint32_t cab, int idx) {
+                const int a = max((int)(rab & 0xffffu) - y0, 0), e = min((int)(rab >> 16) - y0, 32);
+                uint32_t rows = 0u;
+                if (e > a && x >= (int)(cab & 0xffffu) && x < (int)(cab >> 16))
+                    rows = (e >= 32 ? ~0u : ((1u << e) - 1u)) & ~((1u << a) - 1u) & ~filled;
                 if (rows) {
                     filled |= rows;
-                    spair[warp][np][lane] = make_int2(lo + base - src, (int)rows);
+                    spair[warp][np][lane] = make_int2(idx, (int)rows);
                     ++np;
                 }
+            };
+            while (m) {
+                ++n_it;
+                const int s0 = __ffs(m) - 1;
+                m &= m - 1;
+                const bool two = m != 0u;
+                const int s1 = two ? __ffs(m) - 1 : s0;
+                m &= m - 1;
+                const uint32_t rab0 = __shfl_sync(FULL, rows_ab, s0), cab0 = __shfl_sync(FULL, cols_ab, s0);
+                const int id0 = __shfl_sync(FULL, ridx, s0);
+                const uint32_t rab1 = __shfl_sync(FULL, rows_ab, s1), cab1 = __shfl_sync(FULL, cols_ab, s1);
+                const int id1 = __shfl_sync(FULL, ridx, s1);
+                take(rab0, cab0, id0);
+                if (two) take(rab1, cab1, id1);
             }
             if (__all_sync(FULL, filled == ~0u)) break;
         }
+        t_walk += clock64() - t_mark;
     }
     __syncwarp();
-    if (!live) return;
-    // pairs -> owner per row, every lane for its own column (each row belongs to at most one pair)
+    PP(1);
+    PPV(4, t_stage);
+    PPV(5, t_walk);
+    PPV(6, n_it);
+    // pairs -> owner per row, every lane for its own 32 pixels (each row belongs to at most one pair)
     int own[32];
 #pragma unroll
     for (int r = 0; r < 32; ++r) own[r] = -1;
@@ -127,11 +209,12 @@ __global__ void __launch_bounds__(PT) paint_kernel(const PaintRec* __restrict__ 
         for (int r = 0; r < 32; ++r)
             if (((uint32_t)pr.y >> r) & 1u) own[r] = pr.x;
     }
-    // the tile's pixels, each written once: a row of 32 columns per store instruction (128 bytes per plane)
+    PP(2);
+    // the lane's pixels, each written once: 8 consecutive columns (one 32-byte sector per plane) per row group and store
     float* o = out + (size_t)b * 3 * HW;
     int32_t* oo = owner_out ? owner_out + (size_t)b * HW : nullptr;
     const int rows_here = min(32, H - y0);
-    if (x < W) {
+    if (x < W && rows_here > 0) {
         constexpr int RU = 8;  // rows per step: their 3 x RU value loads are in flight together (one L2 round trip)
 #pragma unroll
         for (int r0 = 0; r0 < 32; r0 += RU) {
@@ -158,22 +241,43 @@ __global__ void __launch_bounds__(PT) paint_kernel(const PaintRec* __restrict__ 
             }
         }
     }
+    PP(3);
+    { long long gt_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_)); PPV(9, gt_); }
 }
 
-cudaError_t launch_paint(const PaintRec* recs, int n_per_frame, int rec_stride, const int32_t* counts, int B, int H,
-                         int W, float* out, int32_t* owner, cudaStream_t st, int* launches) {
-    const int tiles_x = (W + 31) / 32, tiles_y = (H + 31) / 32, n_tiles = tiles_x * tiles_y;
+constexpr size_t PAINT_DYN_SMEM = sizeof(int2) * (PT / 32) * 32 * 32;
+
+// static + dynamic shared memory exceed 48 KB: the opt-in is process-wide state of the runtime, set once per device
+static cudaError_t paint_setup() {
+    static std::mutex mu;
+    static std::map<int, cudaError_t> done;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> g(mu);
+    auto f = done.find(dev);
+    if (f != done.end()) return f->second;
+    e = cudaFuncSetAttribute(paint_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PAINT_DYN_SMEM);
+    done[dev] = e;
+    return e;
+}
+
+cudaError_t launch_paint(const PaintRec* recs, const short4* rects, int n_per_frame, int rec_stride, const int32_t* counts,
+                         int B, int H, int W, float* out, int32_t* owner, cudaStream_t st, int* launches) {
+    if (cudaError_t es = paint_setup()) return es;
+    const int tiles_x = (W + 31) / 32;
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
     memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3((n_tiles + PT / 32 - 1) / (PT / 32), B);
+    cfg.gridDim = dim3(tiles_x * ((H + PAINT_ROWS - 1) / PAINT_ROWS), B);
     cfg.blockDim = dim3(PT);
+    cfg.dynamicSmemBytes = PAINT_DYN_SMEM;
     cfg.stream = st;
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, paint_kernel, recs, n_per_frame, rec_stride, counts, H, W, tiles_x, n_tiles, out, owner);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, paint_kernel, recs, rects, n_per_frame, rec_stride, counts, H, W, tiles_x, out, owner);
     if (e == cudaSuccess) ++*launches;
     return e;
 }
@@ -481,6 +585,7 @@ struct PillarParams {
     int B, Nmax, img_w, img_h, H, W;
     double ox, oy, oz, max_dist, z_offset;
     PaintRec* recs;
+    short4* rects;  // the rectangles once more, dense (paint_kernel's staging reads these)
 };
 
 __device__ __forceinline__ double dot3(double a0, double x, double a1, double y, double a2, double z) {
@@ -500,6 +605,7 @@ __global__ void __launch_bounds__(128) pillar_rects_kernel(const PillarParams p)
     PaintRec* dst = p.recs + (size_t)b * p.Nmax + i;
     if (i >= p.counts[b]) {
         *dst = r;
+        if (p.rects) p.rects[(size_t)b * p.Nmax + i] = make_short4(0, 0, 0, 0);
         return;
     }
     const double* pt = p.points + ((size_t)b * p.Nmax + i) * 5;
@@ -565,11 +671,12 @@ __global__ void __launch_bounds__(128) pillar_rects_kernel(const PillarParams p)
         r.v2 = (float)pt[4];
     }
     *dst = r;
+    if (p.rects) p.rects[(size_t)b * p.Nmax + i] = make_short4(r.ra, r.rb, r.ca, r.cb);
 }
 
 cudaError_t launch_pillar_rects(const double* points, const int32_t* counts, const int32_t* flip, int B, int Nmax, const double* cam,
                                 const double* calib, const double* A, int img_w, int img_h, int H, int W, double ph,
-                                double pw, double pl, double max_dist, double z_offset, PaintRec* recs,
+                                double pw, double pl, double max_dist, double z_offset, PaintRec* recs, short4* rects,
                                 cudaStream_t st, int* launches) {
     PillarParams p;
     p.points = points;
@@ -577,6 +684,7 @@ cudaError_t launch_pillar_rects(const double* points, const int32_t* counts, con
     p.calib = calib;
     p.A = A;
     p.counts = counts;
+    p.rects = rects;
     p.flip = flip;
     p.B = B;
     p.Nmax = Nmax;
@@ -609,3 +717,9 @@ cudaError_t launch_pillar_rects(const double* points, const int32_t* counts, con
 }
 
 }  // namespace cf
+
+#ifdef CFD3D_PROFILE
+extern "C" __attribute__((visibility("default"))) int cf_debug_read_paint_prof(long long* out, int n) {
+    return (int)cudaMemcpyFromSymbol(out, cf::g_paint_prof, sizeof(long long) * 16 * n);
+}
+#endif

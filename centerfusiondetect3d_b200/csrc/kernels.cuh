@@ -126,8 +126,8 @@ cudaError_t launch_radar_sort(const double* points, const int32_t* counts, int B
 int debug_read_prof(long long* out, int n_cta);  // -DCFD3D_PROFILE builds only
 void debug_set_plan(int force_cs, int max_clusters);
 void last_plan(cf_plan_info_t* out);
-cudaError_t launch_paint(const PaintRec* recs, int n_per_frame, int rec_stride, const int32_t* counts, int B, int H,
-                         int W, float* out, int32_t* owner, cudaStream_t st, int* launches);
+cudaError_t launch_paint(const PaintRec* recs, const short4* rects, int n_per_frame, int rec_stride, const int32_t* counts,
+                         int B, int H, int W, float* out, int32_t* owner, cudaStream_t st, int* launches);
 cudaError_t launch_nms(const float* heat, int B, int C, int H, int W, float* out, cudaStream_t st, int* launches);
 cudaError_t launch_gather(const float* feat, int B, int ch, int64_t HW, const int64_t* inds, int M, float* out,
                           cudaStream_t st, int* launches);
@@ -139,7 +139,7 @@ cudaError_t launch_pc2hm_single(float* pc_hm, const float* pc_dep, int H, int W,
                                 cudaStream_t st, int* launches);
 cudaError_t launch_pillar_rects(const double* points, const int32_t* counts, const int32_t* flip, int B, int Nmax, const double* cam,
                                 const double* calib, const double* A, int img_w, int img_h, int H, int W, double ph,
-                                double pw, double pl, double max_dist, double z_offset, PaintRec* recs,
+                                double pw, double pl, double max_dist, double z_offset, PaintRec* recs, short4* rects,
                                 cudaStream_t st, int* launches);
 
 }  // namespace cf
