@@ -101,6 +101,32 @@ def test_golden_pillars(ops):
         assert ((npy(owner) >= 0) == (ref[:, 0] != 0)).all()
 
 
+def test_pillars_with_a_records_only_workspace(ops):
+    """cf_radar_pillars sizes its workspace with cf_pillars_workspace_bytes (records + the dense rectangle array the
+    paint stages from); a caller that still passes the records-only size of earlier builds (B * Nmax * 32 + 256) gets the
+    same pc_dep -- the paint then reads the rectangles out of the records."""
+    import ctypes as C
+    from centerfusiondetect3d_b200 import _lib
+    g = load_golden("pillars")
+    L = _lib.lib()
+    for tag in "ac":
+        H, W = (int(v) for v in g[f"in_hw_{tag}"])
+        calib = g[f"in_calib_{tag}"]
+        pts, cnt = cu(g[f"in_points_{tag}"]), cu(g[f"in_counts_{tag}"].astype(np.int32))
+        cam, cal, A = cu(np.ascontiguousarray(calib[:, :, :3])), cu(calib), cu(g[f"in_A_{tag}"])
+        B, Nmax, _ = pts.shape
+        small = B * Nmax * 32 + 256
+        assert small < L.cf_pillars_workspace_bytes(B, Nmax)
+        ws = torch.empty(small, dtype=torch.uint8, device=DEV)
+        out = torch.full((B, 3, H, W), float("nan"), device=DEV)
+        pd = (C.c_double * 3)(1.5, 0.2, 0.2)
+        rc = L.cf_radar_pillars(pts.data_ptr(), cnt.data_ptr(), B, Nmax, cam.data_ptr(), cal.data_ptr(), A.data_ptr(), 1600, 900,
+                                H, W, pd, 60.0, 0.0, out.data_ptr(), None, ws.data_ptr(), small,
+                                torch.cuda.current_stream().cuda_stream)
+        assert rc == 0, L.cf_last_error().decode()
+        eq(npy(out), g[f"out_pc_dep_{tag}"], f"pillars {tag}, records-only workspace")
+
+
 def test_golden_frustum(ops):
     g = load_golden("frustum_decode")
     K = int(g["in_K"])
