@@ -297,7 +297,10 @@ CF_API int cf_fusion_stage_post(const float* heat, const float* wh, const float*
  * ascending by Z by the caller (np.argsort in the reference is unstable: order is an input contract);
  * counts (B) i32; cam (B,3,3) fp64 intrinsic; calib (B,3,4) fp64; A (B,2,3) fp64 output affine;
  * pillar_dims_host: 3 doubles (h,w,l) on the HOST.  Writes pc_dep (B,3,H,W) fp32 completely; owner (B,H,W)
- * i32 optional = index of the surviving point per pixel or -1. */
+ * i32 optional = index of the surviving point per pixel or -1.
+ * ws: cf_pillars_workspace_bytes(B, Nmax) bytes = the paint records (32 bytes per point) + a dense 8-byte copy of their
+ * rectangles that the paint stages from; a workspace of B * Nmax * 32 bytes alone is accepted too (the paint then reads
+ * the rectangles out of the records: same result, slower). */
 CF_API size_t cf_pillars_workspace_bytes(int B, int Nmax);
 CF_API int cf_radar_pillars(const double* points, const int32_t* counts, int B, int Nmax, const double* cam,
                             const double* calib, const double* A, int img_w, int img_h, int H, int W,
