@@ -29,18 +29,7 @@
 
 namespace cf {
 
-constexpr int MERGE_WIN = 1024;  // survivors ranked directly; more go through block_select first
-
-
-template <int T>
-struct ListSrc {
-    const unsigned long long* cand;
-    int n_in, n_round;
-    template <class F>
-    __device__ __forceinline__ void for_each(F&& f) const {
-        for (int i = threadIdx.x; i < n_round; i += T) f(i < n_in ? __ldcg(cand + i) : 0ull);
-    }
-};
+constexpr int MERGE_WIN = 1024;  // survivors a HALF of the CTA ranks directly (the whole CTA: a full list, CAND_CAP)
 
 // overflow path: the frame itself as the source (slow, exact; only reached under massive ties)
 template <int T>
@@ -82,28 +71,19 @@ struct MergeSmem {
     unsigned long long win[MERGE_WIN];
 };
 
-// more survivors than the rank window (dense ties), or a list flagged overflowed: exact block-level selection of the
-// K best into win[] from the list or, failing that, from the frame itself.  Slow, exact, rare -> never inlined.
+// a list that overflowed its CAND_CAP slots (dense ties), or was flagged so (no useful bound): exact block-level
+// selection of the K best into win[] from the frame itself.  Slow, exact, rare -> never inlined.
 template <int T>
-__device__ __noinline__ void select_overflow(const MergeParams& p, MergeSmem& sm, int b, int list, uint32_t n,
-                                             const unsigned long long* cand) {
+__device__ __noinline__ void select_overflow(const MergeParams& p, MergeSmem& sm, int b, int list) {
     const int K = p.K, HWi = p.H * p.W;
-    if (n <= (uint32_t)CAND_CAP) {
-        ListSrc<T> src;
-        src.cand = cand;
-        src.n_in = (int)n;
-        src.n_round = (src.n_in + T - 1) / T * T;
-        block_select<T, 1>(src, K, sm.sc, [&](uint32_t slot, unsigned long long c) { sm.win[slot] = c; });
-    } else {
-        FrameSrc<T> src;
-        src.frame = p.heat + (size_t)b * p.C * HWi;
-        src.CH = p.C * p.H;
-        src.H = p.H;
-        src.W = p.W;
-        src.n_round = (p.C * HWi + T - 1) / T * T;
-        src.nms = list == 1;
-        block_select<T, 1>(src, K, sm.sc, [&](uint32_t slot, unsigned long long c) { sm.win[slot] = c; });
-    }
+    FrameSrc<T> src;
+    src.frame = p.heat + (size_t)b * p.C * HWi;
+    src.CH = p.C * p.H;
+    src.H = p.H;
+    src.W = p.W;
+    src.n_round = (p.C * HWi + T - 1) / T * T;
+    src.nms = list == 1;
+    block_select<T, 1>(src, K, sm.sc, [&](uint32_t slot, unsigned long long c) { sm.win[slot] = c; });
     __syncthreads();
 }
 
@@ -116,8 +96,9 @@ __device__ __forceinline__ void group_sync(int bar) {
 
 // The sorted top-K of job li by the thread group (tid in [0, T); named barrier `bar`, or the whole CTA): emit(rank, composite) for every element
 // of the K best.  Composites are distinct, so ranks are a permutation.  n = survivors appended to the job's list (>= K by
-// construction; the caller read the cluster's counter).  Lists longer than the rank window (dense ties) or flagged
-// overflowed need the exact block-level selection first, which only the whole CTA can run (WHOLE).
+// construction; the caller read the cluster's counter).  A half of the CTA takes lists up to MERGE_WIN entries, the whole
+// CTA any list that fits its slots; one that overflowed them (dense ties) or was flagged overflowed needs the exact
+// block-level selection from the frame first, which only the whole CTA can run (WHOLE).
 template <int T, bool WHOLE, class Emit>
 __device__ __forceinline__ void merge_select(const MergeParams& p, MergeSmem& sm, int b, int li, int tid, int bar, uint32_t n,
                                              Emit&& emit) {
@@ -137,7 +118,7 @@ __device__ __forceinline__ void merge_select(const MergeParams& p, MergeSmem& sm
 #pragma unroll
         for (int u = 0; u < U; ++u) me[u] = tid + u * T < nw ? __ldcg(cand + tid + u * T) : 0ull;
     } else {
-        if (WHOLE) select_overflow<T>(p, sm, b, list, n, cand);  // rare, out of line: keeps the common path's code small
+        if (WHOLE) select_overflow<T>(p, sm, b, list);  // rare, out of line: keeps the common path's code small
         nw = K;
 #pragma unroll
         for (int u = 0; u < U; ++u) me[u] = tid + u * T < nw ? sm.win[tid + u * T] : 0ull;
