@@ -503,11 +503,16 @@ __device__ __forceinline__ void merge_tail_decode(const MergeParams& p, int n_jo
 // the DRAM at the same moment from every cluster, and whoever is served last sets the pace of the phase.  The frustum
 // epilogue starts as soon as ITS group has landed.  defer_decode (one batch only): the decode epilogue is left to the
 // caller (merge_tail_decode on a few warps beside the association's ROI scans); the closing barrier here comes after
-// every thread has waited for its decode copies.
+// every thread has waited for its decode copies.  late_d (with defer_decode; CTAs that own many detections): the decode
+// job's copies are not even issued here -- an SM moves ~0.15 scattered sectors per clock, and a thread that issues
+// copies into a full queue stalls: the caller's late_dw decode warps leave as soon as the frustum job's copies have
+// landed, issue the decode job's, wait for them and run the decode epilogue, beside the frustum epilogue and the ROI
+// scans of the other warps.
 template <int T, bool FUSED>
 __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int b, int first, int stride, int n_local,
                                            const unsigned long long* xs_comp, const int32_t* xs_ind, float* gath, int GB,
-                                           DetParam* sdet, short4* sroi, const float* cal, bool defer_decode) {
+                                           DetParam* sdet, short4* sroi, const float* cal, bool defer_decode, int late_dw = 0) {
+    const bool late_d = late_dw > 0;  // (number of decode warps)
     const int K = p.K, HWi = p.H * p.W;
     const int tid = (int)threadIdx.x;
     for (int kl0 = 0; kl0 < n_local; kl0 += GB) {
@@ -515,8 +520,9 @@ __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int
         if (FUSED) {  // group 0: the frustum job (job 0), group 1: the decode job (job 1)
             gather_issue<FS_N>(p.job[0].gt, b, (size_t)HWi, xs_ind, first, stride, kl0, nb, gath, tid, T);
             cp_async_commit();
-            gather_issue<DS_N>(p.job[1].gt, b, (size_t)HWi, xs_ind + K, first, stride, kl0, nb,
-                               gath + (size_t)GB * GATH_STRIDE, tid, T);
+            if (!late_d)
+                gather_issue<DS_N>(p.job[1].gt, b, (size_t)HWi, xs_ind + K, first, stride, kl0, nb,
+                                   gath + (size_t)GB * GATH_STRIDE, tid, T);
             cp_async_commit();
         } else {
 #pragma unroll
@@ -537,6 +543,17 @@ __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int
         cp_async_wait<1>();
         __syncthreads();
         CF_MERGE_PROF(3);
+        if (FUSED && late_d) {
+            // the decode warps leave now (the caller has them issue the decode job's copies); the others run the frustum
+            // epilogue and meet at a barrier of their own (one batch: defer_decode)
+            const int Td = T - late_dw * 32;
+            if (tid >= Td) return;
+            epilogue_frustum(p, p.job[0], b, xs_comp, xs_ind, first, stride, kl0, nb, gath, sdet, sroi, cal, tid, Td);
+            CF_MERGE_PROF(7);
+            asm volatile("bar.sync 4, %0;" ::"r"(Td) : "memory");
+            CF_MERGE_PROF(4);
+            return;
+        }
         if (FUSED) {
             epilogue_frustum(p, p.job[0], b, xs_comp, xs_ind, first, stride, kl0, nb, gath, sdet, sroi, cal, tid, T);
         } else {
@@ -551,7 +568,7 @@ __device__ __forceinline__ void merge_tail(const MergeParams& p, int n_jobs, int
             }
         }
         CF_MERGE_PROF(7);
-        cp_async_wait<0>();  // (this thread's decode copies: prefetched into L2 long ago, issued a phase ago)
+        if (!late_d) cp_async_wait<0>();  // (this thread's decode copies: prefetched into L2 long ago, issued a phase ago)
         if (!defer_decode) {
             __syncthreads();
             merge_tail_decode<FUSED>(p, n_jobs, b, first, stride, kl0, nb, xs_comp, gath, GB, tid, T);

@@ -182,6 +182,9 @@ struct StageParams {
     int wl_entries;    // words of the pass-B work list
     int g_log2;        // a lane's group in passes A / B = 2^g_log2 float4 items of a chunk (32 << g_log2 >= R * Wp / 4) ...
     int g_contig;      // ... consecutive ones (1) or every 32nd (0)
+    int late_iw;       // ... of which this many issue the copies
+    int late_decode;   // > 0: this many decode warps issue the decode job's gathers themselves and run its epilogue beside
+                       // the frustum epilogue and the ROI scans (merge_tail, late_dw)
     int hot_passes;    // hot prefetch: 2 = frustum + decode channels, 1 = frustum only, 0 = none
     int gmax_off;      // streamed shares: byte offset (from the histogram) of the per-(chunk, lane) group maxima, then the flagged list
     int fl_cap;        // capacity of the flagged-group list
@@ -995,7 +998,7 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
         const bool defer_decode = do_frustum && n_jobs == 2 && n_local <= p.GB && n_local <= ST / 2;
         merge_tail<ST, FUSED>(mp, n_jobs, b, (int)rank, (int)cs, n_local, xs_comp, xs_ind, reinterpret_cast<float*>(smem + p.off_gath),
                        p.GB, sdet, do_frustum ? reinterpret_cast<short4*>(smem + p.off_best) : nullptr,
-                       do_frustum ? s_cal : nullptr, defer_decode);
+                       do_frustum ? s_cal : nullptr, defer_decode, (FUSED && defer_decode) ? p.late_decode : 0);
         PROF(24);
         if (!do_frustum) continue;
 
@@ -1014,7 +1017,8 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
             // once per detection on one warp and is priced by its instruction count)
             // (deferred decode epilogue: the last DW warps run it now, beside the scans of the others -- its copies landed
             // before the tail's closing barrier)
-            constexpr int DW = 3;
+            const bool late_d = FUSED && defer_decode && p.late_decode;  // (FUSED: job 1 is the decode job)
+            const int DW = late_d ? p.late_decode : 3;
             const int nsw = defer_decode ? SNW - DW : SNW;  // scanning warps
             // The two velocity values of a match are LOADED by the warp that found it (lanes 0, 1) and parked in the
             // detection's parameters one scan later (the box corners there are dead by now): the finishing threads below
@@ -1032,6 +1036,17 @@ __global__ void __launch_bounds__(ST, 1) fusion_stage_kernel(const __grid_consta
                     vpend = __ldg(p.pc_vel + (size_t)b * 3 * HW + (size_t)(lane + 1) * HW + (uint32_t)best);
             };
             if (warp >= nsw) {
+                if (late_d) {  // the decode job's copies: issued, awaited and consumed by these warps alone
+                    const int iw = min(DW, max(1, p.late_iw));  // (issuing warps: few, so that the SM's queue of scattered
+                                                                 // requests leaves room for everybody else's accesses)
+                    if (warp - nsw < iw)
+                        gather_issue<DS_N>(mp.job[1].gt, b, HW, xs_ind + K, (int)rank, (int)cs, 0, n_local,
+                                           reinterpret_cast<float*>(smem + p.off_gath) + (size_t)p.GB * GATH_STRIDE,
+                                           tid - (ST - DW * 32), iw * 32);
+                    cp_async_commit();
+                    cp_async_wait<0>();
+                    asm volatile("bar.sync 3, %0;" ::"r"(DW * 32) : "memory");
+                }
                 CF_PROF_SLOT(ST - DW * 32, 35, 0);
                 merge_tail_decode<FUSED>(mp, n_jobs, b, (int)rank, (int)cs, 0, n_local, xs_comp,
                                   reinterpret_cast<const float*>(smem + p.off_gath), p.GB, tid - (ST - DW * 32), DW * 32);
@@ -1125,12 +1140,18 @@ struct StageEnv {
     bool verbose, no_pdl;
     int prof, force_cs;
     long long chunk_bytes;
+    int late_min, late_dw, late_iw;
     StageEnv() {
         verbose = getenv("CFD3D_VERBOSE") != nullptr;
         no_pdl = getenv("CFD3D_NO_PDL") != nullptr;
         prof = getenv("CFD3D_PROF") ? atoi(getenv("CFD3D_PROF")) : 0;
         force_cs = getenv("CFD3D_FORCE_CS") ? atoi(getenv("CFD3D_FORCE_CS")) : 0;  // plan exploration (tools/plan_sweep.sh)
         chunk_bytes = 8192;
+        late_min = getenv("CFD3D_LATE_MIN") ? atoi(getenv("CFD3D_LATE_MIN")) : 48;  // detections per CTA (development sweep)
+        // (measured on 256 single-CTA frames: 4 decode warps of which 1 issues -> 151.7 us; 3 / 3 -> 153.6; 5 / 5 -> 158.9;
+        // without the late decode 162.4)
+        late_dw = getenv("CFD3D_LATE_DW") ? atoi(getenv("CFD3D_LATE_DW")) : 4;
+        late_iw = getenv("CFD3D_LATE_IW") ? atoi(getenv("CFD3D_LATE_IW")) : 1;
         if (const char* e = getenv("CFD3D_CHUNK_BYTES")) {
             if (atoll(e) >= 256) chunk_bytes = atoll(e);
         }
@@ -1451,6 +1472,8 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     // barrier before hides most of them, and 15 us on one, where the prefetches only move the same wait into that barrier
     // (measured: 4.8 + 12.1 us with, 1.2 + 15.5 us without; 256 frames 163.8 -> 161.6 us).
     p.hot_passes = best.cs == 1 ? 0 : 2;
+    p.late_iw = stage_env().late_iw;
+    p.late_decode = (K + best.cs - 1) / best.cs >= stage_env().late_min ? stage_env().late_dw : 0;
     p.gmax_off = best.gmax_off;
     p.fl_cap = best.fl_cap;
     p.ctr = ws.ctr;
