@@ -1147,7 +1147,7 @@ struct StageEnv {
         prof = getenv("CFD3D_PROF") ? atoi(getenv("CFD3D_PROF")) : 0;
         force_cs = getenv("CFD3D_FORCE_CS") ? atoi(getenv("CFD3D_FORCE_CS")) : 0;  // plan exploration (tools/plan_sweep.sh)
         chunk_bytes = 8192;
-        late_min = getenv("CFD3D_LATE_MIN") ? atoi(getenv("CFD3D_LATE_MIN")) : 48;  // detections per CTA (development sweep)
+        late_min = getenv("CFD3D_LATE_MIN") ? atoi(getenv("CFD3D_LATE_MIN")) : 16;  // detections per CTA (development sweep: 25 per CTA, cfg2, 33.9 -> 32.9 us)
         // (measured on 256 single-CTA frames: 4 decode warps of which 1 issues -> 151.7 us; 3 / 3 -> 153.6; 5 / 5 -> 158.9;
         // without the late decode 162.4)
         late_dw = getenv("CFD3D_LATE_DW") ? atoi(getenv("CFD3D_LATE_DW")) : 4;
