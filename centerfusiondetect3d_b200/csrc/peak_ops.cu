@@ -47,6 +47,12 @@ void finish_job(MergeJob* job) {
         tab_set(gt, FS_DEPTH, job->fh.depth, 1);
         tab_set(gt, FS_DIM, job->fh.dim, 3);
         tab_set(gt, FS_ROT, job->fh.rot, 8);
+        // channels the frustum geometry never reads are not gathered (their slots read 0): the height of the box
+        // (getDistanceThresh takes the corners' x / z extent only, pointcloud.py:214-236) and the two bin scores
+        // get_alpha does not compare (rot[:, 0], rot[:, 4]; pointcloud.py:195-211)
+        gt.base[FS_DIM + 0] = nullptr;
+        gt.base[FS_ROT + 0] = nullptr;
+        gt.base[FS_ROT + 4] = nullptr;
         gt.n = FS_N;
     } else if (job->epilogue == EPI_DECODE) {
         const cf_decode_heads_t& h = job->dec.heads;
