@@ -1474,6 +1474,10 @@ cudaError_t launch_fusion_stage(const float* heat, int B, int C, int H, int W, i
     p.hot_passes = best.cs == 1 ? 0 : 2;
     p.late_iw = stage_env().late_iw;
     p.late_decode = (K + best.cs - 1) / best.cs >= stage_env().late_min ? stage_env().late_dw : 0;
+    // (with the decode job's copies off the association's path, prefetching THEIR sectors only delays the frustum job's
+    // in the same queue: frustum channels alone for clusters of 2 and 4 -- cfg2 32.8 -> 31.9 us, cfg4 89.7 -> 88.9; a
+    // cluster of 8 on a full-resolution map still gains from both, 72.9 vs 73.9)
+    if (p.late_decode && best.cs > 1 && best.cs <= 4) p.hot_passes = 1;
     p.gmax_off = best.gmax_off;
     p.fl_cap = best.fl_cap;
     p.ctr = ws.ctr;
